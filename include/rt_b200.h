@@ -1,0 +1,212 @@
+/* rt_b200.h — C ABI of the B200-native path tracer (librt_b200.so).
+ *
+ * This is the drop-in boundary for ONE path of addiswebb/ray_tracer: the compute entry of
+ * shaders/ray_tracer.wgsl plus the wgpu dispatch / accumulation plumbing around it in
+ * src/core/{ray_tracer,context,texture}.rs.  The reference has no FFI of its own (its only
+ * public symbol is `pub async fn run()`, src/lib.rs:10); each entry point below replaces
+ * the wgpu call(s) cited next to it, which is what a Rust `extern "C"` block would bind
+ * (see INTEGRATION.md for that stub).
+ *
+ * Plain C: opaque handle, POD records byte-identical to the reference's #[repr(C)]
+ * structs, caller-owned buffers, integer status codes.  No exceptions or panics cross
+ * this boundary.  A context is bound to one CUDA device and is not thread-safe (the
+ * reference drives wgpu from the single winit thread, src/lib.rs:23-69).
+ */
+#ifndef RT_B200_H
+#define RT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- records (layouts: SURVEY.md §3.4(17)) ------------------------------------------ */
+
+/* src/core/context.rs:11-21 `Params`; shaders/ray_tracer.wgsl:1-8 reads the first 24 B. */
+typedef struct rt_params {
+    uint32_t width;
+    uint32_t height;
+    int32_t number_of_bounces;   /* the shader traces number_of_bounces+1 segments (wgsl:233) */
+    int32_t rays_per_pixel;      /* the shader takes rays_per_pixel+1 samples, divides by rays_per_pixel (wgsl:312,326) */
+    int32_t skybox;              /* WGSL name: toggle (wgsl:274) */
+    int32_t frames;              /* host-owned counter: Context::update, context.rs:180-184 */
+    int32_t accumulate;          /* host-only */
+} rt_params;
+
+/* src/core/camera.rs:9-29 `CameraUniform` (128 B); wgsl:69-80. */
+typedef struct rt_camera_uniform {
+    float origin[3];            float _padding1;
+    float lower_left_corner[3]; float _padding2;
+    float horizontal[3];        float _padding3;
+    float vertical[3];          float _padding4;
+    float near_;                float far_;      float _padding5[2];
+    float w[3];                 float _padding6;
+    float u[3];                 float _padding7;
+    float v[3];                 float lens_radius;
+} rt_camera_uniform;
+
+/* src/core/scene.rs:11-21 `Sphere` (64 B); wgsl:9-20. smoothness == -1.0 selects glass. */
+typedef struct rt_sphere {
+    float position[3];
+    float radius;
+    float color[4];
+    float emission_color[4];
+    float emission_strength;
+    float smoothness;
+    float _padding[2];
+} rt_sphere;
+
+/* src/core/scene.rs:23-37 `Mesh` (80 B); wgsl:27-33. `first` indexes indices[], `offset`
+ * is added to every index to address vertices[]; several records may alias one range
+ * with different `pos` (translation-only instancing). */
+typedef struct rt_mesh {
+    uint32_t first;
+    uint32_t triangles;
+    uint32_t offset;
+    float _padding;
+    float pos[3];
+    float _padding2;
+    float color[4];
+    float emission_color[4];
+    float emission_strength;
+    float specular;             /* WGSL: material.smoothness */
+    float _padding3[2];
+} rt_mesh;
+
+/* src/core/scene.rs:79-86 `Vertex` (32 B); wgsl:22-25. */
+typedef struct rt_vertex {
+    float pos[3];
+    float _padding1;
+    float normal[3];
+    float _padding2;
+} rt_vertex;
+
+/* Device-side counters since the last rt_reset_counters(). A "ray" is one call of
+ * calculate_ray_collions (wgsl:234), i.e. one path segment, primary included. */
+typedef struct rt_counters {
+    uint64_t rays;            /* path segments traced */
+    uint64_t samples;         /* camera paths started */
+    uint64_t node_visits;     /* BVH nodes fetched (only with RT_OPT_DETAIL_COUNTERS) */
+    uint64_t prim_tests;      /* sphere + triangle tests (only with RT_OPT_DETAIL_COUNTERS) */
+    uint64_t dispatches;      /* reference-equivalent dispatches executed */
+    double kernel_ms;         /* summed CUDA-event time of the trace kernel launches */
+    uint64_t launches;        /* trace kernel launches */
+} rt_counters;
+
+/* ---- status codes ------------------------------------------------------------------- */
+enum {
+    RT_OK = 0,
+    RT_ERR_INVALID_ARGUMENT = -1,
+    RT_ERR_CUDA = -2,
+    RT_ERR_NO_SCENE = -3,
+    RT_ERR_OUT_OF_MEMORY = -4,
+    RT_ERR_BAD_INDEX = -5,       /* an index/first/offset addresses outside the arrays */
+    RT_ERR_UNSUPPORTED = -6
+};
+
+/* ---- options ------------------------------------------------------------------------ */
+enum {
+    RT_OPT_TRAVERSAL = 1,        /* 0 = LBVH (default), 1 = exhaustive brute force (validation) */
+    RT_OPT_SEED_MODE = 2,        /* 0 = strict: f32->u32 saturates (WGSL rule; default) */
+    RT_OPT_PRIMARY_IDS = 3,      /* 1 = record the primary-hit AOV on the next render call */
+    RT_OPT_DETAIL_COUNTERS = 4,  /* 1 = count node visits / primitive tests (slower kernel) */
+    RT_OPT_FRAMES_PER_LAUNCH = 5,/* max reference dispatches fused into one kernel launch (default 64; 1 = one launch per dispatch like the reference) */
+    RT_OPT_LEAF_SIZE = 6         /* max primitives per BVH leaf (1..8, default 4); takes effect at the next rt_upload_scene */
+};
+
+typedef struct rt_ctx rt_ctx;
+
+/* Last error text of `ctx` (or of the failed rt_create when ctx == NULL). Never NULL. */
+const char* rt_last_error(const rt_ctx* ctx);
+
+/* Library/ABI version: (major << 16) | minor. */
+uint32_t rt_version(void);
+
+/* Replaces Context::new's device + Texture::new(w,h,Rgba32Float) (context.rs:41-72,101;
+ * texture.rs:6-31): binds CUDA device `device`, allocates the zero-filled W*H RGBA32F
+ * accumulation image. */
+int rt_create(rt_ctx** out, int device, uint32_t width, uint32_t height);
+
+/* Rust Drop of Context/RayTracer/Texture. NULL is allowed. */
+void rt_destroy(rt_ctx* ctx);
+
+/* Replaces Scene::{sphere,vertex,index,mesh}_buffer (scene.rs:478-507) and the storage
+ * bindings 3..6 of RayTracer::new (ray_tracer.rs:51-94,97-130).  Inputs are borrowed for
+ * the call only.  Zero counts (with NULL pointers) and 0-triangle meshes are legal.
+ * Validates every index, repacks to the SoA device layout and builds the LBVH on the GPU. */
+int rt_upload_scene(rt_ctx* ctx,
+                    const rt_sphere* spheres, uint32_t n_spheres,
+                    const rt_vertex* vertices, uint32_t n_vertices,
+                    const uint32_t* indices, uint32_t n_indices,
+                    const rt_mesh* meshes, uint32_t n_meshes);
+
+/* queue.write_buffer(camera.buffer, uniform) — context.rs:185. */
+int rt_set_camera(rt_ctx* ctx, const rt_camera_uniform* camera);
+
+/* queue.write_buffer(params_buffer, params) — context.rs:186 (also :138,:145).
+ * width/height must equal the context's current size (use rt_resize to change it). */
+int rt_set_params(rt_ctx* ctx, const rt_params* params);
+
+/* The compute pass dispatch_workgroups(ceil(W/8),ceil(H/8),1) — context.rs:196-208 — with
+ * the currently set params (including params.frames). Asynchronous on the context stream. */
+int rt_dispatch(rt_ctx* ctx);
+
+/* n_frames consecutive reference dispatches with params.frames = first_frame,
+ * first_frame+1, ... (what Context::update + render do per redraw, context.rs:176-208),
+ * fused into as few launches as RT_OPT_FRAMES_PER_LAUNCH allows; results are identical to
+ * n_frames rt_dispatch calls. With a shard set (rt_set_shard) only this rank's share is
+ * rendered. Asynchronous. */
+int rt_render_frames(rt_ctx* ctx, int32_t first_frame, uint32_t n_frames);
+
+/* Wait for all work queued on the context (the implicit wait of queue.submit + present,
+ * context.rs:291-292). */
+int rt_sync(rt_ctx* ctx);
+
+/* Context::resize (context.rs:126-142): new zero-filled accumulation image. The caller
+ * then sets params (frames = -1 upstream) and camera aspect as the reference does. */
+int rt_resize(rt_ctx* ctx, uint32_t width, uint32_t height);
+
+/* Zero-fill the accumulation image (a fresh wgpu texture). */
+int rt_clear(rt_ctx* ctx);
+
+/* Multi-GPU partition of the image/sample space (no reference counterpart).
+ * tile_rank/tile_world: 8x8-pixel tiles are dealt round-robin, tile t -> rank t % world;
+ * pixels of other ranks' tiles are left untouched.  frame_rank/frame_world: of the frames
+ * passed to rt_render_frames only those with (frame - first_frame) % world == rank are
+ * rendered, and the running mean weights count this rank's own frames.
+ * world = 1 disables the respective sharding. */
+int rt_set_shard(rt_ctx* ctx, uint32_t tile_rank, uint32_t tile_world,
+                 uint32_t frame_rank, uint32_t frame_world);
+
+int rt_set_option(rt_ctx* ctx, int option, int64_t value);
+int rt_get_option(const rt_ctx* ctx, int option, int64_t* value);
+
+/* Read-out (no upstream counterpart: the texture is only ever sampled by render.wgsl).
+ * Row 0 is the BOTTOM image row, x grows along camera `u`. Synchronous. */
+int rt_read_accum(rt_ctx* ctx, float* rgba, size_t n_floats);          /* W*H*4 */
+int rt_write_accum(rt_ctx* ctx, const float* rgba, size_t n_floats);   /* restore a saved image */
+/* What shaders/render.wgsl:34-39 + the sRGB swapchain (context.rs:75-80) show: clamp to
+ * [0,1], sRGB OETF, 8 bits per channel. */
+int rt_read_rgba8(rt_ctx* ctx, uint8_t* rgba, size_t n_bytes);          /* W*H*4 */
+/* Primary-hit AOV of the last render call made with RT_OPT_PRIMARY_IDS = 1: global
+ * primitive order index (spheres, then triangles mesh by mesh) or 0xFFFFFFFF. */
+int rt_read_primary_ids(rt_ctx* ctx, uint32_t* ids, size_t n);           /* W*H */
+
+int rt_get_counters(rt_ctx* ctx, rt_counters* out);
+int rt_reset_counters(rt_ctx* ctx);
+
+/* Raw device access for host-side plumbing (NCCL combine, CUDA-event timing on the
+ * stream the kernels are launched on). */
+void* rt_accum_device_ptr(rt_ctx* ctx);     /* float4[W*H] */
+void* rt_cuda_stream(rt_ctx* ctx);          /* cudaStream_t */
+int rt_device(const rt_ctx* ctx);
+
+/* BVH introspection for tests: number of nodes, leaves, max depth of the last build. */
+int rt_bvh_stats(rt_ctx* ctx, uint32_t* n_prims, uint32_t* n_nodes, uint32_t* max_depth);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RT_B200_H */

@@ -1,0 +1,435 @@
+// rt_api.cu — the C ABI of include/rt_b200.h over the CUDA kernels.
+// Every entry point cites (in the header) the wgpu call of the reference it replaces.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+#include <string>
+#include <vector>
+#include "rt_kernels.h"
+
+static_assert(sizeof(rt_params) == 28, "Params is 7 x 4 B (context.rs:11-21)");
+static_assert(sizeof(rt_camera_uniform) == 128 && offsetof(rt_camera_uniform, lower_left_corner) == 16 &&
+              offsetof(rt_camera_uniform, horizontal) == 32 && offsetof(rt_camera_uniform, vertical) == 48 &&
+              offsetof(rt_camera_uniform, w) == 80 && offsetof(rt_camera_uniform, u) == 96 &&
+              offsetof(rt_camera_uniform, v) == 112 && offsetof(rt_camera_uniform, lens_radius) == 124,
+              "CameraUniform layout (camera.rs:9-29)");
+static_assert(sizeof(rt_sphere) == 64 && offsetof(rt_sphere, radius) == 12 && offsetof(rt_sphere, color) == 16 &&
+              offsetof(rt_sphere, emission_color) == 32 && offsetof(rt_sphere, emission_strength) == 48 &&
+              offsetof(rt_sphere, smoothness) == 52, "Sphere layout (scene.rs:11-21)");
+static_assert(sizeof(rt_mesh) == 80 && offsetof(rt_mesh, pos) == 16 && offsetof(rt_mesh, color) == 32 &&
+              offsetof(rt_mesh, emission_color) == 48 && offsetof(rt_mesh, emission_strength) == 64 &&
+              offsetof(rt_mesh, specular) == 68, "Mesh layout (scene.rs:23-37)");
+static_assert(sizeof(rt_vertex) == 32 && offsetof(rt_vertex, normal) == 16, "Vertex layout (scene.rs:79-86)");
+
+struct rt_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    uint32_t width = 0, height = 0;
+    float4* accum = nullptr;
+    uint32_t* primary_ids = nullptr;
+    unsigned long long* d_counters = nullptr;     // rays, samples, node visits, prim tests
+    rt::SceneBuffers scene;
+    bool has_scene = false, has_camera = false, has_params = false;
+    rt_params params{};
+    rt_camera_uniform camera{};
+    uint32_t tile_rank = 0, tile_world = 1, frame_rank = 0, frame_world = 1;
+    int64_t opt_traversal = 0, opt_seed_mode = 0, opt_primary_ids = 0, opt_detail = 0, opt_frames_per_launch = 64, opt_leaf_size = 4;
+    uint64_t dispatches = 0, launches = 0;
+    double kernel_ms = 0.0;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> pending, pool;
+    std::string err;
+};
+
+static thread_local std::string g_create_err;
+
+namespace {
+
+int fail(rt_ctx* c, int code, const std::string& msg) { if (c) c->err = msg; else g_create_err = msg; return code; }
+int cuda_fail(rt_ctx* c, cudaError_t e, const char* what)
+{
+    return fail(c, e == cudaErrorMemoryAllocation ? RT_ERR_OUT_OF_MEMORY : RT_ERR_CUDA,
+                std::string(what) + ": " + cudaGetErrorName(e) + " (" + cudaGetErrorString(e) + ")");
+}
+#define CU(c, x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return cuda_fail((c), e_, #x); } while (0)
+
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); else prev = -1; }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+int alloc_image(rt_ctx* c, uint32_t w, uint32_t h)
+{
+    if (c->accum) cudaFree(c->accum);
+    if (c->primary_ids) cudaFree(c->primary_ids);
+    c->accum = nullptr; c->primary_ids = nullptr;
+    size_t n = (size_t)w * h;
+    CU(c, cudaMalloc((void**)&c->accum, n * sizeof(float4)));
+    CU(c, cudaMalloc((void**)&c->primary_ids, n * sizeof(uint32_t)));
+    CU(c, cudaMemsetAsync(c->accum, 0, n * sizeof(float4), c->stream));          // wgpu zero-initialises textures
+    CU(c, cudaMemsetAsync(c->primary_ids, 0xFF, n * sizeof(uint32_t), c->stream));
+    c->width = w; c->height = h;
+    return RT_OK;
+}
+
+void drain_events(rt_ctx* c)
+{
+    for (auto& p : c->pending) {
+        float ms = 0.f;
+        if (cudaEventSynchronize(p.second) == cudaSuccess && cudaEventElapsedTime(&ms, p.first, p.second) == cudaSuccess) c->kernel_ms += ms;
+        c->pool.push_back(p);
+    }
+    c->pending.clear();
+}
+
+rt::CameraDev to_dev(const rt_camera_uniform& u)
+{
+    rt::CameraDev d;
+    d.origin = make_float3(u.origin[0], u.origin[1], u.origin[2]);
+    d.llc = make_float3(u.lower_left_corner[0], u.lower_left_corner[1], u.lower_left_corner[2]);
+    d.horizontal = make_float3(u.horizontal[0], u.horizontal[1], u.horizontal[2]);
+    d.vertical = make_float3(u.vertical[0], u.vertical[1], u.vertical[2]);
+    d.u = make_float3(u.u[0], u.u[1], u.u[2]);
+    d.v = make_float3(u.v[0], u.v[1], u.v[2]);
+    d.lens_radius = u.lens_radius;
+    return d;
+}
+
+// Launch `n_frames` fused dispatches starting at `first_frame` with stride c->frame_world.
+int launch(rt_ctx* c, int32_t first_frame, uint32_t n_frames, bool want_ids)
+{
+    rt::SceneDev sd{};
+    const rt::SceneBuffers& s = c->scene;
+    sd.g0 = s.g0; sd.g1 = s.g1; sd.g2 = s.g2; sd.c0 = s.c0; sd.c1 = s.c1; sd.c2 = s.c2;
+    sd.m0 = s.m0; sd.m1 = s.m1; sd.m2 = s.m2; sd.nodes = s.nodes;
+    sd.n_prims = s.n_prims; sd.n_spheres = s.n_spheres; sd.root = s.root;
+    sd.max_abs = s.max_abs; sd.pad_scale = 1.52587890625e-05f;   // 2^-16
+    rt::LaunchParams lp{};
+    lp.width = c->width; lp.height = c->height;
+    lp.bounces = c->params.number_of_bounces; lp.rpp = c->params.rays_per_pixel; lp.toggle = c->params.skybox;
+    lp.first_frame = first_frame; lp.n_frames = n_frames;
+    lp.tile_rank = c->tile_rank; lp.tile_world = c->tile_world; lp.frame_world = c->frame_world;
+    lp.tiles_x = (c->width + 7) / 8;
+    const uint32_t tiles = lp.tiles_x * ((c->height + 7) / 8);
+    lp.n_tiles_local = tiles > c->tile_rank ? (tiles - c->tile_rank + c->tile_world - 1) / c->tile_world : 0;
+    lp.seed_mode = (int32_t)c->opt_seed_mode;
+
+    std::pair<cudaEvent_t, cudaEvent_t> ev;
+    if (!c->pool.empty()) { ev = c->pool.back(); c->pool.pop_back(); }
+    else { CU(c, cudaEventCreate(&ev.first)); CU(c, cudaEventCreate(&ev.second)); }
+    CU(c, cudaEventRecord(ev.first, c->stream));
+    cudaError_t e = rt::launch_trace(sd, to_dev(c->camera), lp, c->accum, want_ids ? c->primary_ids : nullptr,
+                                     c->d_counters, c->opt_traversal == 1, c->opt_detail != 0, c->stream);
+    if (e != cudaSuccess) return cuda_fail(c, e, "trace kernel launch");
+    CU(c, cudaEventRecord(ev.second, c->stream));
+    c->pending.push_back(ev);
+    if (c->pending.size() > 4096) drain_events(c);
+    c->launches++;
+    c->dispatches += n_frames;
+    return RT_OK;
+}
+
+int check_ready(rt_ctx* c)
+{
+    if (!c) return RT_ERR_INVALID_ARGUMENT;
+    if (!c->has_scene) return fail(c, RT_ERR_NO_SCENE, "no scene uploaded (rt_upload_scene)");
+    if (!c->has_camera) return fail(c, RT_ERR_INVALID_ARGUMENT, "no camera set (rt_set_camera)");
+    if (!c->has_params) return fail(c, RT_ERR_INVALID_ARGUMENT, "no params set (rt_set_params)");
+    return RT_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+const char* rt_last_error(const rt_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_err.c_str(); }
+
+uint32_t rt_version(void) { return (0u << 16) | 1u; }
+
+int rt_create(rt_ctx** out, int device, uint32_t width, uint32_t height)
+{
+    if (!out) return fail(nullptr, RT_ERR_INVALID_ARGUMENT, "rt_create: out is NULL");
+    *out = nullptr;
+    if (width == 0 || height == 0) return fail(nullptr, RT_ERR_INVALID_ARGUMENT, "rt_create: zero-sized image");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess) return cuda_fail(nullptr, e, "cudaGetDeviceCount");
+    if (device < 0 || device >= ndev) return fail(nullptr, RT_ERR_INVALID_ARGUMENT, "rt_create: no such CUDA device");
+    rt_ctx* c = new (std::nothrow) rt_ctx();
+    if (!c) return fail(nullptr, RT_ERR_OUT_OF_MEMORY, "rt_create: host allocation failed");
+    c->device = device;
+    DeviceGuard g(device);
+    int rc = RT_OK;
+    do {
+        if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) { rc = cuda_fail(nullptr, e, "cudaStreamCreate"); break; }
+        if ((e = cudaMalloc((void**)&c->d_counters, 4 * sizeof(unsigned long long))) != cudaSuccess) { rc = cuda_fail(nullptr, e, "cudaMalloc counters"); break; }
+        if ((e = cudaMemsetAsync(c->d_counters, 0, 4 * sizeof(unsigned long long), c->stream)) != cudaSuccess) { rc = cuda_fail(nullptr, e, "memset counters"); break; }
+        rc = alloc_image(c, width, height);
+        if (rc != RT_OK) { g_create_err = c->err; break; }
+        if ((e = cudaStreamSynchronize(c->stream)) != cudaSuccess) { rc = cuda_fail(nullptr, e, "cudaStreamSynchronize"); break; }
+    } while (0);
+    if (rc != RT_OK) { rt_destroy(c); return rc; }
+    *out = c;
+    return RT_OK;
+}
+
+void rt_destroy(rt_ctx* c)
+{
+    if (!c) return;
+    DeviceGuard g(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    drain_events(c);
+    for (auto& p : c->pool) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
+    c->scene.release();
+    if (c->accum) cudaFree(c->accum);
+    if (c->primary_ids) cudaFree(c->primary_ids);
+    if (c->d_counters) cudaFree(c->d_counters);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+int rt_upload_scene(rt_ctx* c, const rt_sphere* spheres, uint32_t ns, const rt_vertex* vertices, uint32_t nv,
+                    const uint32_t* indices, uint32_t ni, const rt_mesh* meshes, uint32_t nm)
+{
+    if (!c) return RT_ERR_INVALID_ARGUMENT;
+    if ((ns && !spheres) || (nv && !vertices) || (ni && !indices) || (nm && !meshes))
+        return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_upload_scene: NULL array with non-zero count");
+    // The shader indexes unchecked (wgsl:161-170); here every address is validated up front.
+    uint64_t total_tris = 0;
+    for (uint32_t m = 0; m < nm; m++) {
+        const rt_mesh& me = meshes[m];
+        if (me.triangles == 0) continue;
+        uint64_t end = (uint64_t)me.first + 3ull * me.triangles;
+        if (end > ni) {
+            char b[160]; snprintf(b, sizeof b, "rt_upload_scene: mesh %u reads indices[%u..%llu) of %u", m, me.first, (unsigned long long)end, ni);
+            return fail(c, RT_ERR_BAD_INDEX, b);
+        }
+        for (uint64_t k = me.first; k < end; k++) {
+            if ((uint64_t)me.offset + indices[k] >= nv) {
+                char b[160]; snprintf(b, sizeof b, "rt_upload_scene: mesh %u index %llu -> vertex %llu of %u", m, (unsigned long long)k, (unsigned long long)me.offset + indices[k], nv);
+                return fail(c, RT_ERR_BAD_INDEX, b);
+            }
+        }
+        total_tris += me.triangles;
+    }
+    if ((uint64_t)ns + total_tris >= (1ull << 28))
+        return fail(c, RT_ERR_UNSUPPORTED, "rt_upload_scene: more than 2^28 primitives");
+    DeviceGuard g(c->device);
+    CU(c, cudaStreamSynchronize(c->stream));
+    uint32_t leaf = (uint32_t)(c->opt_leaf_size < 1 ? 1 : (c->opt_leaf_size > 8 ? 8 : c->opt_leaf_size));
+    cudaError_t e = rt::build_scene(c->scene, spheres, ns, vertices, nv, indices, ni, meshes, nm, leaf, c->stream);
+    if (e != cudaSuccess) { c->has_scene = false; return cuda_fail(c, e, "scene build"); }
+    if (c->scene.max_depth > 62) {
+        c->has_scene = false; c->scene.release();
+        return fail(c, RT_ERR_UNSUPPORTED, "rt_upload_scene: BVH deeper than the traversal stack");
+    }
+    c->has_scene = true;
+    return RT_OK;
+}
+
+int rt_set_camera(rt_ctx* c, const rt_camera_uniform* cam)
+{
+    if (!c || !cam) return c ? fail(c, RT_ERR_INVALID_ARGUMENT, "rt_set_camera: NULL") : RT_ERR_INVALID_ARGUMENT;
+    c->camera = *cam; c->has_camera = true;
+    return RT_OK;
+}
+
+int rt_set_params(rt_ctx* c, const rt_params* p)
+{
+    if (!c || !p) return c ? fail(c, RT_ERR_INVALID_ARGUMENT, "rt_set_params: NULL") : RT_ERR_INVALID_ARGUMENT;
+    if (p->width != c->width || p->height != c->height)
+        return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_set_params: width/height differ from the image (call rt_resize first)");
+    c->params = *p; c->has_params = true;
+    return RT_OK;
+}
+
+int rt_dispatch(rt_ctx* c)
+{
+    int rc = check_ready(c);
+    if (rc != RT_OK) return rc;
+    DeviceGuard g(c->device);
+    // a single dispatch is never frame-sharded: it is exactly the reference's compute pass
+    uint32_t fw = c->frame_world; c->frame_world = 1;
+    rc = launch(c, c->params.frames, 1, c->opt_primary_ids != 0);
+    c->frame_world = fw;
+    return rc;
+}
+
+int rt_render_frames(rt_ctx* c, int32_t first_frame, uint32_t n_frames)
+{
+    int rc = check_ready(c);
+    if (rc != RT_OK) return rc;
+    if (n_frames == 0) return RT_OK;
+    if (n_frames > 0x3fffffffu || (int64_t)first_frame + n_frames > 0x7fffffffll) return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_render_frames: frame range overflows i32");
+    DeviceGuard g(c->device);
+    int64_t f = first_frame, end = (int64_t)first_frame + n_frames;
+    const int64_t world = c->frame_world;
+    if (world > 1) {
+        if (first_frame < 0) return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_render_frames: frame sharding needs first_frame >= 0");
+        int64_t r = f % world;
+        f += (c->frame_rank + world - r) % world;       // first frame of this rank
+    }
+    bool want_ids = c->opt_primary_ids != 0;
+    const int64_t per = c->opt_frames_per_launch < 1 ? 1 : c->opt_frames_per_launch;
+    while (f < end) {
+        int64_t mine = (end - f + world - 1) / world;   // frames f, f+world, ... below end
+        uint32_t n = (uint32_t)(mine < per ? mine : per);
+        rc = launch(c, (int32_t)f, n, want_ids);
+        if (rc != RT_OK) return rc;
+        want_ids = false;
+        f += (int64_t)n * world;
+    }
+    return RT_OK;
+}
+
+int rt_sync(rt_ctx* c)
+{
+    if (!c) return RT_ERR_INVALID_ARGUMENT;
+    DeviceGuard g(c->device);
+    CU(c, cudaStreamSynchronize(c->stream));
+    return RT_OK;
+}
+
+int rt_resize(rt_ctx* c, uint32_t w, uint32_t h)
+{
+    if (!c) return RT_ERR_INVALID_ARGUMENT;
+    if (w == 0 || h == 0) return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_resize: zero-sized image");   // context.rs:127 ignores it
+    DeviceGuard g(c->device);
+    CU(c, cudaStreamSynchronize(c->stream));
+    int rc = alloc_image(c, w, h);
+    c->has_params = false;
+    return rc;
+}
+
+int rt_clear(rt_ctx* c)
+{
+    if (!c) return RT_ERR_INVALID_ARGUMENT;
+    DeviceGuard g(c->device);
+    CU(c, cudaMemsetAsync(c->accum, 0, (size_t)c->width * c->height * sizeof(float4), c->stream));
+    return RT_OK;
+}
+
+int rt_set_shard(rt_ctx* c, uint32_t tile_rank, uint32_t tile_world, uint32_t frame_rank, uint32_t frame_world)
+{
+    if (!c) return RT_ERR_INVALID_ARGUMENT;
+    if (tile_world == 0 || frame_world == 0 || tile_rank >= tile_world || frame_rank >= frame_world)
+        return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_set_shard: rank must be < world, world >= 1");
+    c->tile_rank = tile_rank; c->tile_world = tile_world; c->frame_rank = frame_rank; c->frame_world = frame_world;
+    return RT_OK;
+}
+
+int rt_set_option(rt_ctx* c, int option, int64_t value)
+{
+    if (!c) return RT_ERR_INVALID_ARGUMENT;
+    switch (option) {
+    case RT_OPT_TRAVERSAL: if (value != 0 && value != 1) break; c->opt_traversal = value; return RT_OK;
+    case RT_OPT_SEED_MODE: if (value != 0) break; c->opt_seed_mode = value; return RT_OK;
+    case RT_OPT_PRIMARY_IDS: c->opt_primary_ids = value != 0; return RT_OK;
+    case RT_OPT_DETAIL_COUNTERS: c->opt_detail = value != 0; return RT_OK;
+    case RT_OPT_FRAMES_PER_LAUNCH: if (value < 1 || value > (1 << 20)) break; c->opt_frames_per_launch = value; return RT_OK;
+    case RT_OPT_LEAF_SIZE: if (value < 1 || value > 8) break; c->opt_leaf_size = value; return RT_OK;
+    default: return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_set_option: unknown option");
+    }
+    return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_set_option: value out of range");
+}
+
+int rt_get_option(const rt_ctx* c, int option, int64_t* value)
+{
+    if (!c || !value) return RT_ERR_INVALID_ARGUMENT;
+    switch (option) {
+    case RT_OPT_TRAVERSAL: *value = c->opt_traversal; return RT_OK;
+    case RT_OPT_SEED_MODE: *value = c->opt_seed_mode; return RT_OK;
+    case RT_OPT_PRIMARY_IDS: *value = c->opt_primary_ids; return RT_OK;
+    case RT_OPT_DETAIL_COUNTERS: *value = c->opt_detail; return RT_OK;
+    case RT_OPT_FRAMES_PER_LAUNCH: *value = c->opt_frames_per_launch; return RT_OK;
+    case RT_OPT_LEAF_SIZE: *value = c->opt_leaf_size; return RT_OK;
+    default: return RT_ERR_INVALID_ARGUMENT;
+    }
+}
+
+int rt_read_accum(rt_ctx* c, float* rgba, size_t n_floats)
+{
+    if (!c || !rgba) return c ? fail(c, RT_ERR_INVALID_ARGUMENT, "rt_read_accum: NULL") : RT_ERR_INVALID_ARGUMENT;
+    if (n_floats != (size_t)c->width * c->height * 4) return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_read_accum: size must be W*H*4");
+    DeviceGuard g(c->device);
+    CU(c, cudaMemcpyAsync(rgba, c->accum, n_floats * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    return RT_OK;
+}
+
+int rt_write_accum(rt_ctx* c, const float* rgba, size_t n_floats)
+{
+    if (!c || !rgba) return c ? fail(c, RT_ERR_INVALID_ARGUMENT, "rt_write_accum: NULL") : RT_ERR_INVALID_ARGUMENT;
+    if (n_floats != (size_t)c->width * c->height * 4) return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_write_accum: size must be W*H*4");
+    DeviceGuard g(c->device);
+    CU(c, cudaMemcpyAsync(c->accum, rgba, n_floats * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    return RT_OK;
+}
+
+int rt_read_rgba8(rt_ctx* c, uint8_t* rgba, size_t n_bytes)
+{
+    if (!c || !rgba) return c ? fail(c, RT_ERR_INVALID_ARGUMENT, "rt_read_rgba8: NULL") : RT_ERR_INVALID_ARGUMENT;
+    size_t n = (size_t)c->width * c->height;
+    if (n_bytes != n * 4) return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_read_rgba8: size must be W*H*4");
+    DeviceGuard g(c->device);
+    uint8_t* d = nullptr;
+    CU(c, cudaMalloc((void**)&d, n * 4));
+    cudaError_t e = rt::launch_tonemap(c->accum, d, n, c->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(rgba, d, n * 4, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFree(d);
+    if (e != cudaSuccess) return cuda_fail(c, e, "tonemap");
+    return RT_OK;
+}
+
+int rt_read_primary_ids(rt_ctx* c, uint32_t* ids, size_t n)
+{
+    if (!c || !ids) return c ? fail(c, RT_ERR_INVALID_ARGUMENT, "rt_read_primary_ids: NULL") : RT_ERR_INVALID_ARGUMENT;
+    if (n != (size_t)c->width * c->height) return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_read_primary_ids: size must be W*H");
+    DeviceGuard g(c->device);
+    CU(c, cudaMemcpyAsync(ids, c->primary_ids, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    return RT_OK;
+}
+
+int rt_get_counters(rt_ctx* c, rt_counters* out)
+{
+    if (!c || !out) return RT_ERR_INVALID_ARGUMENT;
+    DeviceGuard g(c->device);
+    unsigned long long h[4];
+    CU(c, cudaMemcpyAsync(h, c->d_counters, sizeof h, cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    drain_events(c);
+    out->rays = h[0]; out->samples = h[1]; out->node_visits = h[2]; out->prim_tests = h[3];
+    out->dispatches = c->dispatches; out->kernel_ms = c->kernel_ms; out->launches = c->launches;
+    return RT_OK;
+}
+
+int rt_reset_counters(rt_ctx* c)
+{
+    if (!c) return RT_ERR_INVALID_ARGUMENT;
+    DeviceGuard g(c->device);
+    CU(c, cudaStreamSynchronize(c->stream));
+    drain_events(c);
+    CU(c, cudaMemsetAsync(c->d_counters, 0, 4 * sizeof(unsigned long long), c->stream));
+    c->dispatches = c->launches = 0; c->kernel_ms = 0.0;
+    return RT_OK;
+}
+
+void* rt_accum_device_ptr(rt_ctx* c) { return c ? (void*)c->accum : nullptr; }
+void* rt_cuda_stream(rt_ctx* c) { return c ? (void*)c->stream : nullptr; }
+int rt_device(const rt_ctx* c) { return c ? c->device : -1; }
+
+int rt_bvh_stats(rt_ctx* c, uint32_t* n_prims, uint32_t* n_nodes, uint32_t* max_depth)
+{
+    if (!c) return RT_ERR_INVALID_ARGUMENT;
+    if (!c->has_scene) return fail(c, RT_ERR_NO_SCENE, "no scene uploaded");
+    if (n_prims) *n_prims = c->scene.n_prims;
+    if (n_nodes) *n_nodes = c->scene.n_nodes;
+    if (max_depth) *max_depth = c->scene.max_depth;
+    return RT_OK;
+}
+
+} // extern "C"

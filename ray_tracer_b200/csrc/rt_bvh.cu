@@ -1,0 +1,337 @@
+// rt_bvh.cu — scene repack (AoS records -> SoA 128-bit slots) and GPU LBVH build.
+//
+// No reference counterpart: upstream scans every sphere and triangle per segment
+// (shaders/ray_tracer.wgsl:149-185).  The build is result-invisible by construction: the
+// values the exact tests consume (A = a.pos + mesh.pos, e1 = B - A, e2 = C - A, r*r) are
+// produced here with the same single f32 operations the reference performs per test
+// (wgsl:172-174, 127-128, 111), and the hierarchy only decides which tests are skipped.
+//
+// Pipeline (all on the GPU): primitive setup + bounds -> scene bounds (atomic min/max) ->
+// 63-bit Morton keys of box centres -> radix sort (CUB) -> Karras 2012 radix tree ->
+// bottom-up refit with arrival flags -> node emission with both child boxes in the parent
+// and subtrees of <= leaf_size primitives collapsed into one leaf.
+#include <cub/cub.cuh>
+#include <vector>
+#include "rt_kernels.h"
+
+namespace rt {
+
+namespace {
+
+struct RawScene {
+    const rt_sphere* spheres; const rt_vertex* vertices; const uint32_t* indices; const rt_mesh* meshes;
+    const uint32_t* tri_start;      // [nm+1] prefix sum of mesh.triangles
+    uint32_t ns, nm, nt;
+};
+
+__device__ __forceinline__ int fenc(float f) { int i = __float_as_int(f); return i >= 0 ? i : i ^ 0x7fffffff; }
+__device__ __forceinline__ float fdec(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7fffffff); }
+
+// one thread per primitive id: hot/cold records in id order, exact bounds, scene bounds
+__global__ void setup_prims(RawScene rs, float4* h0, float4* h1, float4* h2, float4* c0, float4* c1, float4* c2,
+                            float4* bmin, float4* bmax, int* scene_bounds /*[6] encoded*/)
+{
+    uint32_t id = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t n = rs.ns + rs.nt;
+    float3 lo = f3(INFINITY, INFINITY, INFINITY), hi = f3(-INFINITY, -INFINITY, -INFINITY);
+    if (id < n) {
+        if (id < rs.ns) {
+            const rt_sphere& s = rs.spheres[id];
+            float r = s.radius;
+            float3 c = f3(s.position[0], s.position[1], s.position[2]);
+            h0[id] = make_float4(c.x, c.y, c.z, __uint_as_float(id));
+            h1[id] = make_float4(r, r * r, 0.f, 0.f);
+            h2[id] = make_float4(0.f, 0.f, 0.f, 0.f);
+            c0[id] = make_float4(c.x, c.y, c.z, __uint_as_float(id));
+            c1[id] = c2[id] = make_float4(0.f, 0.f, 0.f, 0.f);
+            float ar = fabsf(r);
+            lo = f3(c.x - ar, c.y - ar, c.z - ar); hi = f3(c.x + ar, c.y + ar, c.z + ar);
+        } else {
+            uint32_t t = id - rs.ns;
+            uint32_t a = 0, b = rs.nm;               // mesh m with tri_start[m] <= t < tri_start[m+1]
+            while (b - a > 1) { uint32_t mid = (a + b) >> 1; if (rs.tri_start[mid] <= t) a = mid; else b = mid; }
+            const rt_mesh& m = rs.meshes[a];
+            uint32_t i = t - rs.tri_start[a];
+            const rt_vertex& va = rs.vertices[m.offset + rs.indices[m.first + i * 3u]];
+            const rt_vertex& vb = rs.vertices[m.offset + rs.indices[m.first + i * 3u + 1u]];
+            const rt_vertex& vc = rs.vertices[m.offset + rs.indices[m.first + i * 3u + 2u]];
+            float3 mp = f3(m.pos[0], m.pos[1], m.pos[2]);
+            float3 A = f3(va.pos[0], va.pos[1], va.pos[2]) + mp;       // wgsl:172-174
+            float3 B = f3(vb.pos[0], vb.pos[1], vb.pos[2]) + mp;
+            float3 C = f3(vc.pos[0], vc.pos[1], vc.pos[2]) + mp;
+            float3 e1 = B - A, e2 = C - A;                              // wgsl:127-128
+            h0[id] = make_float4(A.x, A.y, A.z, __uint_as_float(id));
+            h1[id] = make_float4(e1.x, e1.y, e1.z, e2.x);
+            h2[id] = make_float4(e2.y, e2.z, 0.f, 0.f);
+            c0[id] = make_float4(va.normal[0], va.normal[1], va.normal[2], __uint_as_float(rs.ns + a));
+            c1[id] = make_float4(vb.normal[0], vb.normal[1], vb.normal[2], 0.f);
+            c2[id] = make_float4(vc.normal[0], vc.normal[1], vc.normal[2], 0.f);
+            lo = f3(fminf(A.x, fminf(B.x, C.x)), fminf(A.y, fminf(B.y, C.y)), fminf(A.z, fminf(B.z, C.z)));
+            hi = f3(fmaxf(A.x, fmaxf(B.x, C.x)), fmaxf(A.y, fmaxf(B.y, C.y)), fmaxf(A.z, fmaxf(B.z, C.z)));
+        }
+        bmin[id] = make_float4(lo.x, lo.y, lo.z, 0.f);
+        bmax[id] = make_float4(hi.x, hi.y, hi.z, 0.f);
+    }
+    // warp-reduce then one atomic per warp; NaN bounds are ignored by fminf/fmaxf
+    for (int o = 16; o > 0; o >>= 1) {
+        lo.x = fminf(lo.x, __shfl_xor_sync(0xffffffffu, lo.x, o)); lo.y = fminf(lo.y, __shfl_xor_sync(0xffffffffu, lo.y, o));
+        lo.z = fminf(lo.z, __shfl_xor_sync(0xffffffffu, lo.z, o)); hi.x = fmaxf(hi.x, __shfl_xor_sync(0xffffffffu, hi.x, o));
+        hi.y = fmaxf(hi.y, __shfl_xor_sync(0xffffffffu, hi.y, o)); hi.z = fmaxf(hi.z, __shfl_xor_sync(0xffffffffu, hi.z, o));
+    }
+    if ((threadIdx.x & 31) == 0 && lo.x <= hi.x) {
+        atomicMin(scene_bounds + 0, fenc(lo.x)); atomicMin(scene_bounds + 1, fenc(lo.y)); atomicMin(scene_bounds + 2, fenc(lo.z));
+        atomicMax(scene_bounds + 3, fenc(hi.x)); atomicMax(scene_bounds + 4, fenc(hi.y)); atomicMax(scene_bounds + 5, fenc(hi.z));
+    }
+}
+
+__global__ void setup_materials(RawScene rs, float4* m0, float4* m1, float4* m2)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= rs.ns + rs.nm) return;
+    const float* col; const float* emi; float str, smooth;
+    if (i < rs.ns) { const rt_sphere& s = rs.spheres[i]; col = s.color; emi = s.emission_color; str = s.emission_strength; smooth = s.smoothness; }
+    else { const rt_mesh& m = rs.meshes[i - rs.ns]; col = m.color; emi = m.emission_color; str = m.emission_strength; smooth = m.specular; }
+    m0[i] = make_float4(col[0], col[1], col[2], col[3]);
+    m1[i] = make_float4(emi[0] * str, emi[1] * str, emi[2] * str, emi[3] * str);   // wgsl:271
+    m2[i] = make_float4(smooth, 0.f, 0.f, 0.f);
+}
+
+__device__ __forceinline__ uint64_t spread21(uint32_t v)
+{
+    uint64_t x = v & 0x1fffffu;
+    x = (x | x << 32) & 0x1f00000000ffffull;
+    x = (x | x << 16) & 0x1f0000ff0000ffull;
+    x = (x | x << 8) & 0x100f00f00f00f00full;
+    x = (x | x << 4) & 0x10c30c30c30c30c3ull;
+    x = (x | x << 2) & 0x1249249249249249ull;
+    return x;
+}
+
+__global__ void morton_keys(uint32_t n, const float4* bmin, const float4* bmax, const int* scene_bounds,
+                            uint64_t* keys, uint32_t* ids)
+{
+    uint32_t id = blockIdx.x * blockDim.x + threadIdx.x;
+    if (id >= n) return;
+    float3 slo = f3(fdec(scene_bounds[0]), fdec(scene_bounds[1]), fdec(scene_bounds[2]));
+    float3 shi = f3(fdec(scene_bounds[3]), fdec(scene_bounds[4]), fdec(scene_bounds[5]));
+    float4 lo = bmin[id], hi = bmax[id];
+    float cx = 0.5f * lo.x + 0.5f * hi.x, cy = 0.5f * lo.y + 0.5f * hi.y, cz = 0.5f * lo.z + 0.5f * hi.z;
+    float ex = fmaxf(shi.x - slo.x, 1e-30f), ey = fmaxf(shi.y - slo.y, 1e-30f), ez = fmaxf(shi.z - slo.z, 1e-30f);
+    float e = fmaxf(ex, fmaxf(ey, ez));              // cubic cells: same resolution on every axis
+    float qx = fminf(fmaxf((cx - slo.x) / e, 0.f), 1.f), qy = fminf(fmaxf((cy - slo.y) / e, 0.f), 1.f), qz = fminf(fmaxf((cz - slo.z) / e, 0.f), 1.f);
+    if (!(qx == qx)) qx = 0.f; if (!(qy == qy)) qy = 0.f; if (!(qz == qz)) qz = 0.f;
+    uint32_t ix = (uint32_t)fminf(qx * 2097152.0f, 2097151.0f), iy = (uint32_t)fminf(qy * 2097152.0f, 2097151.0f), iz = (uint32_t)fminf(qz * 2097152.0f, 2097151.0f);
+    keys[id] = (spread21(ix) << 2) | (spread21(iy) << 1) | spread21(iz);
+    ids[id] = id;
+}
+
+__global__ void gather_slots(uint32_t n, const uint32_t* sorted_ids, const float4* h0, const float4* h1, const float4* h2,
+                             const float4* bmin, const float4* bmax, float4* g0, float4* g1, float4* g2, float4* lmin, float4* lmax)
+{
+    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    uint32_t id = sorted_ids[k];
+    g0[k] = h0[id]; g1[k] = h1[id]; g2[k] = h2[id];
+    lmin[k] = bmin[id]; lmax[k] = bmax[id];
+}
+
+__device__ __forceinline__ int delta(const uint64_t* keys, int n, int i, int j)
+{
+    if (j < 0 || j >= n) return -1;
+    uint64_t a = keys[i], b = keys[j];
+    if (a == b) return 64 + __clz((uint32_t)i ^ (uint32_t)j);
+    return __clzll((long long)(a ^ b));
+}
+
+// Karras 2012: inner node i covers sorted range [first,last]; children encoded as
+// index (inner) or ~slot (leaf); parents recorded for the refit.
+__global__ void build_radix_tree(int n, const uint64_t* keys, int2* children, int2* ranges, int* parent_inner, int* parent_leaf)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    int d = (delta(keys, n, i, i + 1) - delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+    int dmin = delta(keys, n, i, i - d);
+    int lmax = 2;
+    while (delta(keys, n, i, i + lmax * d) > dmin) lmax <<= 1;
+    int l = 0;
+    for (int t = lmax >> 1; t >= 1; t >>= 1)
+        if (delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+    int j = i + l * d;
+    int dnode = delta(keys, n, i, j);
+    int s = 0;
+    for (int t = (l + 1) >> 1;; t = (t + 1) >> 1) {
+        if (delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+        if (t == 1) break;
+    }
+    int gamma = i + s * d + min(d, 0);
+    int first = min(i, j), last = max(i, j);
+    int left = (first == gamma) ? ~gamma : gamma;
+    int right = (last == gamma + 1) ? ~(gamma + 1) : gamma + 1;
+    children[i] = make_int2(left, right);
+    ranges[i] = make_int2(first, last);
+    if (left >= 0) parent_inner[left] = i; else parent_leaf[~left] = i;
+    if (right >= 0) parent_inner[right] = i; else parent_leaf[~right] = i;
+    if (i == 0) parent_inner[0] = -1;
+}
+
+// bottom-up boxes of inner nodes; the second thread to arrive at a node owns it
+__global__ void refit(int n, const int2* children, const int* parent_inner, const int* parent_leaf,
+                      const float4* lmin, const float4* lmax, float4* imin, float4* imax, int* flags, int* max_depth)
+{
+    int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    int node = parent_leaf[k];
+    int depth = 1;
+    while (node >= 0) {
+        __threadfence();
+        if (atomicAdd(flags + node, 1) == 0) { depth = 0; break; }
+        int2 ch = children[node];
+        float4 alo = ch.x >= 0 ? ((volatile float4*)imin)[ch.x] : lmin[~ch.x], ahi = ch.x >= 0 ? ((volatile float4*)imax)[ch.x] : lmax[~ch.x];
+        float4 blo = ch.y >= 0 ? ((volatile float4*)imin)[ch.y] : lmin[~ch.y], bhi = ch.y >= 0 ? ((volatile float4*)imax)[ch.y] : lmax[~ch.y];
+        imin[node] = make_float4(fminf(alo.x, blo.x), fminf(alo.y, blo.y), fminf(alo.z, blo.z), 0.f);
+        imax[node] = make_float4(fmaxf(ahi.x, bhi.x), fmaxf(ahi.y, bhi.y), fmaxf(ahi.z, bhi.z), 0.f);
+        node = parent_inner[node];
+        depth++;
+    }
+    (void)depth;
+    // depth of this leaf (independent climb; cheap, log n)
+    int dd = 0;
+    for (int p = parent_leaf[k]; p >= 0; p = parent_inner[p]) dd++;
+    atomicMax(max_depth, dd);
+}
+
+__device__ __forceinline__ int encode_child(int c, const int2* ranges, int leaf_size)
+{
+    if (c < 0) return ~(((~c) << 3) | 0);
+    int2 r = ranges[c];
+    int cnt = r.y - r.x + 1;
+    if (cnt <= leaf_size) return ~((r.x << 3) | (cnt - 1));
+    return c;
+}
+
+__global__ void emit_nodes(int n_inner, const int2* children, const int2* ranges, const float4* lmin, const float4* lmax,
+                           const float4* imin, const float4* imax, int leaf_size, float4* nodes)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_inner) return;
+    int2 ch = children[i];
+    float4 alo = ch.x >= 0 ? imin[ch.x] : lmin[~ch.x], ahi = ch.x >= 0 ? imax[ch.x] : lmax[~ch.x];
+    float4 blo = ch.y >= 0 ? imin[ch.y] : lmin[~ch.y], bhi = ch.y >= 0 ? imax[ch.y] : lmax[~ch.y];
+    int el = encode_child(ch.x, ranges, leaf_size), er = encode_child(ch.y, ranges, leaf_size);
+    nodes[4 * (size_t)i + 0] = make_float4(alo.x, alo.y, alo.z, ahi.x);
+    nodes[4 * (size_t)i + 1] = make_float4(ahi.y, ahi.z, blo.x, blo.y);
+    nodes[4 * (size_t)i + 2] = make_float4(blo.z, bhi.x, bhi.y, bhi.z);
+    nodes[4 * (size_t)i + 3] = make_float4(__int_as_float(el), __int_as_float(er), 0.f, 0.f);
+}
+
+__global__ void emit_single(const float4* lmin, const float4* lmax, float4* nodes)
+{
+    float4 lo = lmin[0], hi = lmax[0];
+    const float big = 3.0e38f;
+    nodes[0] = make_float4(lo.x, lo.y, lo.z, hi.x);
+    nodes[1] = make_float4(hi.y, hi.z, big, big);
+    nodes[2] = make_float4(big, -big, -big, -big);
+    nodes[3] = make_float4(__int_as_float(~0), __int_as_float(~0), 0.f, 0.f);
+}
+
+template <typename T>
+cudaError_t dalloc(T** p, size_t n) { return cudaMalloc((void**)p, (n ? n : 1) * sizeof(T)); }
+
+} // namespace
+
+void SceneBuffers::release()
+{
+    float4** ps[] = {&g0, &g1, &g2, &c0, &c1, &c2, &m0, &m1, &m2, &nodes};
+    for (auto p : ps) { if (*p) cudaFree(*p); *p = nullptr; }
+    n_prims = n_spheres = n_tris = n_mats = n_nodes = max_depth = 0; root = -1; max_abs = 0.f;
+}
+
+#define RT_TRY(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { err = e_; goto done; } } while (0)
+
+cudaError_t build_scene(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns, const rt_vertex* vertices,
+                        uint32_t nv, const uint32_t* indices, uint32_t ni, const rt_mesh* meshes, uint32_t nm,
+                        uint32_t leaf_size, cudaStream_t stream)
+{
+    out.release();
+    cudaError_t err = cudaSuccess;
+    std::vector<uint32_t> tri_start(nm + 1, 0);
+    for (uint32_t m = 0; m < nm; m++) tri_start[m + 1] = tri_start[m] + meshes[m].triangles;
+    const uint32_t nt = tri_start[nm], n = ns + nt, nmat = ns + nm;
+    const int T = 256;
+
+    rt_sphere* d_sph = nullptr; rt_vertex* d_vtx = nullptr; uint32_t* d_idx = nullptr; rt_mesh* d_mesh = nullptr;
+    uint32_t* d_tstart = nullptr;
+    float4 *h0 = nullptr, *h1 = nullptr, *h2 = nullptr, *bmin = nullptr, *bmax = nullptr, *lmin = nullptr, *lmax = nullptr, *imin = nullptr, *imax = nullptr;
+    int* d_bounds = nullptr; uint64_t *keys = nullptr, *keys2 = nullptr; uint32_t *ids = nullptr, *ids2 = nullptr;
+    int2 *children = nullptr, *ranges = nullptr; int *pin = nullptr, *plf = nullptr, *flags = nullptr, *d_depth = nullptr;
+    void* cub_tmp = nullptr; size_t cub_bytes = 0;
+    int hb[6]; int h_init[6] = {0x7fffffff, 0x7fffffff, 0x7fffffff, (int)0x80000000, (int)0x80000000, (int)0x80000000};
+    int h_depth = 0;
+
+    RT_TRY(dalloc(&d_sph, ns)); RT_TRY(dalloc(&d_vtx, nv)); RT_TRY(dalloc(&d_idx, ni)); RT_TRY(dalloc(&d_mesh, nm));
+    RT_TRY(dalloc(&d_tstart, nm + 1));
+    if (ns) RT_TRY(cudaMemcpyAsync(d_sph, spheres, ns * sizeof(rt_sphere), cudaMemcpyHostToDevice, stream));
+    if (nv) RT_TRY(cudaMemcpyAsync(d_vtx, vertices, nv * sizeof(rt_vertex), cudaMemcpyHostToDevice, stream));
+    if (ni) RT_TRY(cudaMemcpyAsync(d_idx, indices, ni * sizeof(uint32_t), cudaMemcpyHostToDevice, stream));
+    if (nm) RT_TRY(cudaMemcpyAsync(d_mesh, meshes, nm * sizeof(rt_mesh), cudaMemcpyHostToDevice, stream));
+    RT_TRY(cudaMemcpyAsync(d_tstart, tri_start.data(), (nm + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice, stream));
+
+    RT_TRY(dalloc(&out.g0, n)); RT_TRY(dalloc(&out.g1, n)); RT_TRY(dalloc(&out.g2, n));
+    RT_TRY(dalloc(&out.c0, n)); RT_TRY(dalloc(&out.c1, n)); RT_TRY(dalloc(&out.c2, n));
+    RT_TRY(dalloc(&out.m0, nmat)); RT_TRY(dalloc(&out.m1, nmat)); RT_TRY(dalloc(&out.m2, nmat));
+    out.n_prims = n; out.n_spheres = ns; out.n_tris = nt; out.n_mats = nmat;
+    {
+        RawScene rs{d_sph, d_vtx, d_idx, d_mesh, d_tstart, ns, nm, nt};
+        if (nmat) setup_materials<<<(nmat + T - 1) / T, T, 0, stream>>>(rs, out.m0, out.m1, out.m2);
+        if (n == 0) { RT_TRY(cudaStreamSynchronize(stream)); goto done; }
+
+        RT_TRY(dalloc(&h0, n)); RT_TRY(dalloc(&h1, n)); RT_TRY(dalloc(&h2, n)); RT_TRY(dalloc(&bmin, n)); RT_TRY(dalloc(&bmax, n));
+        RT_TRY(dalloc(&lmin, n)); RT_TRY(dalloc(&lmax, n)); RT_TRY(dalloc(&imin, n)); RT_TRY(dalloc(&imax, n));
+        RT_TRY(dalloc(&d_bounds, 6)); RT_TRY(dalloc(&keys, n)); RT_TRY(dalloc(&keys2, n)); RT_TRY(dalloc(&ids, n)); RT_TRY(dalloc(&ids2, n));
+        RT_TRY(dalloc(&children, n)); RT_TRY(dalloc(&ranges, n)); RT_TRY(dalloc(&pin, n)); RT_TRY(dalloc(&plf, n)); RT_TRY(dalloc(&flags, n));
+        RT_TRY(dalloc(&d_depth, 1));
+        RT_TRY(cudaMemcpyAsync(d_bounds, h_init, sizeof(h_init), cudaMemcpyHostToDevice, stream));
+        RT_TRY(cudaMemsetAsync(flags, 0, n * sizeof(int), stream));
+        RT_TRY(cudaMemsetAsync(d_depth, 0, sizeof(int), stream));
+
+        const int nb = (n + T - 1) / T;
+        setup_prims<<<nb, T, 0, stream>>>(rs, h0, h1, h2, out.c0, out.c1, out.c2, bmin, bmax, d_bounds);
+        morton_keys<<<nb, T, 0, stream>>>(n, bmin, bmax, d_bounds, keys, ids);
+        RT_TRY(cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, keys, keys2, ids, ids2, (int)n, 0, 63, stream));
+        RT_TRY(cudaMalloc(&cub_tmp, cub_bytes ? cub_bytes : 1));
+        RT_TRY(cub::DeviceRadixSort::SortPairs(cub_tmp, cub_bytes, keys, keys2, ids, ids2, (int)n, 0, 63, stream));
+        gather_slots<<<nb, T, 0, stream>>>(n, ids2, h0, h1, h2, bmin, bmax, out.g0, out.g1, out.g2, lmin, lmax);
+        if (n == 1) {
+            RT_TRY(dalloc(&out.nodes, 4));
+            emit_single<<<1, 1, 0, stream>>>(lmin, lmax, out.nodes);
+            out.n_nodes = 1; out.root = 0; h_depth = 1;
+        } else {
+            RT_TRY(dalloc(&out.nodes, 4 * (size_t)(n - 1)));
+            build_radix_tree<<<nb, T, 0, stream>>>((int)n, keys2, children, ranges, pin, plf);
+            refit<<<nb, T, 0, stream>>>((int)n, children, pin, plf, lmin, lmax, imin, imax, flags, d_depth);
+            emit_nodes<<<nb, T, 0, stream>>>((int)n - 1, children, ranges, lmin, lmax, imin, imax, (int)leaf_size, out.nodes);
+            out.n_nodes = n - 1; out.root = 0;
+            RT_TRY(cudaMemcpyAsync(&h_depth, d_depth, sizeof(int), cudaMemcpyDeviceToHost, stream));
+        }
+        RT_TRY(cudaMemcpyAsync(hb, d_bounds, sizeof(hb), cudaMemcpyDeviceToHost, stream));
+        RT_TRY(cudaStreamSynchronize(stream));
+        RT_TRY(cudaGetLastError());
+        out.max_depth = (uint32_t)h_depth;
+        float m = 0.f;
+        for (int k = 0; k < 6; k++) {
+            int e = hb[k]; int b = e >= 0 ? e : e ^ 0x7fffffff; float f; memcpy(&f, &b, 4);
+            if (f == f && fabsf(f) <= 3.0e38f && fabsf(f) > m) m = fabsf(f);
+        }
+        out.max_abs = m;
+    }
+done:
+    {
+        void* tmp[] = {d_sph, d_vtx, d_idx, d_mesh, d_tstart, h0, h1, h2, bmin, bmax, lmin, lmax, imin, imax, d_bounds,
+                       keys, keys2, ids, ids2, children, ranges, pin, plf, flags, d_depth, cub_tmp};
+        for (void* p : tmp) if (p) cudaFree(p);
+    }
+    if (err != cudaSuccess) out.release();
+    return err;
+}
+
+} // namespace rt

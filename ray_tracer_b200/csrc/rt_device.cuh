@@ -1,0 +1,98 @@
+// rt_device.cuh — device-side scene layout and small vector helpers.
+//
+// HBM layout (all arrays 16-byte aligned, read through the read-only path as 128-bit loads):
+//
+//  hot, indexed by BVH slot k (primitives in Morton order):
+//    g0[k] = (A.x, A.y, A.z, id)        triangle: A = a.pos + mesh.pos   | sphere: centre
+//    g1[k] = (e1.x, e1.y, e1.z, e2.x)   e1 = B - A                        | (radius, radius^2, 0, 0)
+//    g2[k] = (e2.y, e2.z, 0, 0)         e2 = C - A
+//    `id` = global primitive order index of the reference's brute-force loop
+//    (wgsl:149-185): spheres 0..S-1 in array order, then triangles mesh by mesh; it is
+//    the tie-break key and tells the two primitive kinds apart (id < S).
+//  cold, indexed by id, fetched once per path segment for the winning hit only:
+//    c0[id] = (nA.xyz, material index)  | sphere: (centre, material index)
+//    c1[id] = (nB.xyz, 0)  c2[id] = (nC.xyz, 0)
+//  materials, indexed by material index (sphere i -> i, mesh m -> S + m):
+//    m0 = color, m1 = emission_color * emission_strength, m2.x = smoothness
+//  BVH nodes, 64 B each (both children's boxes live in the parent, one fetch = two tests):
+//    n[4*i+0] = (L.min.xyz, L.max.x)  n[4*i+1] = (L.max.yz, R.min.xy)
+//    n[4*i+2] = (R.min.z, R.max.xyz)  n[4*i+3] = (left, right, 0, 0) as int bits
+//    child >= 0: inner node index; child < 0: leaf, ~child = (first_slot << 3) | (count - 1)
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "rt_math.cuh"
+
+namespace rt {
+
+struct SceneDev {
+    const float4* g0; const float4* g1; const float4* g2;
+    const float4* c0; const float4* c1; const float4* c2;
+    const float4* m0; const float4* m1; const float4* m2;
+    const float4* nodes;
+    uint32_t n_prims;      // slots
+    uint32_t n_spheres;    // ids below this are spheres
+    int32_t root;          // root node index, or -1 when the scene is empty
+    float max_abs;         // largest |coordinate| of the scene bounds
+    float pad_scale;       // box padding = pad_scale * max(max_abs, |ray origin|)
+};
+
+struct CameraDev {         // the fields of CameraUniform the shader reads (wgsl:69-80)
+    float3 origin, llc, horizontal, vertical, u, v;
+    float lens_radius;
+};
+
+struct LaunchParams {
+    uint32_t width, height;
+    int32_t bounces, rpp, toggle;
+    int32_t first_frame;       // params.frames of the first fused dispatch
+    uint32_t n_frames;         // fused dispatches (frame stride = frame_world)
+    uint32_t tile_rank, tile_world;
+    uint32_t frame_world;      // stride between frames rendered by this rank
+    uint32_t tiles_x, n_tiles_local; // 8x8 tiles per row; tiles owned by this rank
+    int32_t seed_mode;
+};
+
+// ---- vector helpers (the fused forms are the arithmetic contract's) -----
+__device__ __forceinline__ float3 f3(float x, float y, float z) { return make_float3(x, y, z); }
+__device__ __forceinline__ float3 operator+(float3 a, float3 b) { return f3(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ float3 operator-(float3 a, float3 b) { return f3(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ float3 operator-(float3 a) { return f3(-a.x, -a.y, -a.z); }
+__device__ __forceinline__ float3 operator*(float3 a, float s) { return f3(a.x * s, a.y * s, a.z * s); }
+__device__ __forceinline__ float4 operator*(float4 a, float4 b) { return make_float4(a.x * b.x, a.y * b.y, a.z * b.z, a.w * b.w); }
+__device__ __forceinline__ float4 operator+(float4 a, float4 b) { return make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w); }
+
+__device__ __forceinline__ float dot3(float3 a, float3 b) { return __fmaf_rn(a.z, b.z, __fmaf_rn(a.y, b.y, a.x * b.x)); }
+__device__ __forceinline__ float3 cross3(float3 a, float3 b)
+{
+    return f3(__fmaf_rn(a.y, b.z, -(a.z * b.y)), __fmaf_rn(a.z, b.x, -(a.x * b.z)), __fmaf_rn(a.x, b.y, -(a.y * b.x)));
+}
+__device__ __forceinline__ float3 fma3(float3 a, float s, float3 c)
+{
+    return f3(__fmaf_rn(a.x, s, c.x), __fmaf_rn(a.y, s, c.y), __fmaf_rn(a.z, s, c.z));
+}
+__device__ __forceinline__ float length3(float3 a) { return sqrtf(dot3(a, a)); }
+__device__ __forceinline__ float3 normalize3(float3 a) { float inv = 1.0f / sqrtf(dot3(a, a)); return a * inv; }
+__device__ __forceinline__ float3 reflect3(float3 i, float3 n) { float t = 2.0f * dot3(n, i); return fma3(n, -t, i); }
+__device__ __forceinline__ float mix1(float a, float b, float t) { return __fmaf_rn(b, t, a * (1.0f - t)); }
+__device__ __forceinline__ float sign1(float x) { return (x > 0.0f) ? 1.0f : ((x < 0.0f) ? -1.0f : 0.0f); }
+__device__ __forceinline__ float smoothstep1(float e0, float e1, float x)
+{
+    float t = fminf(fmaxf((x - e0) / (e1 - e0), 0.0f), 1.0f);
+    return (t * t) * (3.0f - 2.0f * t);
+}
+__device__ __forceinline__ float3 xyz(float4 v) { return f3(v.x, v.y, v.z); }
+
+// ---- RNG: PCG-RXS-M-XS-32 hash stream (wgsl:205-210), rand in [0,1] (wgsl:187-189) -----
+__device__ __forceinline__ uint32_t next_random_number(uint32_t& s)
+{
+    s = s * 747796405u + 2891336453u;
+    uint32_t r = ((s >> ((s >> 28u) + 4u)) ^ s) * 277803737u;
+    return (r >> 22u) ^ r;
+}
+__device__ __forceinline__ float rand01(uint32_t& s)
+{
+    return __uint2float_rn(next_random_number(s)) * 2.3283064365386963e-10f; // exact scaling by 2^-32
+}
+
+} // namespace rt

@@ -1,0 +1,36 @@
+// rt_kernels.h — host-callable launchers of the CUDA kernels (internal to librt_b200.so).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "rt_device.cuh"
+#include "../../include/rt_b200.h"
+
+#define RT_BLOCK_THREADS 128
+
+namespace rt {
+
+cudaError_t launch_trace(const SceneDev& sc, const CameraDev& cam, const LaunchParams& lp, float4* accum,
+                         uint32_t* primary_ids, unsigned long long* counters, bool brute, bool detail,
+                         cudaStream_t stream);
+
+// Device-resident scene: SoA primitive arrays + LBVH, built on the GPU from the AoS records.
+struct SceneBuffers {
+    float4 *g0 = nullptr, *g1 = nullptr, *g2 = nullptr;
+    float4 *c0 = nullptr, *c1 = nullptr, *c2 = nullptr;
+    float4 *m0 = nullptr, *m1 = nullptr, *m2 = nullptr;
+    float4* nodes = nullptr;
+    uint32_t n_prims = 0, n_spheres = 0, n_tris = 0, n_mats = 0, n_nodes = 0, max_depth = 0;
+    int32_t root = -1;
+    float max_abs = 0.0f;
+    void release();
+};
+
+// Repack + LBVH build. All pointers are host pointers to the caller's records (already
+// validated). Synchronous with respect to `stream` on return.
+cudaError_t build_scene(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns, const rt_vertex* vertices,
+                        uint32_t nv, const uint32_t* indices, uint32_t ni, const rt_mesh* meshes, uint32_t nm,
+                        uint32_t leaf_size, cudaStream_t stream);
+
+cudaError_t launch_tonemap(const float4* accum, uint8_t* rgba8, size_t n_pixels, cudaStream_t stream);
+
+} // namespace rt

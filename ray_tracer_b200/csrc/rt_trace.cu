@@ -1,0 +1,360 @@
+// rt_trace.cu — the path-tracing kernel: camera ray generation, LBVH closest hit over the
+// SoA primitive layout, material bounce loop, sky, progressive accumulation.
+//
+// Replaces the compute entry `main` of shaders/ray_tracer.wgsl (wgsl:50-67) and everything
+// it calls (frag :306-327, trace :229-282, calculate_ray_collions :149-185, ray_sphere
+// :106-123, ray_triangle :125-147, the RNG :187-227, reflectance/refract :284-295,
+// get_environment_light :297-304).  It is NOT a transliteration: one launch covers many
+// reference dispatches, the per-pixel work is a flat state machine that refills a lane with
+// its next camera path as soon as its current one ends (no lane waits for the longest path
+// of its warp), closest hit goes through a BVH instead of the O(S+T) scan, and only the
+// winning primitive's shading data is ever fetched.  What is kept bit for bit is the
+// arithmetic contract of every value that can change a pixel.
+//
+// Build: -fmad=false (no implicit contraction), IEEE div/sqrt, no fast-math.
+#include "rt_device.cuh"
+#include "rt_kernels.h"
+
+namespace rt {
+
+#define RT_MISS 0xFFFFFFFFu
+#define RT_FLT_MAX 3.40282346638528859812e+38f
+#define RT_STACK 64
+
+struct HitRec {
+    float dst, u, v;
+    uint32_t id;
+};
+
+struct RayCtx {
+    float3 o, d;
+    float a2, a4;        // 2*dot(d,d), 4*dot(d,d) for the sphere quadratic
+};
+
+// wgsl:106-123 on slot data. Returns through `best` under the tie rule of wgsl:154.
+__device__ __forceinline__ void test_sphere(const RayCtx& r, float4 q0, float4 q1, uint32_t id, HitRec& best)
+{
+    float3 oc = r.o - xyz(q0);
+    float b = 2.0f * dot3(oc, r.d);
+    float c = dot3(oc, oc) - q1.y;                       // q1.y = radius*radius
+    float disc = __fmaf_rn(b, b, -(r.a4 * c));
+    if (disc >= 0.0f) {
+        float dst = (-b - sqrtf(disc)) / r.a2;
+        if (dst >= 0.0f && (dst < best.dst || (dst == best.dst && id < best.id && dst != RT_FLT_MAX))) {
+            best.dst = dst; best.id = id;
+        }
+    }
+}
+
+// wgsl:125-147 on slot data (A pre-translated, e1 = B-A, e2 = C-A).
+__device__ __forceinline__ void test_triangle(const RayCtx& r, float4 q0, float4 q1, float4 q2, uint32_t id, HitRec& best)
+{
+    float3 e1 = f3(q1.x, q1.y, q1.z);
+    float3 e2 = f3(q1.w, q2.x, q2.y);
+    float3 n = cross3(e1, e2);
+    float det = -dot3(r.d, n);
+    if (!(det >= 1e-6f)) return;
+    float3 ao = r.o - xyz(q0);
+    float3 dao = cross3(ao, r.d);
+    float inv = 1.0f / det;
+    float dst = dot3(ao, n) * inv;
+    float u = dot3(e2, dao) * inv;
+    float v = -(dot3(e1, dao) * inv);
+    float w = (1.0f - u) - v;
+    if (dst >= 0.0f && u >= 0.0f && v >= 0.0f && w >= 0.0f &&
+        (dst < best.dst || (dst == best.dst && id < best.id && dst != RT_FLT_MAX))) {
+        best.dst = dst; best.u = u; best.v = v; best.id = id;
+    }
+}
+
+template <bool DETAIL>
+__device__ __forceinline__ void test_slot(const SceneDev& sc, const RayCtx& r, uint32_t k, HitRec& best, uint32_t& n_tests)
+{
+    float4 q0 = __ldg(sc.g0 + k);
+    float4 q1 = __ldg(sc.g1 + k);
+    uint32_t id = __float_as_uint(q0.w);
+    if (DETAIL) n_tests++;
+    if (id < sc.n_spheres) {
+        test_sphere(r, q0, q1, id, best);
+    } else {
+        float4 q2 = __ldg(sc.g2 + k);
+        test_triangle(r, q0, q1, q2, id, best);
+    }
+}
+
+// Closest hit. BRUTE scans every slot (validation mode, the reference's own algorithm);
+// otherwise a stack traversal of the LBVH with near-child-first ordering. Box tests are
+// padded by `pad` in position space so that culling can never drop a primitive the exact
+// test would accept (DESIGN.md "Conservative culling").
+template <bool BRUTE, bool DETAIL>
+__device__ __forceinline__ HitRec closest_hit(const SceneDev& sc, const RayCtx& r, uint32_t& n_nodes, uint32_t& n_tests)
+{
+    HitRec best;
+    best.dst = RT_FLT_MAX; best.u = 0.0f; best.v = 0.0f; best.id = RT_MISS;
+    if (BRUTE) {
+        for (uint32_t k = 0; k < sc.n_prims; k++) test_slot<DETAIL>(sc, r, k, best, n_tests);
+        return best;
+    }
+    if (sc.root < 0) return best;
+
+    // per-ray slab setup: t = plane*inv - (o*inv +/- pad*|inv|); not parity-relevant
+    float3 inv = f3(__fdividef(1.0f, r.d.x), __fdividef(1.0f, r.d.y), __fdividef(1.0f, r.d.z));
+    float pad = sc.pad_scale * fmaxf(fmaxf(sc.max_abs, fabsf(r.o.x)), fmaxf(fabsf(r.o.y), fabsf(r.o.z)));
+    float3 oi = f3(r.o.x * inv.x, r.o.y * inv.y, r.o.z * inv.z);
+    float3 pi = f3(pad * fabsf(inv.x), pad * fabsf(inv.y), pad * fabsf(inv.z));
+    float3 on = f3(-(oi.x + pi.x), -(oi.y + pi.y), -(oi.z + pi.z));   // near-plane offset
+    float3 of = f3(-(oi.x - pi.x), -(oi.y - pi.y), -(oi.z - pi.z));   // far-plane offset
+    const bool sx = inv.x >= 0.0f, sy = inv.y >= 0.0f, sz = inv.z >= 0.0f;
+
+    int stack[RT_STACK];
+    int sp = 0;
+    int node = sc.root;
+    for (;;) {
+        if (node >= 0) {
+            const float4* np = sc.nodes + 4 * (size_t)node;
+            float4 n0 = __ldg(np + 0), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3);
+            if (DETAIL) n_nodes++;
+            // left box: min (n0.x,n0.y,n0.z) max (n0.w,n1.x,n1.y); right: min (n1.z,n1.w,n2.x) max (n2.y,n2.z,n2.w)
+            float lnx = sx ? n0.x : n0.w, lfx = sx ? n0.w : n0.x;
+            float lny = sy ? n0.y : n1.x, lfy = sy ? n1.x : n0.y;
+            float lnz = sz ? n0.z : n1.y, lfz = sz ? n1.y : n0.z;
+            float rnx = sx ? n1.z : n2.y, rfx = sx ? n2.y : n1.z;
+            float rny = sy ? n1.w : n2.z, rfy = sy ? n2.z : n1.w;
+            float rnz = sz ? n2.x : n2.w, rfz = sz ? n2.w : n2.x;
+            float ltn = fmaxf(fmaxf(__fmaf_rn(lnx, inv.x, on.x), __fmaf_rn(lny, inv.y, on.y)), fmaxf(__fmaf_rn(lnz, inv.z, on.z), 0.0f));
+            float ltf = fminf(fminf(__fmaf_rn(lfx, inv.x, of.x), __fmaf_rn(lfy, inv.y, of.y)), fminf(__fmaf_rn(lfz, inv.z, of.z), best.dst));
+            float rtn = fmaxf(fmaxf(__fmaf_rn(rnx, inv.x, on.x), __fmaf_rn(rny, inv.y, on.y)), fmaxf(__fmaf_rn(rnz, inv.z, on.z), 0.0f));
+            float rtf = fminf(fminf(__fmaf_rn(rfx, inv.x, of.x), __fmaf_rn(rfy, inv.y, of.y)), fminf(__fmaf_rn(rfz, inv.z, of.z), best.dst));
+            bool hl = ltn <= ltf, hr = rtn <= rtf;
+            int cl = __float_as_int(n3.x), cr = __float_as_int(n3.y);
+            if (hl && hr) {
+                bool left_first = ltn <= rtn;
+                stack[sp++] = left_first ? cr : cl;
+                node = left_first ? cl : cr;
+                continue;
+            } else if (hl) { node = cl; continue; }
+            else if (hr) { node = cr; continue; }
+        } else {
+            uint32_t leaf = (uint32_t)(~node);
+            uint32_t first = leaf >> 3, count = (leaf & 7u) + 1u;
+            for (uint32_t k = first; k < first + count; k++) test_slot<DETAIL>(sc, r, k, best, n_tests);
+        }
+        if (sp == 0) break;
+        node = stack[--sp];
+    }
+    return best;
+}
+
+// wgsl:284-288
+__device__ __forceinline__ float reflectance(float cosine, float ratio)
+{
+    float r0 = (1.0f - ratio) / (1.0f + ratio);
+    r0 = r0 * r0;
+    float x = 1.0f - cosine;
+    float x2 = x * x;
+    return r0 + (1.0f - r0) * ((x2 * x2) * x);
+}
+// wgsl:290-295 (length, not length squared — kept)
+__device__ __forceinline__ float3 refract3(float3 uv, float3 n, float ratio)
+{
+    float cos_theta = fminf(dot3(-uv, n), 1.0f);
+    float3 perp = fma3(n, cos_theta, uv) * ratio;
+    float k = -sqrtf(fabsf(1.0f - length3(perp)));
+    return fma3(n, k, perp);
+}
+// wgsl:199-203
+__device__ __forceinline__ float rand_normal_dist(uint32_t& rng)
+{
+    float theta = 6.2831852f * rand01(rng);
+    float rho = sqrtf(-2.0f * spec_logf(rand01(rng)));
+    return rho * spec_cosf(theta);
+}
+// wgsl:297-304
+__device__ __forceinline__ float4 environment_light(float3 d)
+{
+    float sky_t = spec_powf(smoothstep1(0.0f, 0.4f, d.y), 0.35f);
+    float g2s = smoothstep1(-0.01f, 0.0f, d.y);
+    float sun = spec_powf(fmaxf(0.0f, dot3(d, f3(0.1f, 1.0f, 0.1f))), 500.0f) * 0.1f;
+    float s = sun * ((g2s >= 1.0f) ? 1.0f : 0.0f);
+    float4 sky = make_float4(mix1(1.0f, 0.0788092f, sky_t), mix1(1.0f, 0.36480793f, sky_t), mix1(1.0f, 0.7264151f, sky_t), mix1(0.0f, 0.0f, sky_t));
+    return make_float4(mix1(0.35f, sky.x, g2s) + s, mix1(0.3f, sky.y, g2s) + s, mix1(0.35f, sky.z, g2s) + s, mix1(0.0f, sky.w, g2s) + s);
+}
+
+// wgsl:307-308; strict mode saturates the f32->u32 conversion (WGSL rule)
+__device__ __forceinline__ uint32_t pixel_seed(uint32_t x, uint32_t y, uint32_t w, uint32_t h, int32_t frames)
+{
+    float px = (float)x * (float)w;
+    float py = (float)y * (float)h;
+    float lin = py * (float)w + px;
+    uint32_t af = (frames < 0) ? (0u - (uint32_t)frames) : (uint32_t)frames;
+    return __float2uint_rz(lin) + af * 71939u;
+}
+
+template <bool BRUTE, bool DETAIL>
+__global__ void __launch_bounds__(RT_BLOCK_THREADS)
+trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ accum,
+             uint32_t* __restrict__ primary_ids, unsigned long long* __restrict__ counters)
+{
+    // block = 2 tiles of 8x8 pixels; a warp covers 8x4 pixels of one tile
+    const uint32_t lt = blockIdx.x * (RT_BLOCK_THREADS / 64) + (threadIdx.x >> 6);
+    const uint32_t in_tile = threadIdx.x & 63u;
+    uint32_t n_rays = 0, n_samples = 0, n_nodes = 0, n_tests = 0;
+    bool active = lt < lp.n_tiles_local;
+    uint32_t px = 0, py = 0;
+    if (active) {
+        const uint32_t t = lt * lp.tile_world + lp.tile_rank;
+        px = (t % lp.tiles_x) * 8u + (in_tile & 7u);
+        py = (t / lp.tiles_x) * 8u + (in_tile >> 3);
+        active = px < lp.width && py < lp.height;
+    }
+    if (active) {
+        const size_t pix = (size_t)py * lp.width + px;
+        const float fx = (float)px, fy = (float)py, sw = (float)lp.width, sh = (float)lp.height;
+        const float rppf = (float)lp.rpp;
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        bool acc_loaded = false;
+
+        uint32_t fi = 0;
+        int32_t frames = lp.first_frame;
+        uint32_t rng = pixel_seed(px, py, lp.width, lp.height, frames);
+        int32_t j = 0, seg = 0;
+        float4 total = make_float4(0.f, 0.f, 0.f, 0.f);
+        float4 incoming = total, color = make_float4(1.f, 1.f, 1.f, 1.f);
+        RayCtx ray;
+        ray.o = ray.d = f3(0.f, 0.f, 0.f); ray.a2 = ray.a4 = 0.f;
+        bool need_path = true;
+
+        for (;;) {
+            if (need_path) {
+                if (j > lp.rpp) {
+                    // end of one reference dispatch: wgsl:326 then the store of wgsl:59-66
+                    float4 fr = make_float4(total.x / rppf, total.y / rppf, total.z / rppf, total.w / rppf);
+                    const int32_t blend = (frames >= 0) ? (int32_t)((uint32_t)frames / lp.frame_world) : frames;
+                    if (blend >= 1) {
+                        if (!acc_loaded) { acc = accum[pix]; acc_loaded = true; }
+                        float weight = 1.0f / (float)(blend + 1);
+                        float om = 1.0f - weight;
+                        acc = make_float4(acc.x * om + fr.x * weight, acc.y * om + fr.y * weight,
+                                          acc.z * om + fr.z * weight, acc.w * om + fr.w * weight);
+                    } else {
+                        acc = fr; acc_loaded = true;
+                    }
+                    fi++;
+                    if (fi == lp.n_frames) break;
+                    frames = lp.first_frame + (int32_t)(fi * lp.frame_world);
+                    rng = pixel_seed(px, py, lp.width, lp.height, frames);
+                    j = 0;
+                    total = make_float4(0.f, 0.f, 0.f, 0.f);
+                    continue;
+                }
+                // camera ray, wgsl:313-321
+                float aax = rand01(rng), aay = rand01(rng);
+                float posx = (fx + aax) / sw, posy = (fy + aay) / sh;
+                float rdx, rdy;
+                for (;;) {                                   // rand_in_unit_disk, wgsl:216-227
+                    float r1 = rand01(rng) * 2.0f, r2 = rand01(rng) * 2.0f;
+                    rdx = r1 - 1.0f; rdy = r2 - 1.0f;
+                    if (length3(f3(rdx, rdy, 0.0f)) <= 1.0f) break;
+                }
+                rdx = rdx * cam.lens_radius; rdy = rdy * cam.lens_radius;
+                float3 offset = fma3(cam.v, rdy, cam.u * rdx);
+                ray.o = cam.origin + offset;
+                ray.d = fma3(cam.vertical, posy, fma3(cam.horizontal, posx, cam.llc)) - ray.o;
+                incoming = make_float4(0.f, 0.f, 0.f, 0.f);
+                color = make_float4(1.f, 1.f, 1.f, 1.f);
+                seg = 0;
+                need_path = false;
+                n_samples++;
+                if (lp.bounces < 0) { j++; need_path = true; continue; }   // wgsl:233 loop never runs
+            }
+
+            // ---- one path segment: wgsl:234 -------------------------------------------
+            float a = dot3(ray.d, ray.d);
+            ray.a2 = 2.0f * a; ray.a4 = 4.0f * a;
+            HitRec hit = closest_hit<BRUTE, DETAIL>(sc, ray, n_nodes, n_tests);
+            n_rays++;
+            if (primary_ids != nullptr && fi == 0 && j == 0 && seg == 0) primary_ids[pix] = hit.id;
+
+            bool done;
+            if (hit.id != RT_MISS) {
+                float3 hp = fma3(ray.d, hit.dst, ray.o);
+                float4 k0 = __ldg(sc.c0 + hit.id);
+                float3 normal;
+                if (hit.id < sc.n_spheres) {
+                    normal = normalize3(hp - xyz(k0));
+                } else {
+                    float4 k1 = __ldg(sc.c1 + hit.id), k2 = __ldg(sc.c2 + hit.id);
+                    float w = (1.0f - hit.u) - hit.v;
+                    normal = normalize3(fma3(xyz(k2), hit.v, fma3(xyz(k1), hit.u, xyz(k0) * w)));
+                }
+                const uint32_t mi = __float_as_uint(k0.w);
+                float4 mcolor = __ldg(sc.m0 + mi), emitted = __ldg(sc.m1 + mi);
+                const float smooth = __ldg(sc.m2 + mi).x;
+                float3 unit_dir = normalize3(ray.d);
+                float3 nd;
+                if (smooth == -1.0f) {                       // glass, wgsl:240-264
+                    mcolor = make_float4(1.f, 1.f, 1.f, 1.f);
+                    bool front_face = !(dot3(ray.d, normal) > 0.0f);
+                    float ratio = front_face ? (1.0f / 1.5f) : 1.5f;
+                    float cos_theta = fminf(dot3(-unit_dir, normal), 1.0f);
+                    float sin_theta = sqrtf(1.0f - cos_theta * cos_theta);
+                    bool cannot_refract = ratio * sin_theta > 1.0f;
+                    if (cannot_refract || reflectance(cos_theta, ratio) > rand01(rng)) nd = reflect3(unit_dir, normal);
+                    else nd = refract3(unit_dir, normal, ratio);
+                } else {                                     // wgsl:265-269
+                    float gx = rand_normal_dist(rng), gy = rand_normal_dist(rng), gz = rand_normal_dist(rng);
+                    float3 dir = normalize3(f3(gx, gy, gz));
+                    float3 diffuse = dir * sign1(dot3(normal, dir));
+                    float3 spec = reflect3(unit_dir, normal);
+                    nd = f3(mix1(diffuse.x, spec.x, smooth), mix1(diffuse.y, spec.y, smooth), mix1(diffuse.z, spec.z, smooth));
+                }
+                ray.o = hp; ray.d = nd;
+                incoming = incoming + emitted * color;         // wgsl:271-272
+                color = color * mcolor;                        // wgsl:273
+                seg++;
+                done = seg > lp.bounces;
+            } else {
+                if (lp.toggle != 0) incoming = incoming + environment_light(ray.d) * color;  // wgsl:274-279
+                done = true;
+            }
+            if (done) {
+                total = total + incoming;                      // wgsl:323
+                j++;
+                need_path = true;
+            }
+        }
+        accum[pix] = acc;
+    }
+
+    // counters: one atomic per warp
+    unsigned long long r = n_rays, s = n_samples, nn = n_nodes, nt = n_tests;
+    for (int o = 16; o > 0; o >>= 1) {
+        r += __shfl_xor_sync(0xffffffffu, r, o);
+        s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (DETAIL) { nn += __shfl_xor_sync(0xffffffffu, nn, o); nt += __shfl_xor_sync(0xffffffffu, nt, o); }
+    }
+    if ((threadIdx.x & 31u) == 0) {
+        atomicAdd(counters + 0, r);
+        atomicAdd(counters + 1, s);
+        if (DETAIL) { atomicAdd(counters + 2, nn); atomicAdd(counters + 3, nt); }
+    }
+}
+
+cudaError_t launch_trace(const SceneDev& sc, const CameraDev& cam, const LaunchParams& lp, float4* accum,
+                         uint32_t* primary_ids, unsigned long long* counters, bool brute, bool detail,
+                         cudaStream_t stream)
+{
+    if (lp.n_tiles_local == 0 || lp.n_frames == 0) return cudaSuccess;
+    const uint32_t tiles_per_block = RT_BLOCK_THREADS / 64;
+    dim3 grid((lp.n_tiles_local + tiles_per_block - 1) / tiles_per_block), block(RT_BLOCK_THREADS);
+    if (brute) {
+        if (detail) trace_kernel<true, true><<<grid, block, 0, stream>>>(sc, cam, lp, accum, primary_ids, counters);
+        else trace_kernel<true, false><<<grid, block, 0, stream>>>(sc, cam, lp, accum, primary_ids, counters);
+    } else {
+        if (detail) trace_kernel<false, true><<<grid, block, 0, stream>>>(sc, cam, lp, accum, primary_ids, counters);
+        else trace_kernel<false, false><<<grid, block, 0, stream>>>(sc, cam, lp, accum, primary_ids, counters);
+    }
+    return cudaGetLastError();
+}
+
+} // namespace rt

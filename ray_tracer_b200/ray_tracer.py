@@ -1,0 +1,158 @@
+"""RayTracer — the compute pipeline object of the reference, over the C ABI.
+
+Mirrors /root/reference/src/core/ray_tracer.rs: `RayTracer::new(device, texture,
+params_buffer, scene)` (:12-147) creates the pipeline and binds params, camera, the
+RGBA32F storage texture and the four scene buffers; `update_bind_group` (:149-184) rebinds
+after a resize.  Here "device" is a CUDA device ordinal, the storage texture is the
+context's accumulation image in HBM, and the bind group is the uploaded SoA scene + LBVH.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import (CAMERA_DT, MESH_DT, PARAMS_DT, SPHERE_DT, VERTEX_DT, Counters)
+
+
+class RtError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("rt_b200 error %d: %s" % (code, msg))
+        self.code = code
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None and a.size else None
+
+
+class RayTracer:
+    """One CUDA device, one accumulation image, one uploaded scene."""
+
+    def __init__(self, device, width, height, scene=None, params=None):
+        self._L = _lib.lib()
+        self._h = C.c_void_p()
+        rc = self._L.rt_create(C.byref(self._h), int(device), int(width), int(height))
+        if rc != 0:
+            raise RtError(rc, self._L.rt_last_error(None).decode())
+        self.width, self.height = int(width), int(height)
+        if scene is not None:
+            self.upload_scene(*scene)
+        if params is not None:
+            self.set_params(params)
+
+    # -- lifetime ---------------------------------------------------------------------
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            self._L.rt_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise RtError(rc, self._L.rt_last_error(self._h).decode())
+
+    # -- bindings 3..6: the scene buffers (ray_tracer.rs:51-94) ------------------------
+    def upload_scene(self, spheres, vertices, indices, meshes):
+        sp = np.ascontiguousarray(spheres, dtype=SPHERE_DT).reshape(-1)
+        vs = np.ascontiguousarray(vertices, dtype=VERTEX_DT).reshape(-1)
+        ix = np.ascontiguousarray(indices, dtype=np.uint32).reshape(-1)
+        ms = np.ascontiguousarray(meshes, dtype=MESH_DT).reshape(-1)
+        self._ck(self._L.rt_upload_scene(self._h, _ptr(sp), sp.size, _ptr(vs), vs.size, _ptr(ix), ix.size,
+                                         _ptr(ms), ms.size))
+
+    # -- bindings 0,1: uniforms (context.rs:185-186) -----------------------------------
+    def set_camera(self, camera_uniform):
+        cu = np.ascontiguousarray(camera_uniform, dtype=CAMERA_DT).reshape(1)
+        self._ck(self._L.rt_set_camera(self._h, _ptr(cu)))
+
+    def set_params(self, params=None, **kw):
+        p = np.zeros(1, PARAMS_DT)
+        if params is not None:
+            p[0] = np.ascontiguousarray(params, dtype=PARAMS_DT).reshape(1)[0]
+        else:
+            p["width"], p["height"] = self.width, self.height
+            p["accumulate"] = 1
+        for k, v in kw.items():
+            p[k] = v
+        self._ck(self._L.rt_set_params(self._h, _ptr(p)))
+        self.params = p
+
+    # -- the compute pass (context.rs:196-208) -----------------------------------------
+    def dispatch(self):
+        self._ck(self._L.rt_dispatch(self._h))
+
+    def render_frames(self, first_frame, n_frames):
+        self._ck(self._L.rt_render_frames(self._h, int(first_frame), int(n_frames)))
+
+    def sync(self):
+        self._ck(self._L.rt_sync(self._h))
+
+    def update_bind_group(self, width, height):
+        """ray_tracer.rs:149-184 after Context::resize: new zero-filled image."""
+        self._ck(self._L.rt_resize(self._h, int(width), int(height)))
+        self.width, self.height = int(width), int(height)
+
+    def clear(self):
+        self._ck(self._L.rt_clear(self._h))
+
+    def set_shard(self, tile_rank=0, tile_world=1, frame_rank=0, frame_world=1):
+        self._ck(self._L.rt_set_shard(self._h, tile_rank, tile_world, frame_rank, frame_world))
+
+    def set_option(self, option, value):
+        self._ck(self._L.rt_set_option(self._h, int(option), int(value)))
+
+    # -- read-out ----------------------------------------------------------------------
+    def read_accum(self, out=None):
+        if out is None:
+            out = np.empty((self.height, self.width, 4), np.float32)
+        self._ck(self._L.rt_read_accum(self._h, _ptr(out), out.size))
+        return out
+
+    def write_accum(self, img):
+        img = np.ascontiguousarray(img, dtype=np.float32)
+        self._ck(self._L.rt_write_accum(self._h, _ptr(img), img.size))
+
+    def read_rgba8(self):
+        out = np.empty((self.height, self.width, 4), np.uint8)
+        self._ck(self._L.rt_read_rgba8(self._h, _ptr(out), out.size))
+        return out
+
+    def read_primary_ids(self):
+        out = np.empty((self.height, self.width), np.uint32)
+        self._ck(self._L.rt_read_primary_ids(self._h, _ptr(out), out.size))
+        return out
+
+    def counters(self):
+        c = Counters()
+        self._ck(self._L.rt_get_counters(self._h, C.byref(c)))
+        return {f[0]: getattr(c, f[0]) for f in Counters._fields_}
+
+    def reset_counters(self):
+        self._ck(self._L.rt_reset_counters(self._h))
+
+    def bvh_stats(self):
+        a, b, d = C.c_uint32(), C.c_uint32(), C.c_uint32()
+        self._ck(self._L.rt_bvh_stats(self._h, C.byref(a), C.byref(b), C.byref(d)))
+        return {"n_prims": a.value, "n_nodes": b.value, "max_depth": d.value}
+
+    @property
+    def accum_device_ptr(self):
+        return self._L.rt_accum_device_ptr(self._h)
+
+    @property
+    def cuda_stream(self):
+        return self._L.rt_cuda_stream(self._h)
+
+    @property
+    def device(self):
+        return self._L.rt_device(self._h)
