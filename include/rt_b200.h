@@ -88,8 +88,10 @@ typedef struct rt_vertex {
 typedef struct rt_counters {
     uint64_t rays;            /* path segments traced */
     uint64_t samples;         /* camera paths started */
-    uint64_t node_visits;     /* BVH nodes fetched (only with RT_OPT_DETAIL_COUNTERS) */
-    uint64_t prim_tests;      /* sphere + triangle tests (only with RT_OPT_DETAIL_COUNTERS) */
+    uint64_t node_visits;     /* BVH nodes fetched, 2 box tests each (only with RT_OPT_DETAIL_COUNTERS) */
+    uint64_t tri_tests;       /* ray-triangle tests (only with RT_OPT_DETAIL_COUNTERS) */
+    uint64_t sphere_tests;    /* ray-sphere tests (only with RT_OPT_DETAIL_COUNTERS) */
+    uint64_t hit_segments;    /* segments that hit something, i.e. were shaded (only with RT_OPT_DETAIL_COUNTERS) */
     uint64_t dispatches;      /* reference-equivalent dispatches executed */
     double kernel_ms;         /* summed CUDA-event time of the trace kernel launches */
     uint64_t launches;        /* trace kernel launches */
@@ -174,8 +176,8 @@ int rt_clear(rt_ctx* ctx);
 /* Multi-GPU partition of the image/sample space (no reference counterpart).
  * tile_rank/tile_world: 8x8-pixel tiles are dealt round-robin, tile t -> rank t % world;
  * pixels of other ranks' tiles are left untouched.  frame_rank/frame_world: of the frames
- * passed to rt_render_frames only those with (frame - first_frame) % world == rank are
- * rendered, and the running mean weights count this rank's own frames.
+ * passed to rt_render_frames only those with frame % world == rank are rendered, and the
+ * running-mean weight of frame f is 1/(f / world + 1), i.e. counts this rank's own frames.
  * world = 1 disables the respective sharding. */
 int rt_set_shard(rt_ctx* ctx, uint32_t tile_rank, uint32_t tile_world,
                  uint32_t frame_rank, uint32_t frame_world);
@@ -202,6 +204,11 @@ int rt_reset_counters(rt_ctx* ctx);
 void* rt_accum_device_ptr(rt_ctx* ctx);     /* float4[W*H] */
 void* rt_cuda_stream(rt_ctx* ctx);          /* cudaStream_t */
 int rt_device(const rt_ctx* ctx);
+
+/* FP32 roofline denominator: runs an FFMA-only microbenchmark (independent chains, every
+ * SM busy) on `device` and returns the best achieved TFLOP/s (2 flop per FFMA) of `reps`
+ * launches, with the duration of that launch. */
+int rt_measure_fp32_peak(int device, int reps, double* tflops, double* seconds);
 
 /* BVH introspection for tests: number of nodes, leaves, max depth of the last build. */
 int rt_bvh_stats(rt_ctx* ctx, uint32_t* n_prims, uint32_t* n_nodes, uint32_t* max_depth);

@@ -40,7 +40,8 @@ assert (PARAMS_DT.itemsize, CAMERA_DT.itemsize, SPHERE_DT.itemsize, MESH_DT.item
 
 class Counters(C.Structure):
     _fields_ = [("rays", C.c_uint64), ("samples", C.c_uint64), ("node_visits", C.c_uint64),
-                ("prim_tests", C.c_uint64), ("dispatches", C.c_uint64), ("kernel_ms", C.c_double),
+                ("tri_tests", C.c_uint64), ("sphere_tests", C.c_uint64), ("hit_segments", C.c_uint64),
+                ("dispatches", C.c_uint64), ("kernel_ms", C.c_double),
                 ("launches", C.c_uint64)]
 
 
@@ -77,6 +78,7 @@ SYMBOLS = {
     "rt_accum_device_ptr": (_vp, [_vp]),
     "rt_cuda_stream": (_vp, [_vp]),
     "rt_device": (C.c_int, [_vp]),
+    "rt_measure_fp32_peak": (C.c_int, [C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "rt_bvh_stats": (C.c_int, [_vp, C.POINTER(_u32), C.POINTER(_u32), C.POINTER(_u32)]),
 }
 

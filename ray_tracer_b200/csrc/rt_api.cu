@@ -163,8 +163,8 @@ int rt_create(rt_ctx** out, int device, uint32_t width, uint32_t height)
     int rc = RT_OK;
     do {
         if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) { rc = cuda_fail(nullptr, e, "cudaStreamCreate"); break; }
-        if ((e = cudaMalloc((void**)&c->d_counters, 4 * sizeof(unsigned long long))) != cudaSuccess) { rc = cuda_fail(nullptr, e, "cudaMalloc counters"); break; }
-        if ((e = cudaMemsetAsync(c->d_counters, 0, 4 * sizeof(unsigned long long), c->stream)) != cudaSuccess) { rc = cuda_fail(nullptr, e, "memset counters"); break; }
+        if ((e = cudaMalloc((void**)&c->d_counters, 6 * sizeof(unsigned long long))) != cudaSuccess) { rc = cuda_fail(nullptr, e, "cudaMalloc counters"); break; }
+        if ((e = cudaMemsetAsync(c->d_counters, 0, 6 * sizeof(unsigned long long), c->stream)) != cudaSuccess) { rc = cuda_fail(nullptr, e, "memset counters"); break; }
         rc = alloc_image(c, width, height);
         if (rc != RT_OK) { g_create_err = c->err; break; }
         if ((e = cudaStreamSynchronize(c->stream)) != cudaSuccess) { rc = cuda_fail(nullptr, e, "cudaStreamSynchronize"); break; }
@@ -398,11 +398,11 @@ int rt_get_counters(rt_ctx* c, rt_counters* out)
 {
     if (!c || !out) return RT_ERR_INVALID_ARGUMENT;
     DeviceGuard g(c->device);
-    unsigned long long h[4];
+    unsigned long long h[6];
     CU(c, cudaMemcpyAsync(h, c->d_counters, sizeof h, cudaMemcpyDeviceToHost, c->stream));
     CU(c, cudaStreamSynchronize(c->stream));
     drain_events(c);
-    out->rays = h[0]; out->samples = h[1]; out->node_visits = h[2]; out->prim_tests = h[3];
+    out->rays = h[0]; out->samples = h[1]; out->node_visits = h[2]; out->tri_tests = h[3]; out->sphere_tests = h[4]; out->hit_segments = h[5];
     out->dispatches = c->dispatches; out->kernel_ms = c->kernel_ms; out->launches = c->launches;
     return RT_OK;
 }
@@ -413,7 +413,7 @@ int rt_reset_counters(rt_ctx* c)
     DeviceGuard g(c->device);
     CU(c, cudaStreamSynchronize(c->stream));
     drain_events(c);
-    CU(c, cudaMemsetAsync(c->d_counters, 0, 4 * sizeof(unsigned long long), c->stream));
+    CU(c, cudaMemsetAsync(c->d_counters, 0, 6 * sizeof(unsigned long long), c->stream));
     c->dispatches = c->launches = 0; c->kernel_ms = 0.0;
     return RT_OK;
 }

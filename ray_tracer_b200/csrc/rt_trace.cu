@@ -68,15 +68,16 @@ __device__ __forceinline__ void test_triangle(const RayCtx& r, float4 q0, float4
 }
 
 template <bool DETAIL>
-__device__ __forceinline__ void test_slot(const SceneDev& sc, const RayCtx& r, uint32_t k, HitRec& best, uint32_t& n_tests)
+__device__ __forceinline__ void test_slot(const SceneDev& sc, const RayCtx& r, uint32_t k, HitRec& best, uint32_t& n_tri, uint32_t& n_sph)
 {
     float4 q0 = __ldg(sc.g0 + k);
     float4 q1 = __ldg(sc.g1 + k);
     uint32_t id = __float_as_uint(q0.w);
-    if (DETAIL) n_tests++;
     if (id < sc.n_spheres) {
+        if (DETAIL) n_sph++;
         test_sphere(r, q0, q1, id, best);
     } else {
+        if (DETAIL) n_tri++;
         float4 q2 = __ldg(sc.g2 + k);
         test_triangle(r, q0, q1, q2, id, best);
     }
@@ -87,12 +88,12 @@ __device__ __forceinline__ void test_slot(const SceneDev& sc, const RayCtx& r, u
 // padded by `pad` in position space so that culling can never drop a primitive the exact
 // test would accept (DESIGN.md "Conservative culling").
 template <bool BRUTE, bool DETAIL>
-__device__ __forceinline__ HitRec closest_hit(const SceneDev& sc, const RayCtx& r, uint32_t& n_nodes, uint32_t& n_tests)
+__device__ __forceinline__ HitRec closest_hit(const SceneDev& sc, const RayCtx& r, uint32_t& n_nodes, uint32_t& n_tri, uint32_t& n_sph)
 {
     HitRec best;
     best.dst = RT_FLT_MAX; best.u = 0.0f; best.v = 0.0f; best.id = RT_MISS;
     if (BRUTE) {
-        for (uint32_t k = 0; k < sc.n_prims; k++) test_slot<DETAIL>(sc, r, k, best, n_tests);
+        for (uint32_t k = 0; k < sc.n_prims; k++) test_slot<DETAIL>(sc, r, k, best, n_tri, n_sph);
         return best;
     }
     if (sc.root < 0) return best;
@@ -137,7 +138,7 @@ __device__ __forceinline__ HitRec closest_hit(const SceneDev& sc, const RayCtx& 
         } else {
             uint32_t leaf = (uint32_t)(~node);
             uint32_t first = leaf >> 3, count = (leaf & 7u) + 1u;
-            for (uint32_t k = first; k < first + count; k++) test_slot<DETAIL>(sc, r, k, best, n_tests);
+            for (uint32_t k = first; k < first + count; k++) test_slot<DETAIL>(sc, r, k, best, n_tri, n_sph);
         }
         if (sp == 0) break;
         node = stack[--sp];
@@ -198,7 +199,7 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ a
     // block = 2 tiles of 8x8 pixels; a warp covers 8x4 pixels of one tile
     const uint32_t lt = blockIdx.x * (RT_BLOCK_THREADS / 64) + (threadIdx.x >> 6);
     const uint32_t in_tile = threadIdx.x & 63u;
-    uint32_t n_rays = 0, n_samples = 0, n_nodes = 0, n_tests = 0;
+    uint32_t n_rays = 0, n_samples = 0, n_nodes = 0, n_tri = 0, n_sph = 0, n_hits = 0;
     bool active = lt < lp.n_tiles_local;
     uint32_t px = 0, py = 0;
     if (active) {
@@ -271,12 +272,13 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ a
             // ---- one path segment: wgsl:234 -------------------------------------------
             float a = dot3(ray.d, ray.d);
             ray.a2 = 2.0f * a; ray.a4 = 4.0f * a;
-            HitRec hit = closest_hit<BRUTE, DETAIL>(sc, ray, n_nodes, n_tests);
+            HitRec hit = closest_hit<BRUTE, DETAIL>(sc, ray, n_nodes, n_tri, n_sph);
             n_rays++;
             if (primary_ids != nullptr && fi == 0 && j == 0 && seg == 0) primary_ids[pix] = hit.id;
 
             bool done;
             if (hit.id != RT_MISS) {
+                if (DETAIL) n_hits++;
                 float3 hp = fma3(ray.d, hit.dst, ray.o);
                 float4 k0 = __ldg(sc.c0 + hit.id);
                 float3 normal;
@@ -327,16 +329,19 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ a
     }
 
     // counters: one atomic per warp
-    unsigned long long r = n_rays, s = n_samples, nn = n_nodes, nt = n_tests;
+    unsigned long long r = n_rays, s = n_samples, nn = n_nodes, nt = n_tri, ns = n_sph, nh = n_hits;
     for (int o = 16; o > 0; o >>= 1) {
         r += __shfl_xor_sync(0xffffffffu, r, o);
         s += __shfl_xor_sync(0xffffffffu, s, o);
-        if (DETAIL) { nn += __shfl_xor_sync(0xffffffffu, nn, o); nt += __shfl_xor_sync(0xffffffffu, nt, o); }
+        if (DETAIL) {
+            nn += __shfl_xor_sync(0xffffffffu, nn, o); nt += __shfl_xor_sync(0xffffffffu, nt, o);
+            ns += __shfl_xor_sync(0xffffffffu, ns, o); nh += __shfl_xor_sync(0xffffffffu, nh, o);
+        }
     }
     if ((threadIdx.x & 31u) == 0) {
         atomicAdd(counters + 0, r);
         atomicAdd(counters + 1, s);
-        if (DETAIL) { atomicAdd(counters + 2, nn); atomicAdd(counters + 3, nt); }
+        if (DETAIL) { atomicAdd(counters + 2, nn); atomicAdd(counters + 3, nt); atomicAdd(counters + 4, ns); atomicAdd(counters + 5, nh); }
     }
 }
 

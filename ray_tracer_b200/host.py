@@ -1,0 +1,245 @@
+"""Python face of the C++ host mirror (librt_host.so <- ray_tracer_b200/host/*.cpp).
+
+Same names as the reference's host types: Camera (camera.rs), Scene (scene.rs),
+load_model (resource.rs), Context (context.rs: params / frames logic / compute pass).
+All arithmetic happens in the C++ layer; this file only marshals arrays.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from . import _lib
+from ._lib import CAMERA_DT, MESH_DT, PARAMS_DT, SPHERE_DT, VERTEX_DT
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+HOST_LIB_PATH = os.path.join(_HERE, "librt_host.so")
+_hl = None
+
+
+def build(force=False):
+    _lib.build(force)
+    src = os.path.join(_HERE, "host")
+    newest = max(os.path.getmtime(os.path.join(src, f)) for f in os.listdir(src))
+    newest = max(newest, os.path.getmtime(_lib.LIB_PATH))
+    if force or not os.path.exists(HOST_LIB_PATH) or os.path.getmtime(HOST_LIB_PATH) < newest:
+        subprocess.check_call(["make", "-C", src, "-s"])
+    return HOST_LIB_PATH
+
+
+def hostlib():
+    global _hl
+    if _hl is None:
+        if not os.path.exists(HOST_LIB_PATH):
+            raise RuntimeError("librt_host.so is not built (%s); run __graft_entry__.build()" % HOST_LIB_PATH)
+        _lib.lib()      # loads librt_b200.so first (also found through the rpath)
+        L = C.CDLL(HOST_LIB_PATH)
+        vp, u32, f32 = C.c_void_p, C.c_uint32, C.c_float
+        L.rth_last_error.restype = C.c_char_p
+        L.rth_camera_to_uniform.argtypes = [vp, vp, vp, f32, f32, f32, f32, f32, f32, vp]
+        L.rth_scene_builtin.argtypes = [C.c_int, f32, u32]
+        L.rth_scene_builtin.restype = vp
+        L.rth_scene_from_model.argtypes = [C.c_char_p]
+        L.rth_scene_from_model.restype = vp
+        L.rth_scene_free.argtypes = [vp]
+        L.rth_scene_counts.argtypes = [vp] + [C.POINTER(u32)] * 4
+        L.rth_scene_copy.argtypes = [vp] * 6
+        L.rth_loader_mesh.argtypes = [u32, u32, u32, u32, vp]
+        L.rth_context_new.argtypes = [C.c_int, u32, u32]
+        L.rth_context_new.restype = vp
+        L.rth_context_free.argtypes = [vp]
+        for n in ("update", "render", "clear_accululation", "sync"):
+            getattr(L, "rth_context_" + n).argtypes = [vp]
+        L.rth_context_run_frames.argtypes = [vp, u32]
+        L.rth_context_resize.argtypes = [vp, u32, u32]
+        L.rth_context_set_scene.argtypes = [vp, C.c_int]
+        L.rth_context_set_scene_arrays.argtypes = [vp, vp, vp, u32, vp, u32, vp, u32, vp, u32]
+        L.rth_context_get_params.argtypes = [vp, vp]
+        L.rth_context_set_params.argtypes = [vp, vp]
+        L.rth_context_read_texture.argtypes = [vp, vp, C.c_size_t]
+        L.rth_context_handle.argtypes = [vp]
+        L.rth_context_handle.restype = vp
+        _hl = L
+    return _hl
+
+
+class HostError(RuntimeError):
+    pass
+
+
+def _err():
+    return HostError(hostlib().rth_last_error().decode())
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None and a.size else None
+
+
+def _f3(v):
+    return np.ascontiguousarray(v, dtype=np.float32).reshape(3)
+
+
+class Camera:
+    """camera.rs:31-78 Camera::new(origin, look_at, view_up, fov, aspect, near, far, aperture, focus_dist)."""
+
+    def __init__(self, origin, look_at, view_up, fov, aspect, near, far, aperture, focus_dist):
+        self.origin, self.look_at, self.view_up = _f3(origin), _f3(look_at), _f3(view_up)
+        self.fov, self.aspect, self.near, self.far = float(fov), float(aspect), float(near), float(far)
+        self.aperture, self.focus_dist = float(aperture), float(focus_dist)
+
+    def to_uniform(self):
+        """camera.rs:79-121 (computed by the C++ mirror)."""
+        out = np.zeros(1, CAMERA_DT)
+        if hostlib().rth_camera_to_uniform(_ptr(self.origin), _ptr(self.look_at), _ptr(self.view_up), self.fov,
+                                           self.aspect, self.near, self.far, self.aperture, self.focus_dist,
+                                           _ptr(out)) != 0:
+            raise _err()
+        return out
+
+    def packed(self):
+        return np.concatenate([self.origin, self.look_at, self.view_up,
+                               np.array([self.fov, self.aspect, self.near, self.far, self.aperture, self.focus_dist],
+                                        np.float32)]).astype(np.float32)
+
+
+class Scene:
+    """scene.rs:94-100: camera uniform + the four arrays."""
+
+    def __init__(self, camera, spheres, vertices, indices, meshes):
+        self.camera = camera            # Camera, or a CAMERA_DT uniform for builtin scenes
+        self.spheres = np.ascontiguousarray(spheres, dtype=SPHERE_DT).reshape(-1)
+        self.vertices = np.ascontiguousarray(vertices, dtype=VERTEX_DT).reshape(-1)
+        self.indices = np.ascontiguousarray(indices, dtype=np.uint32).reshape(-1)
+        self.meshes = np.ascontiguousarray(meshes, dtype=MESH_DT).reshape(-1)
+
+    def camera_uniform(self):
+        return self.camera.to_uniform() if isinstance(self.camera, Camera) else self.camera
+
+    def arrays(self):
+        return self.spheres, self.vertices, self.indices, self.meshes
+
+    def as_tuple(self):
+        return (self.camera_uniform(),) + self.arrays()
+
+    @staticmethod
+    def _from_handle(h):
+        L = hostlib()
+        if not h:
+            raise _err()
+        try:
+            n = [C.c_uint32() for _ in range(4)]
+            L.rth_scene_counts(h, *[C.byref(x) for x in n])
+            cam = np.zeros(1, CAMERA_DT)
+            sp, vs = np.zeros(n[0].value, SPHERE_DT), np.zeros(n[1].value, VERTEX_DT)
+            ix, ms = np.zeros(n[2].value, np.uint32), np.zeros(n[3].value, MESH_DT)
+            L.rth_scene_copy(h, _ptr(cam), _ptr(sp), _ptr(vs), _ptr(ix), _ptr(ms))
+        finally:
+            L.rth_scene_free(h)
+        return Scene(cam, sp, vs, ix, ms)
+
+    # scene.rs:121-476; ids as context.rs:261-278
+    @staticmethod
+    def balls(aspect=1.0):
+        return Scene._from_handle(hostlib().rth_scene_builtin(0, aspect, 0))
+
+    @staticmethod
+    def random_balls(aspect=1.0, seed=12345):
+        return Scene._from_handle(hostlib().rth_scene_builtin(1, aspect, seed))
+
+    @staticmethod
+    def room(aspect=1.0):
+        return Scene._from_handle(hostlib().rth_scene_builtin(2, aspect, 0))
+
+    @staticmethod
+    def metal(aspect=1.0):
+        return Scene._from_handle(hostlib().rth_scene_builtin(3, aspect, 0))
+
+
+def load_model(path):
+    """resource.rs:27-45: returns (vertices, indices, meshes) as load_model would append them."""
+    s = Scene._from_handle(hostlib().rth_scene_from_model(os.fsencode(path)))
+    return s.vertices, s.indices, s.meshes
+
+
+def loader_mesh(mesh_count, n_indices, first, offset):
+    out = np.zeros(1, MESH_DT)
+    hostlib().rth_loader_mesh(mesh_count, n_indices, first, offset, _ptr(out))
+    return out
+
+
+class Context:
+    """context.rs: params + scene + compute pass, headless."""
+
+    def __init__(self, device, width, height):
+        self._L = hostlib()
+        self._h = self._L.rth_context_new(int(device), int(width), int(height))
+        if not self._h:
+            raise _err()
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.rth_context_free(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise _err()
+
+    @property
+    def params(self):
+        p = np.zeros(1, PARAMS_DT)
+        self._L.rth_context_get_params(self._h, _ptr(p))
+        return p
+
+    @params.setter
+    def params(self, p):
+        p = np.ascontiguousarray(p, dtype=PARAMS_DT).reshape(1)
+        self._L.rth_context_set_params(self._h, _ptr(p))
+
+    def set(self, **kw):
+        p = self.params
+        for k, v in kw.items():
+            p[k] = v
+        self.params = p
+
+    def update(self):
+        self._ck(self._L.rth_context_update(self._h))
+
+    def render(self):
+        self._ck(self._L.rth_context_render(self._h))
+
+    def run_frames(self, n):
+        self._ck(self._L.rth_context_run_frames(self._h, int(n)))
+
+    def resize(self, w, h):
+        self._ck(self._L.rth_context_resize(self._h, int(w), int(h)))
+
+    def clear_accululation(self):
+        self._ck(self._L.rth_context_clear_accululation(self._h))
+
+    def set_scene(self, scene):
+        if isinstance(scene, int):
+            self._ck(self._L.rth_context_set_scene(self._h, scene))
+            return
+        if not isinstance(scene.camera, Camera):
+            raise HostError("Context.set_scene needs a Scene with a Camera (not a baked uniform)")
+        cam = scene.camera.packed()
+        self._ck(self._L.rth_context_set_scene_arrays(self._h, _ptr(cam), _ptr(scene.spheres), scene.spheres.size,
+                                                      _ptr(scene.vertices), scene.vertices.size, _ptr(scene.indices),
+                                                      scene.indices.size, _ptr(scene.meshes), scene.meshes.size))
+
+    def sync(self):
+        self._ck(self._L.rth_context_sync(self._h))
+
+    def read_texture(self):
+        p = self.params
+        out = np.empty((int(p["height"][0]), int(p["width"][0]), 4), np.float32)
+        self._ck(self._L.rth_context_read_texture(self._h, _ptr(out), out.size))
+        return out
+
+    @property
+    def rt_handle(self):
+        return self._L.rth_context_handle(self._h)

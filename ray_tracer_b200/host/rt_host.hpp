@@ -1,0 +1,109 @@
+// rt_host.hpp — C++ mirror of the reference's host side of the path, above the C ABI.
+//
+// The reference is a Rust crate; no Rust toolchain exists in this image, so the host
+// layer a Rust user would keep (scene/camera/material/mesh types, Context::update/render
+// frame logic, model loaders) is mirrored here in C++ with the same names, argument
+// meaning and arithmetic, and drives librt_b200.so exactly as the Rust FFI stub in
+// INTEGRATION.md would.  Citations are to /root/reference/src/core/.
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+#include "../../include/rt_b200.h"
+
+namespace rtb {
+
+struct Vec3 { float x, y, z; };
+struct Vec4 { float x, y, z, w; };
+
+// glam 0.23 scalar Vec3 operations (operation order matters for bit-equal uniforms)
+Vec3 operator+(Vec3 a, Vec3 b);
+Vec3 operator-(Vec3 a, Vec3 b);
+Vec3 operator*(float s, Vec3 a);
+Vec3 operator/(Vec3 a, float s);
+float dot(Vec3 a, Vec3 b);
+Vec3 cross(Vec3 a, Vec3 b);
+float length(Vec3 a);
+Vec3 normalize(Vec3 a);
+
+// scene.rs:46-58 — Sphere::new (smoothness = specular clamped to <= 1, -1 passes = glass)
+rt_sphere Sphere(Vec3 position, float radius, Vec4 color, Vec4 emission_color, float emission_strength, float specular);
+// scene.rs:61-77 — Mesh::new
+rt_mesh Mesh(Vec3 pos, uint32_t first, uint32_t triangles, uint32_t offset, Vec4 color, Vec4 emission_color,
+             float emission_strength, float specular);
+// scene.rs:88-92 — Vertex::new
+rt_vertex Vertex(Vec3 pos, Vec3 normal);
+
+// camera.rs:31-47 (state) — the controller/fly-cam part is interactive input, out of scope
+struct Camera {
+    Vec3 origin{0, 0, 0}, look_at{0, 0, -1}, view_up{0, 1, 0};
+    float fov = 45.0f, aspect = 1.0f, near_ = 0.1f, far_ = 100.0f, aperture = 0.0f, focus_dist = 0.1f;
+    Camera() = default;
+    // camera.rs:49-78 — Camera::new(origin, look_at, view_up, fov, aspect, near, far, aperture, focus_dist)
+    Camera(Vec3 origin, Vec3 look_at, Vec3 view_up, float fov, float aspect, float near_, float far_, float aperture,
+           float focus_dist);
+    // camera.rs:79-121
+    rt_camera_uniform to_uniform() const;
+};
+// camera.rs:248-250
+float radians(float deg);
+
+// scene.rs:94-100
+struct Scene {
+    Camera camera;
+    std::vector<rt_sphere> spheres;
+    std::vector<rt_vertex> vertices;
+    std::vector<uint32_t> indices;
+    std::vector<rt_mesh> meshes;
+
+    static Scene empty(float aspect);                          // scene.rs:103-119
+    static Scene random_balls(float aspect, uint32_t seed);    // scene.rs:121-197 (thread_rng -> fixed stream)
+    static Scene room(float aspect);                           // scene.rs:198-310
+    static Scene metal(float aspect);                          // scene.rs:311-378
+    static Scene balls(float aspect);                          // scene.rs:379-476
+    static Scene by_id(int id, float aspect);                  // context.rs:261-278: 0 balls, 1 random_balls, 2 room, 3 metal
+    void add_dummy_mesh();                                     // the 0-triangle mesh of scene.rs:432-445
+};
+
+// resource.rs:27-45 — dispatch on extension; appends to the three arrays. Throws std::runtime_error.
+void load_model(const std::string& path, std::vector<rt_vertex>& vertices, std::vector<uint32_t>& indices,
+                std::vector<rt_mesh>& meshes);
+void load_model_obj(const std::string& path, std::vector<rt_vertex>& v, std::vector<uint32_t>& i, std::vector<rt_mesh>& m);   // :47-107
+void load_model_gltf(const std::string& path, std::vector<rt_vertex>& v, std::vector<uint32_t>& i, std::vector<rt_mesh>& m);  // :109-192
+void load_model_glb(const std::string& path, std::vector<rt_vertex>& v, std::vector<uint32_t>& i, std::vector<rt_mesh>& m);   // :194-278
+// the hard-coded record each loaded primitive gets (resource.rs:73-85)
+rt_mesh loader_mesh(uint32_t mesh_count, uint32_t n_indices, uint32_t first, uint32_t offset);
+
+// context.rs:23-37 — the part of Context on the path: params, scene, the compute pipeline,
+// frames/accumulate logic. Surface, swapchain, blit and imgui are out of scope.
+class Context {
+public:
+    rt_params params{};
+    Scene scene;
+    int selected_scene = 0;
+
+    // context.rs:40-124 — defaults bounces=3, rpp=1, skybox=0, frames=0, accumulate=1, Scene::balls
+    Context(int cuda_device, uint32_t width, uint32_t height);
+    ~Context();
+    Context(const Context&) = delete;
+    Context& operator=(const Context&) = delete;
+
+    void resize(uint32_t width, uint32_t height);   // context.rs:126-142
+    void clear_accululation();                      // context.rs:143-146 (spelling as upstream)
+    void update();                                  // context.rs:176-187 (camera fly-cam step omitted)
+    void render();                                  // context.rs:196-208 — the compute pass only
+    void set_scene(int id);                         // context.rs:259-283
+    void set_scene(Scene s);                        // RayTracer::new on a caller-built scene
+    // N redraws (update + render each), fused on the device when nothing changes between them
+    void run_frames(uint32_t n);
+    void sync();
+    std::vector<float> read_texture();              // RGBA32F, row 0 = bottom
+    rt_ctx* handle() { return ctx_; }
+
+private:
+    rt_ctx* ctx_ = nullptr;
+    void check(int rc, const char* what);
+    void upload();
+};
+
+} // namespace rtb

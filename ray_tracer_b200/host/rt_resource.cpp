@@ -1,0 +1,294 @@
+// rt_resource.cpp — model loaders, mirroring /root/reference/src/core/resource.rs.
+//
+// Upstream leans on the tobj 3.2.5 and gltf 1.1.0 crates for parsing; neither is vendored
+// in the reference tree, so the parsing itself is written here against the published
+// formats (Wavefront OBJ; glTF 2.0 JSON + GLB container), keeping exactly what the
+// reference does with the parsed data: one Mesh record per OBJ model / glTF primitive,
+// pos = (mesh_count*3, 0, 0), colour (0.2,0.2,1,1), specular 0.5, triangulated and
+// single-indexed OBJ (resource.rs:57-63), node transforms ignored for .glb (:228-276),
+// positions scaled by the running mesh count for .gltf (:180), normals required.
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <fstream>
+#include <map>
+#include <memory>
+#include <sstream>
+#include <stdexcept>
+#include <tuple>
+#include "rt_host.hpp"
+
+namespace rtb {
+
+namespace {
+
+std::string read_file(const std::string& path, bool binary)
+{
+    std::ifstream f(path, binary ? std::ios::binary : std::ios::in);
+    if (!f) throw std::runtime_error((binary ? "Binary file does not exist: " : "Text file does not exist: ") + path);  // resource.rs:8-12,19-23
+    std::ostringstream ss;
+    ss << f.rdbuf();
+    return ss.str();
+}
+
+bool ends_with(const std::string& s, const char* suf)
+{
+    size_t n = strlen(suf);
+    return s.size() >= n && s.compare(s.size() - n, n, suf) == 0;
+}
+
+std::string sibling(const std::string& path, const std::string& name)
+{
+    size_t p = path.find_last_of('/');
+    return p == std::string::npos ? name : path.substr(0, p + 1) + name;
+}
+
+// ---- minimal JSON (enough for glTF) ----------------------------------------------------
+struct Json {
+    enum Kind { Null, Bool, Num, Str, Arr, Obj } kind = Null;
+    double num = 0; bool b = false; std::string str;
+    std::vector<Json> arr; std::vector<std::pair<std::string, Json>> obj;
+    const Json* get(const char* k) const { for (auto& p : obj) if (p.first == k) return &p.second; return nullptr; }
+    const Json& at(const char* k) const { const Json* j = get(k); if (!j) throw std::runtime_error(std::string("glTF: missing key ") + k); return *j; }
+    long integer(const char* k, long dflt) const { const Json* j = get(k); return j ? (long)j->num : dflt; }
+};
+
+struct JsonParser {
+    const char* p; const char* e;
+    void ws() { while (p < e && (*p == ' ' || *p == '\n' || *p == '\r' || *p == '\t')) p++; }
+    [[noreturn]] void bad(const char* m) { throw std::runtime_error(std::string("JSON: ") + m); }
+    Json value()
+    {
+        ws();
+        if (p >= e) bad("unexpected end");
+        Json j;
+        if (*p == '{') {
+            j.kind = Json::Obj; p++; ws();
+            if (p < e && *p == '}') { p++; return j; }
+            for (;;) {
+                ws(); Json k = value(); if (k.kind != Json::Str) bad("object key");
+                ws(); if (p >= e || *p != ':') bad("':'"); p++;
+                j.obj.emplace_back(k.str, value());
+                ws(); if (p < e && *p == ',') { p++; continue; }
+                if (p < e && *p == '}') { p++; return j; }
+                bad("'}'");
+            }
+        } else if (*p == '[') {
+            j.kind = Json::Arr; p++; ws();
+            if (p < e && *p == ']') { p++; return j; }
+            for (;;) {
+                j.arr.push_back(value());
+                ws(); if (p < e && *p == ',') { p++; continue; }
+                if (p < e && *p == ']') { p++; return j; }
+                bad("']'");
+            }
+        } else if (*p == '"') {
+            j.kind = Json::Str; p++;
+            while (p < e && *p != '"') {
+                if (*p == '\\' && p + 1 < e) {
+                    p++;
+                    switch (*p) {
+                    case 'n': j.str += '\n'; break; case 't': j.str += '\t'; break; case 'r': j.str += '\r'; break;
+                    case 'b': j.str += '\b'; break; case 'f': j.str += '\f'; break;
+                    case 'u': { if (p + 4 >= e) bad("\\u"); unsigned c = (unsigned)strtoul(std::string(p + 1, p + 5).c_str(), nullptr, 16); j.str += (c < 128) ? (char)c : '?'; p += 4; break; }
+                    default: j.str += *p;
+                    }
+                    p++;
+                } else j.str += *p++;
+            }
+            if (p >= e) bad("unterminated string");
+            p++;
+            return j;
+        } else if (!strncmp(p, "true", 4)) { j.kind = Json::Bool; j.b = true; p += 4; return j; }
+        else if (!strncmp(p, "false", 5)) { j.kind = Json::Bool; p += 5; return j; }
+        else if (!strncmp(p, "null", 4)) { p += 4; return j; }
+        else {
+            char* end = nullptr;
+            j.kind = Json::Num; j.num = strtod(p, &end);
+            if (end == p) bad("value");
+            p = end;
+            return j;
+        }
+    }
+};
+
+Json parse_json(const std::string& s) { JsonParser jp{s.data(), s.data() + s.size()}; return jp.value(); }
+
+// ---- glTF accessors --------------------------------------------------------------------
+struct Accessor { const unsigned char* base; size_t stride, count; int comp, ncomp; };
+
+Accessor accessor(const Json& g, const std::vector<std::string>& buffers, long k)
+{
+    const Json& a = g.at("accessors").arr.at((size_t)k);
+    const Json& bv = g.at("bufferViews").arr.at((size_t)a.integer("bufferView", 0));
+    int comp = (int)a.integer("componentType", 0);
+    const std::string& type = a.at("type").str;
+    int nc = type == "SCALAR" ? 1 : type == "VEC2" ? 2 : type == "VEC3" ? 3 : type == "VEC4" ? 4 : type == "MAT4" ? 16 : 0;
+    size_t sz = (comp == 5120 || comp == 5121) ? 1 : (comp == 5122 || comp == 5123) ? 2 : (comp == 5125 || comp == 5126) ? 4 : 0;
+    if (!nc || !sz) throw std::runtime_error("glTF: unsupported accessor type");
+    size_t stride = (size_t)bv.integer("byteStride", 0);
+    if (!stride) stride = sz * (size_t)nc;
+    size_t off = (size_t)bv.integer("byteOffset", 0) + (size_t)a.integer("byteOffset", 0);
+    size_t count = (size_t)a.integer("count", 0);
+    const std::string& buf = buffers.at((size_t)bv.integer("buffer", 0));
+    if (count && off + (count - 1) * stride + sz * (size_t)nc > buf.size()) throw std::runtime_error("glTF: accessor outside its buffer");
+    return Accessor{(const unsigned char*)buf.data() + off, stride, count, comp, nc};
+}
+
+void append_primitive(const Json& g, const std::vector<std::string>& buffers, const Json& prim, bool scale_by_mesh_count,
+                      std::vector<rt_vertex>& vertices, std::vector<uint32_t>& indices, std::vector<rt_mesh>& meshes)
+{
+    const Json& attrs = prim.at("attributes");
+    const Json* jp = attrs.get("POSITION"); const Json* jn = attrs.get("NORMAL");
+    if (!jp || !jn) throw std::runtime_error("glTF: primitive without POSITION/NORMAL (the reference unwraps both)");  // resource.rs:149-150
+    Accessor ap = accessor(g, buffers, (long)jp->num), an = accessor(g, buffers, (long)jn->num);
+    if (ap.comp != 5126 || an.comp != 5126 || ap.ncomp != 3 || an.ncomp != 3) throw std::runtime_error("glTF: POSITION/NORMAL must be f32 VEC3");
+    std::vector<uint32_t> idx;
+    if (const Json* ji = prim.get("indices")) {
+        Accessor ai = accessor(g, buffers, (long)ji->num);
+        idx.resize(ai.count);
+        for (size_t r = 0; r < ai.count; r++) {
+            const unsigned char* q = ai.base + r * ai.stride;
+            if (ai.comp == 5121) idx[r] = *q;
+            else if (ai.comp == 5123) { uint16_t v; memcpy(&v, q, 2); idx[r] = v; }
+            else if (ai.comp == 5125) { uint32_t v; memcpy(&v, q, 4); idx[r] = v; }
+            else throw std::runtime_error("glTF: index component type");
+        }
+    } else {
+        idx.resize(ap.count);
+        for (size_t r = 0; r < ap.count; r++) idx[r] = (uint32_t)r;
+    }
+    meshes.push_back(loader_mesh((uint32_t)meshes.size(), (uint32_t)idx.size(), (uint32_t)indices.size(), (uint32_t)vertices.size()));
+    const float scale = (float)meshes.size();                     // resource.rs:180 (after the push)
+    size_t n = ap.count < an.count ? ap.count : an.count;         // positions.zip(normals)
+    for (size_t r = 0; r < n; r++) {
+        rt_vertex v{};
+        memcpy(v.pos, ap.base + r * ap.stride, 12);
+        memcpy(v.normal, an.base + r * an.stride, 12);
+        if (scale_by_mesh_count) { v.pos[0] *= scale; v.pos[1] *= scale; v.pos[2] *= scale; }
+        vertices.push_back(v);
+    }
+    indices.insert(indices.end(), idx.begin(), idx.end());
+}
+
+} // namespace
+
+rt_mesh loader_mesh(uint32_t mesh_count, uint32_t n_indices, uint32_t first, uint32_t offset)
+{
+    rt_mesh m{};
+    m.triangles = n_indices / 3; m.first = first; m.offset = offset;
+    m.pos[0] = (float)mesh_count * 3.0f;
+    m.color[0] = 0.2f; m.color[1] = 0.2f; m.color[2] = 1.0f; m.color[3] = 1.0f;
+    m.specular = 0.5f;
+    return m;
+}
+
+void load_model(const std::string& path, std::vector<rt_vertex>& v, std::vector<uint32_t>& i, std::vector<rt_mesh>& m)
+{
+    if (ends_with(path, ".obj")) load_model_obj(path, v, i, m);
+    else if (ends_with(path, ".gltf")) load_model_gltf(path, v, i, m);
+    else if (ends_with(path, ".glb")) load_model_glb(path, v, i, m);
+    else throw std::runtime_error("Unsupported model format");     // resource.rs:43
+}
+
+void load_model_obj(const std::string& path, std::vector<rt_vertex>& vertices, std::vector<uint32_t>& indices, std::vector<rt_mesh>& meshes)
+{
+    std::istringstream in(read_file(path, false));
+    std::vector<float> pos, nrm;
+    struct Model { std::map<std::tuple<long, long, long>, uint32_t> map; std::vector<rt_vertex> v; std::vector<uint32_t> idx; };
+    std::vector<Model> models;
+    std::unique_ptr<Model> cur;
+    auto flush = [&]() { if (cur && !cur->idx.empty()) models.push_back(std::move(*cur)); cur.reset(); };
+    auto fix = [](long i, size_t n) -> long { return i > 0 ? i - 1 : (long)n + i; };
+    std::string line;
+    while (std::getline(in, line)) {
+        std::istringstream ls(line);
+        std::string tag;
+        if (!(ls >> tag) || tag[0] == '#') continue;
+        if (tag == "v") { float x, y, z; ls >> x >> y >> z; pos.insert(pos.end(), {x, y, z}); }
+        else if (tag == "vn") { float x, y, z; ls >> x >> y >> z; nrm.insert(nrm.end(), {x, y, z}); }
+        else if (tag == "o" || tag == "g") { flush(); cur.reset(new Model()); }
+        else if (tag == "f") {
+            if (!cur) cur.reset(new Model());
+            std::vector<uint32_t> corner;
+            std::string c;
+            while (ls >> c) {
+                long vi = 0, ti = 0, ni = 0; bool ht = false, hn = false;
+                size_t s1 = c.find('/');
+                vi = atol(c.substr(0, s1).c_str());
+                if (s1 != std::string::npos) {
+                    size_t s2 = c.find('/', s1 + 1);
+                    std::string t = c.substr(s1 + 1, s2 == std::string::npos ? std::string::npos : s2 - s1 - 1);
+                    if (!t.empty()) { ti = atol(t.c_str()); ht = true; }
+                    if (s2 != std::string::npos && s2 + 1 < c.size()) { ni = atol(c.substr(s2 + 1).c_str()); hn = true; }
+                }
+                long v0 = fix(vi, pos.size() / 3), t0 = ht ? fix(ti, 0) : -1, n0 = hn ? fix(ni, nrm.size() / 3) : -1;
+                if (v0 < 0 || (size_t)v0 >= pos.size() / 3) throw std::runtime_error("OBJ: vertex index out of range");
+                if (n0 < 0 || (size_t)n0 >= nrm.size() / 3) throw std::runtime_error("OBJ: face without a valid normal (the reference indexes normals unconditionally)");  // resource.rs:96-100
+                auto key = std::make_tuple(v0, t0, n0);
+                auto it = cur->map.find(key);
+                if (it == cur->map.end()) {
+                    rt_vertex vv{};
+                    memcpy(vv.pos, &pos[(size_t)v0 * 3], 12); memcpy(vv.normal, &nrm[(size_t)n0 * 3], 12);
+                    it = cur->map.emplace(key, (uint32_t)cur->v.size()).first;
+                    cur->v.push_back(vv);
+                }
+                corner.push_back(it->second);
+            }
+            for (size_t k = 1; k + 1 < corner.size(); k++) { cur->idx.push_back(corner[0]); cur->idx.push_back(corner[k]); cur->idx.push_back(corner[k + 1]); }
+        }
+    }
+    flush();
+    for (auto& mdl : models) {
+        meshes.push_back(loader_mesh((uint32_t)meshes.size(), (uint32_t)mdl.idx.size(), (uint32_t)indices.size(), (uint32_t)vertices.size()));
+        vertices.insert(vertices.end(), mdl.v.begin(), mdl.v.end());
+        indices.insert(indices.end(), mdl.idx.begin(), mdl.idx.end());
+    }
+}
+
+void load_model_glb(const std::string& path, std::vector<rt_vertex>& vertices, std::vector<uint32_t>& indices, std::vector<rt_mesh>& meshes)
+{
+    std::string data = read_file(path, true);
+    if (data.size() < 20 || memcmp(data.data(), "glTF", 4) != 0) throw std::runtime_error("GLB: bad magic");
+    std::string json, blob; bool have_blob = false;
+    size_t off = 12;
+    while (off + 8 <= data.size()) {
+        uint32_t clen, ctype; memcpy(&clen, &data[off], 4); memcpy(&ctype, &data[off + 4], 4);
+        if (off + 8 + clen > data.size()) throw std::runtime_error("GLB: truncated chunk");
+        if (ctype == 0x4E4F534Au) json.assign(data, off + 8, clen);
+        else if (ctype == 0x004E4942u && !have_blob) { blob.assign(data, off + 8, clen); have_blob = true; }
+        off += 8 + (size_t)clen;
+    }
+    Json g = parse_json(json);
+    std::vector<std::string> buffers;
+    if (const Json* jb = g.get("buffers"))
+        for (const Json& b : jb->arr) {
+            if (const Json* uri = b.get("uri")) buffers.push_back(read_file(sibling(path, uri->str), true));
+            else { if (!have_blob) throw std::runtime_error("Missing blob"); buffers.push_back(blob); }   // resource.rs:211-216
+        }
+    if (const Json* jm = g.get("meshes"))
+        for (const Json& mesh : jm->arr)
+            for (const Json& prim : mesh.at("primitives").arr) append_primitive(g, buffers, prim, false, vertices, indices, meshes);
+}
+
+void load_model_gltf(const std::string& path, std::vector<rt_vertex>& vertices, std::vector<uint32_t>& indices, std::vector<rt_mesh>& meshes)
+{
+    Json g = parse_json(read_file(path, false));
+    std::vector<std::string> buffers;
+    if (const Json* jb = g.get("buffers"))
+        for (const Json& b : jb->arr) {
+            const Json* uri = b.get("uri");
+            buffers.push_back(uri ? read_file(sibling(path, uri->str), true) : std::string());   // resource.rs:123-133
+        }
+    if (const Json* js = g.get("scenes"))
+        for (const Json& sc : js->arr)
+            for (const Json& ni : sc.at("nodes").arr) {
+                const Json& node = g.at("nodes").arr.at((size_t)ni.num);
+                const Json* jm = node.get("mesh");
+                if (!jm) throw std::runtime_error("Failed to get mesh");   // resource.rs:142
+                for (const Json& prim : g.at("meshes").arr.at((size_t)jm->num).at("primitives").arr)
+                    append_primitive(g, buffers, prim, true, vertices, indices, meshes);
+            }
+}
+
+} // namespace rtb

@@ -1,0 +1,80 @@
+"""GPU parity on the mesh configurations (C2-C5 at reduced resolution / counts): CUDA LBVH
+path vs the brute-force CPU oracle, bit for bit, plus LBVH vs the GPU's own exhaustive mode
+at sizes the CPU cannot finish."""
+import numpy as np
+import pytest
+
+from util import assert_bits_equal
+
+pytestmark = pytest.mark.gpu
+
+
+def _gpu(rt, scene, w, h, frames, bounces, sky, brute=False, leaf=None):
+    cam, sp, vs, ix, ms = scene.as_tuple()
+    tr = rt.RayTracer(0, w, h)
+    if leaf is not None:
+        tr.set_option(rt._lib.RT_OPT_LEAF_SIZE, leaf)
+    tr.upload_scene(sp, vs, ix, ms)
+    tr.set_camera(cam)
+    tr.set_params(number_of_bounces=bounces, rays_per_pixel=1, skybox=sky, frames=0)
+    tr.set_option(rt._lib.RT_OPT_PRIMARY_IDS, 1)
+    tr.set_option(rt._lib.RT_OPT_TRAVERSAL, 1 if brute else 0)
+    tr.render_frames(0, frames)
+    out = tr.read_accum(), tr.read_primary_ids(), tr.counters(), tr.bvh_stats()
+    tr.close()
+    return out
+
+
+def _cpu(oracle, scene, w, h, frames, bounces, sky):
+    cam, sp, vs, ix, ms = scene.as_tuple()
+    sc = (cam.view(oracle.CAMERA_DT), sp.view(oracle.SPHERE_DT), vs.view(oracle.VERTEX_DT), ix, ms.view(oracle.MESH_DT))
+    ids = np.full((h, w), 0xFFFFFFFF, np.uint32)
+    ctr = np.zeros(3, np.uint64)
+    return oracle.render(sc, w, h, frames, bounces, 1, sky, 0, ids, ctr), ids, ctr
+
+
+@pytest.mark.parametrize("name,w,h,frames", [("c2_cube", 160, 90, 2), ("c3_teapot", 96, 54, 1), ("c4_tree", 96, 54, 1)])
+def test_config_vs_oracle(rtlib, oracle, name, w, h, frames):
+    from ray_tracer_b200 import configs
+    scene, meta = configs.build(name, w, h)
+    p = meta["params"]
+    gi, gid, gc, st = _gpu(rtlib, scene, w, h, frames, p["number_of_bounces"], p["skybox"])
+    ci, cid, cc = _cpu(oracle, scene, w, h, frames, p["number_of_bounces"], p["skybox"])
+    assert (gid != 0xFFFFFFFF).sum() > 0.02 * w * h, "camera does not see the model"
+    assert np.array_equal(gid, cid), "primary ids differ at %d pixels" % int((gid != cid).sum())
+    assert gc["rays"] == int(cc[0])
+    assert_bits_equal(gi, ci, name)
+
+
+@pytest.mark.parametrize("name,w,h,frames", [("c3_teapot", 480, 270, 2), ("c4_tree", 480, 270, 2), ("c2_cube", 480, 270, 2)])
+def test_config_bvh_vs_gpu_brute_force(rtlib, name, w, h, frames):
+    from ray_tracer_b200 import configs
+    scene, meta = configs.build(name, w, h)
+    p = meta["params"]
+    a, aid, ac, st = _gpu(rtlib, scene, w, h, frames, p["number_of_bounces"], p["skybox"])
+    b, bid, bc, _ = _gpu(rtlib, scene, w, h, frames, p["number_of_bounces"], p["skybox"], brute=True)
+    assert np.array_equal(aid, bid)
+    assert ac["rays"] == bc["rays"]
+    assert_bits_equal(a, b, name)
+
+
+@pytest.mark.parametrize("leaf", [1, 2, 8])
+def test_leaf_size_is_result_invisible(rtlib, leaf):
+    from ray_tracer_b200 import configs
+    scene, meta = configs.build("c3_teapot", 192, 108)
+    a, aid, ac, _ = _gpu(rtlib, scene, 192, 108, 2, 8, 1)
+    b, bid, bc, _ = _gpu(rtlib, scene, 192, 108, 2, 8, 1, leaf=leaf)
+    assert np.array_equal(aid, bid) and ac["rays"] == bc["rays"]
+    assert_bits_equal(a, b, "leaf size %d" % leaf)
+
+
+def test_stress_scene_builds_and_matches_brute_force_on_a_crop(rtlib):
+    """C5 (100k spheres + 64 teapot instances = 1.1 M primitives): LBVH vs exhaustive GPU mode
+    on a small image."""
+    from ray_tracer_b200 import configs
+    scene, meta = configs.build("c5_stress", 64, 36)
+    a, aid, ac, st = _gpu(rtlib, scene, 64, 36, 1, 3, 1)
+    assert st["n_prims"] == 100000 + 64 * 15704
+    b, bid, bc, _ = _gpu(rtlib, scene, 64, 36, 1, 3, 1, brute=True)
+    assert np.array_equal(aid, bid) and ac["rays"] == bc["rays"]
+    assert_bits_equal(a, b, "c5")
