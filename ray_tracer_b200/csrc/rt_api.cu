@@ -28,7 +28,12 @@ struct rt_ctx {
     uint32_t width = 0, height = 0;
     float4* accum = nullptr;
     uint32_t* primary_ids = nullptr;
-    unsigned long long* d_counters = nullptr;     // rays, samples, node visits, prim tests
+    unsigned long long* d_counters = nullptr;     // rays, samples, node visits, tri/sphere tests, hit segments
+    unsigned long long* d_queue = nullptr;        // work-queue head of the persistent trace kernel
+    float4* staging = nullptr;                    // per-dispatch frag planes awaiting the blend
+    uint32_t staging_frames = 0;
+    int n_sms = 148;
+    int64_t opt_staging_bytes = 2ll << 30;
     rt::SceneBuffers scene;
     bool has_scene = false, has_camera = false, has_params = false;
     rt_params params{};
@@ -63,7 +68,8 @@ int alloc_image(rt_ctx* c, uint32_t w, uint32_t h)
 {
     if (c->accum) cudaFree(c->accum);
     if (c->primary_ids) cudaFree(c->primary_ids);
-    c->accum = nullptr; c->primary_ids = nullptr;
+    if (c->staging) cudaFree(c->staging);
+    c->accum = nullptr; c->primary_ids = nullptr; c->staging = nullptr; c->staging_frames = 0;
     size_t n = (size_t)w * h;
     CU(c, cudaMalloc((void**)&c->accum, n * sizeof(float4)));
     CU(c, cudaMalloc((void**)&c->primary_ids, n * sizeof(uint32_t)));
@@ -96,6 +102,24 @@ rt::CameraDev to_dev(const rt_camera_uniform& u)
     return d;
 }
 
+// Dispatches fused per launch: bounded by the option and by the staging budget (one W*H float4 plane each).
+uint32_t frames_per_launch(const rt_ctx* c)
+{
+    int64_t by_mem = c->opt_staging_bytes / (int64_t)((size_t)c->width * c->height * sizeof(float4));
+    int64_t f = c->opt_frames_per_launch;
+    if (f > by_mem) f = by_mem;
+    return (uint32_t)(f < 1 ? 1 : f);
+}
+
+int ensure_staging(rt_ctx* c, uint32_t frames)
+{
+    if (c->staging_frames >= frames) return RT_OK;
+    if (c->staging) { CU(c, cudaStreamSynchronize(c->stream)); cudaFree(c->staging); c->staging = nullptr; c->staging_frames = 0; }
+    CU(c, cudaMalloc((void**)&c->staging, (size_t)frames * c->width * c->height * sizeof(float4)));
+    c->staging_frames = frames;
+    return RT_OK;
+}
+
 // Launch `n_frames` fused dispatches starting at `first_frame` with stride c->frame_world.
 int launch(rt_ctx* c, int32_t first_frame, uint32_t n_frames, bool want_ids)
 {
@@ -112,15 +136,16 @@ int launch(rt_ctx* c, int32_t first_frame, uint32_t n_frames, bool want_ids)
     lp.tile_rank = c->tile_rank; lp.tile_world = c->tile_world; lp.frame_world = c->frame_world;
     lp.tiles_x = (c->width + 7) / 8;
     const uint32_t tiles = lp.tiles_x * ((c->height + 7) / 8);
-    lp.n_tiles_local = tiles > c->tile_rank ? (tiles - c->tile_rank + c->tile_world - 1) / c->tile_world : 0;
+    lp.n_warp_tiles = 2u * (tiles > c->tile_rank ? (tiles - c->tile_rank + c->tile_world - 1) / c->tile_world : 0);
     lp.seed_mode = (int32_t)c->opt_seed_mode;
 
+    { int rc = ensure_staging(c, n_frames); if (rc != RT_OK) return rc; }
     std::pair<cudaEvent_t, cudaEvent_t> ev;
     if (!c->pool.empty()) { ev = c->pool.back(); c->pool.pop_back(); }
     else { CU(c, cudaEventCreate(&ev.first)); CU(c, cudaEventCreate(&ev.second)); }
     CU(c, cudaEventRecord(ev.first, c->stream));
-    cudaError_t e = rt::launch_trace(sd, to_dev(c->camera), lp, c->accum, want_ids ? c->primary_ids : nullptr,
-                                     c->d_counters, c->opt_traversal == 1, c->opt_detail != 0, c->stream);
+    cudaError_t e = rt::launch_trace(sd, to_dev(c->camera), lp, c->staging, c->accum, want_ids ? c->primary_ids : nullptr,
+                                     c->d_counters, c->d_queue, c->opt_traversal == 1, c->opt_detail != 0, c->n_sms, c->stream);
     if (e != cudaSuccess) return cuda_fail(c, e, "trace kernel launch");
     CU(c, cudaEventRecord(ev.second, c->stream));
     c->pending.push_back(ev);
@@ -165,6 +190,8 @@ int rt_create(rt_ctx** out, int device, uint32_t width, uint32_t height)
         if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) { rc = cuda_fail(nullptr, e, "cudaStreamCreate"); break; }
         if ((e = cudaMalloc((void**)&c->d_counters, 6 * sizeof(unsigned long long))) != cudaSuccess) { rc = cuda_fail(nullptr, e, "cudaMalloc counters"); break; }
         if ((e = cudaMemsetAsync(c->d_counters, 0, 6 * sizeof(unsigned long long), c->stream)) != cudaSuccess) { rc = cuda_fail(nullptr, e, "memset counters"); break; }
+        if ((e = cudaMalloc((void**)&c->d_queue, sizeof(unsigned long long))) != cudaSuccess) { rc = cuda_fail(nullptr, e, "cudaMalloc queue"); break; }
+        { cudaDeviceProp prop; if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) { rc = cuda_fail(nullptr, e, "cudaGetDeviceProperties"); break; } c->n_sms = prop.multiProcessorCount; }
         rc = alloc_image(c, width, height);
         if (rc != RT_OK) { g_create_err = c->err; break; }
         if ((e = cudaStreamSynchronize(c->stream)) != cudaSuccess) { rc = cuda_fail(nullptr, e, "cudaStreamSynchronize"); break; }
@@ -185,6 +212,8 @@ void rt_destroy(rt_ctx* c)
     if (c->accum) cudaFree(c->accum);
     if (c->primary_ids) cudaFree(c->primary_ids);
     if (c->d_counters) cudaFree(c->d_counters);
+    if (c->d_queue) cudaFree(c->d_queue);
+    if (c->staging) cudaFree(c->staging);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -271,7 +300,7 @@ int rt_render_frames(rt_ctx* c, int32_t first_frame, uint32_t n_frames)
         f += (c->frame_rank + world - r) % world;       // first frame of this rank
     }
     bool want_ids = c->opt_primary_ids != 0;
-    const int64_t per = c->opt_frames_per_launch < 1 ? 1 : c->opt_frames_per_launch;
+    const int64_t per = frames_per_launch(c);
     while (f < end) {
         int64_t mine = (end - f + world - 1) / world;   // frames f, f+world, ... below end
         uint32_t n = (uint32_t)(mine < per ? mine : per);

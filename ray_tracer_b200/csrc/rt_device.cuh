@@ -49,7 +49,7 @@ struct LaunchParams {
     uint32_t n_frames;         // fused dispatches (frame stride = frame_world)
     uint32_t tile_rank, tile_world;
     uint32_t frame_world;      // stride between frames rendered by this rank
-    uint32_t tiles_x, n_tiles_local; // 8x8 tiles per row; tiles owned by this rank
+    uint32_t tiles_x, n_warp_tiles;  // 8x8 shard tiles per row; 8x4 warp tiles owned by this rank (2 per shard tile)
     int32_t seed_mode;
 };
 

@@ -9,9 +9,13 @@
 
 namespace rt {
 
-cudaError_t launch_trace(const SceneDev& sc, const CameraDev& cam, const LaunchParams& lp, float4* accum,
-                         uint32_t* primary_ids, unsigned long long* counters, bool brute, bool detail,
-                         cudaStream_t stream);
+#define RT_QUEUE_CHUNK 128ull     // work items a warp takes from the global queue per atomic
+
+// trace (persistent warps over the (pixel, dispatch) item queue) + blend (running mean of the
+// staged dispatches into `accum`). `staging` holds lp.n_frames planes of W*H float4.
+cudaError_t launch_trace(const SceneDev& sc, const CameraDev& cam, const LaunchParams& lp, float4* staging, float4* accum,
+                         uint32_t* primary_ids, unsigned long long* counters, unsigned long long* queue,
+                         bool brute, bool detail, int n_sms, cudaStream_t stream);
 
 // Device-resident scene: SoA primitive arrays + LBVH, built on the GPU from the AoS records.
 struct SceneBuffers {

@@ -191,64 +191,127 @@ __device__ __forceinline__ uint32_t pixel_seed(uint32_t x, uint32_t y, uint32_t 
     return __float2uint_rz(lin) + af * 71939u;
 }
 
+// One path segment's shading (wgsl:236-273). Consumes RNG exactly as the reference does,
+// updates the ray in place, returns nothing: the caller decides about path termination.
+__device__ __forceinline__ void shade_hit(const SceneDev& sc, const HitRec& hit, RayCtx& ray, uint32_t& rng,
+                                          float4& incoming, float4& color)
+{
+    float3 hp = fma3(ray.d, hit.dst, ray.o);
+    float4 k0 = __ldg(sc.c0 + hit.id);
+    float3 normal;
+    if (hit.id < sc.n_spheres) {
+        normal = normalize3(hp - xyz(k0));
+    } else {
+        float4 k1 = __ldg(sc.c1 + hit.id), k2 = __ldg(sc.c2 + hit.id);
+        float w = (1.0f - hit.u) - hit.v;
+        normal = normalize3(fma3(xyz(k2), hit.v, fma3(xyz(k1), hit.u, xyz(k0) * w)));
+    }
+    const uint32_t mi = __float_as_uint(k0.w);
+    float4 mcolor = __ldg(sc.m0 + mi), emitted = __ldg(sc.m1 + mi);
+    const float smooth = __ldg(sc.m2 + mi).x;
+    float3 unit_dir = normalize3(ray.d);
+    float3 nd;
+    if (smooth == -1.0f) {                       // glass, wgsl:240-264
+        mcolor = make_float4(1.f, 1.f, 1.f, 1.f);
+        bool front_face = !(dot3(ray.d, normal) > 0.0f);
+        float ratio = front_face ? (1.0f / 1.5f) : 1.5f;
+        float cos_theta = fminf(dot3(-unit_dir, normal), 1.0f);
+        float sin_theta = sqrtf(1.0f - cos_theta * cos_theta);
+        bool cannot_refract = ratio * sin_theta > 1.0f;
+        if (cannot_refract || reflectance(cos_theta, ratio) > rand01(rng)) nd = reflect3(unit_dir, normal);
+        else nd = refract3(unit_dir, normal, ratio);
+    } else {                                     // wgsl:265-269
+        float gx = rand_normal_dist(rng), gy = rand_normal_dist(rng), gz = rand_normal_dist(rng);
+        float3 dir = normalize3(f3(gx, gy, gz));
+        float3 diffuse = dir * sign1(dot3(normal, dir));
+        float3 spec = reflect3(unit_dir, normal);
+        nd = f3(mix1(diffuse.x, spec.x, smooth), mix1(diffuse.y, spec.y, smooth), mix1(diffuse.z, spec.z, smooth));
+    }
+    ray.o = hp; ray.d = nd;
+    incoming = incoming + emitted * color;         // wgsl:271-272
+    color = color * mcolor;                        // wgsl:273
+}
+
+// ---- the trace kernel ---------------------------------------------------------------------
+// Persistent warps pull work from one global queue. A work item is one (pixel, dispatch)
+// pair: the rpp+1 camera paths of one pixel in one reference dispatch, whose mean/rpp
+// ("frag", wgsl:326) goes to the staging plane of that dispatch.  Items are numbered
+// tile-major, dispatch-minor, 32 pixels (an 8x4 tile) at a time, so the lanes of a warp stay
+// on neighbouring pixels while heavy tiles are spread over every SM of the chip.  A lane
+// takes its next item the moment its current one ends — no lane waits for the longest path
+// of its warp, no warp waits for its block.
 template <bool BRUTE, bool DETAIL>
 __global__ void __launch_bounds__(RT_BLOCK_THREADS)
-trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ accum,
-             uint32_t* __restrict__ primary_ids, unsigned long long* __restrict__ counters)
+trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ staging,
+             uint32_t* __restrict__ primary_ids, unsigned long long* __restrict__ counters,
+             unsigned long long* __restrict__ queue)
 {
-    // block = 2 tiles of 8x8 pixels; a warp covers 8x4 pixels of one tile
-    const uint32_t lt = blockIdx.x * (RT_BLOCK_THREADS / 64) + (threadIdx.x >> 6);
-    const uint32_t in_tile = threadIdx.x & 63u;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint64_t n_items = (uint64_t)lp.n_warp_tiles * lp.n_frames * 32ull;
+    const size_t plane = (size_t)lp.width * lp.height;
+    const float sw = (float)lp.width, sh = (float)lp.height, rppf = (float)lp.rpp;
     uint32_t n_rays = 0, n_samples = 0, n_nodes = 0, n_tri = 0, n_sph = 0, n_hits = 0;
-    bool active = lt < lp.n_tiles_local;
-    uint32_t px = 0, py = 0;
-    if (active) {
-        const uint32_t t = lt * lp.tile_world + lp.tile_rank;
-        px = (t % lp.tiles_x) * 8u + (in_tile & 7u);
-        py = (t / lp.tiles_x) * 8u + (in_tile >> 3);
-        active = px < lp.width && py < lp.height;
-    }
-    if (active) {
-        const size_t pix = (size_t)py * lp.width + px;
-        const float fx = (float)px, fy = (float)py, sw = (float)lp.width, sh = (float)lp.height;
-        const float rppf = (float)lp.rpp;
-        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-        bool acc_loaded = false;
 
-        uint32_t fi = 0;
-        int32_t frames = lp.first_frame;
-        uint32_t rng = pixel_seed(px, py, lp.width, lp.height, frames);
-        int32_t j = 0, seg = 0;
-        float4 total = make_float4(0.f, 0.f, 0.f, 0.f);
-        float4 incoming = total, color = make_float4(1.f, 1.f, 1.f, 1.f);
-        RayCtx ray;
-        ray.o = ray.d = f3(0.f, 0.f, 0.f); ray.a2 = ray.a4 = 0.f;
-        bool need_path = true;
+    uint64_t pool_next = 0, pool_end = 0;          // warp-uniform: items granted to this warp
+    bool exhausted = false;                        // warp-uniform: the global queue is empty
 
-        for (;;) {
-            if (need_path) {
-                if (j > lp.rpp) {
-                    // end of one reference dispatch: wgsl:326 then the store of wgsl:59-66
-                    float4 fr = make_float4(total.x / rppf, total.y / rppf, total.z / rppf, total.w / rppf);
-                    const int32_t blend = (frames >= 0) ? (int32_t)((uint32_t)frames / lp.frame_world) : frames;
-                    if (blend >= 1) {
-                        if (!acc_loaded) { acc = accum[pix]; acc_loaded = true; }
-                        float weight = 1.0f / (float)(blend + 1);
-                        float om = 1.0f - weight;
-                        acc = make_float4(acc.x * om + fr.x * weight, acc.y * om + fr.y * weight,
-                                          acc.z * om + fr.z * weight, acc.w * om + fr.w * weight);
-                    } else {
-                        acc = fr; acc_loaded = true;
-                    }
-                    fi++;
-                    if (fi == lp.n_frames) break;
-                    frames = lp.first_frame + (int32_t)(fi * lp.frame_world);
-                    rng = pixel_seed(px, py, lp.width, lp.height, frames);
-                    j = 0;
+    // per-lane state
+    bool has_item = false, need_path = true;
+    uint32_t px = 0, py = 0, fi = 0, rng = 0;
+    float fx = 0.f, fy = 0.f;
+    int32_t j = 0, seg = 0;
+    float4 total = make_float4(0.f, 0.f, 0.f, 0.f), incoming = total, color = total;
+    RayCtx ray;
+    ray.o = ray.d = f3(0.f, 0.f, 0.f); ray.a2 = ray.a4 = 0.f;
+
+    for (;;) {
+        // ---- item boundary: store frag, take the next item (warp-uniform control flow) ----
+        if (has_item && need_path && j > lp.rpp) {
+            staging[(size_t)fi * plane + (size_t)py * lp.width + px] =
+                make_float4(total.x / rppf, total.y / rppf, total.z / rppf, total.w / rppf);   // wgsl:326
+            has_item = false;
+        }
+        unsigned want = __ballot_sync(0xffffffffu, !has_item && !exhausted);
+        while (want) {
+            if (pool_next == pool_end && !exhausted) {
+                unsigned long long g = 0;
+                if (lane == 0) g = atomicAdd(queue, (unsigned long long)RT_QUEUE_CHUNK);
+                g = __shfl_sync(0xffffffffu, g, 0);
+                if (g >= n_items) { exhausted = true; }
+                else { pool_next = g; pool_end = (g + RT_QUEUE_CHUNK < n_items) ? g + RT_QUEUE_CHUNK : n_items; }
+            }
+            if (exhausted) break;
+            const bool mine = (want >> lane) & 1u;
+            const uint32_t rank = __popc(want & ((1u << lane) - 1u));
+            const uint64_t avail = pool_end - pool_next;
+            if (mine && rank < avail) {
+                const uint64_t g = pool_next + rank;
+                const uint32_t pos = (uint32_t)(g & 31ull);
+                const uint64_t tf = g >> 5;
+                fi = (uint32_t)(tf % lp.n_frames);
+                const uint32_t wt = (uint32_t)(tf / lp.n_frames);            // local 8x4 warp tile
+                const uint32_t t = (wt >> 1) * lp.tile_world + lp.tile_rank; // 8x8 shard tile (tile t -> rank t % world)
+                px = (t % lp.tiles_x) * 8u + (pos & 7u);
+                py = (t / lp.tiles_x) * 8u + (wt & 1u) * 4u + (pos >> 3);
+                has_item = true;
+                if (px < lp.width && py < lp.height) {
+                    fx = (float)px; fy = (float)py;
+                    rng = pixel_seed(px, py, lp.width, lp.height, lp.first_frame + (int32_t)(fi * lp.frame_world));
+                    j = 0; need_path = true;
                     total = make_float4(0.f, 0.f, 0.f, 0.f);
-                    continue;
+                } else {
+                    has_item = false;                                        // outside the image: nothing to do
                 }
-                // camera ray, wgsl:313-321
+            }
+            const uint32_t granted = (uint32_t)min((uint64_t)__popc(want), avail);
+            pool_next += granted;
+            want = __ballot_sync(0xffffffffu, !has_item && !exhausted);
+        }
+        if (__ballot_sync(0xffffffffu, has_item) == 0u) break;               // queue empty, every lane idle
+
+        if (has_item) {
+            if (need_path) {
+                // camera ray, wgsl:313-321 (j <= rpp is guaranteed here)
                 float aax = rand01(rng), aay = rand01(rng);
                 float posx = (fx + aax) / sw, posy = (fy + aay) / sh;
                 float rdx, rdy;
@@ -266,58 +329,26 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ a
                 seg = 0;
                 need_path = false;
                 n_samples++;
-                if (lp.bounces < 0) { j++; need_path = true; continue; }   // wgsl:233 loop never runs
             }
-
-            // ---- one path segment: wgsl:234 -------------------------------------------
-            float a = dot3(ray.d, ray.d);
-            ray.a2 = 2.0f * a; ray.a4 = 4.0f * a;
-            HitRec hit = closest_hit<BRUTE, DETAIL>(sc, ray, n_nodes, n_tri, n_sph);
-            n_rays++;
-            if (primary_ids != nullptr && fi == 0 && j == 0 && seg == 0) primary_ids[pix] = hit.id;
-
             bool done;
-            if (hit.id != RT_MISS) {
-                if (DETAIL) n_hits++;
-                float3 hp = fma3(ray.d, hit.dst, ray.o);
-                float4 k0 = __ldg(sc.c0 + hit.id);
-                float3 normal;
-                if (hit.id < sc.n_spheres) {
-                    normal = normalize3(hp - xyz(k0));
-                } else {
-                    float4 k1 = __ldg(sc.c1 + hit.id), k2 = __ldg(sc.c2 + hit.id);
-                    float w = (1.0f - hit.u) - hit.v;
-                    normal = normalize3(fma3(xyz(k2), hit.v, fma3(xyz(k1), hit.u, xyz(k0) * w)));
-                }
-                const uint32_t mi = __float_as_uint(k0.w);
-                float4 mcolor = __ldg(sc.m0 + mi), emitted = __ldg(sc.m1 + mi);
-                const float smooth = __ldg(sc.m2 + mi).x;
-                float3 unit_dir = normalize3(ray.d);
-                float3 nd;
-                if (smooth == -1.0f) {                       // glass, wgsl:240-264
-                    mcolor = make_float4(1.f, 1.f, 1.f, 1.f);
-                    bool front_face = !(dot3(ray.d, normal) > 0.0f);
-                    float ratio = front_face ? (1.0f / 1.5f) : 1.5f;
-                    float cos_theta = fminf(dot3(-unit_dir, normal), 1.0f);
-                    float sin_theta = sqrtf(1.0f - cos_theta * cos_theta);
-                    bool cannot_refract = ratio * sin_theta > 1.0f;
-                    if (cannot_refract || reflectance(cos_theta, ratio) > rand01(rng)) nd = reflect3(unit_dir, normal);
-                    else nd = refract3(unit_dir, normal, ratio);
-                } else {                                     // wgsl:265-269
-                    float gx = rand_normal_dist(rng), gy = rand_normal_dist(rng), gz = rand_normal_dist(rng);
-                    float3 dir = normalize3(f3(gx, gy, gz));
-                    float3 diffuse = dir * sign1(dot3(normal, dir));
-                    float3 spec = reflect3(unit_dir, normal);
-                    nd = f3(mix1(diffuse.x, spec.x, smooth), mix1(diffuse.y, spec.y, smooth), mix1(diffuse.z, spec.z, smooth));
-                }
-                ray.o = hp; ray.d = nd;
-                incoming = incoming + emitted * color;         // wgsl:271-272
-                color = color * mcolor;                        // wgsl:273
-                seg++;
-                done = seg > lp.bounces;
+            if (lp.bounces < 0) {
+                done = true;                                                 // wgsl:233 loop never runs
             } else {
-                if (lp.toggle != 0) incoming = incoming + environment_light(ray.d) * color;  // wgsl:274-279
-                done = true;
+                // ---- one path segment: wgsl:234 ---------------------------------------
+                float a = dot3(ray.d, ray.d);
+                ray.a2 = 2.0f * a; ray.a4 = 4.0f * a;
+                HitRec hit = closest_hit<BRUTE, DETAIL>(sc, ray, n_nodes, n_tri, n_sph);
+                n_rays++;
+                if (primary_ids != nullptr && fi == 0 && j == 0 && seg == 0) primary_ids[(size_t)py * lp.width + px] = hit.id;
+                if (hit.id != RT_MISS) {
+                    if (DETAIL) n_hits++;
+                    shade_hit(sc, hit, ray, rng, incoming, color);
+                    seg++;
+                    done = seg > lp.bounces;
+                } else {
+                    if (lp.toggle != 0) incoming = incoming + environment_light(ray.d) * color;  // wgsl:274-279
+                    done = true;
+                }
             }
             if (done) {
                 total = total + incoming;                      // wgsl:323
@@ -325,7 +356,6 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ a
                 need_path = true;
             }
         }
-        accum[pix] = acc;
     }
 
     // counters: one atomic per warp
@@ -338,27 +368,80 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ a
             ns += __shfl_xor_sync(0xffffffffu, ns, o); nh += __shfl_xor_sync(0xffffffffu, nh, o);
         }
     }
-    if ((threadIdx.x & 31u) == 0) {
+    if (lane == 0) {
         atomicAdd(counters + 0, r);
         atomicAdd(counters + 1, s);
         if (DETAIL) { atomicAdd(counters + 2, nn); atomicAdd(counters + 3, nt); atomicAdd(counters + 4, ns); atomicAdd(counters + 5, nh); }
     }
 }
 
-cudaError_t launch_trace(const SceneDev& sc, const CameraDev& cam, const LaunchParams& lp, float4* accum,
-                         uint32_t* primary_ids, unsigned long long* counters, bool brute, bool detail,
-                         cudaStream_t stream)
+// The store of wgsl:59-66 for the fused dispatches, in dispatch order: one thread per pixel,
+// running mean kept in registers, planes read coalesced. HBM-bound: 16 B per pixel per
+// dispatch in, 16 B per pixel (+16 B when blending into an existing image) per launch.
+__global__ void blend_kernel(LaunchParams lp, const float4* __restrict__ staging, float4* __restrict__ accum)
 {
-    if (lp.n_tiles_local == 0 || lp.n_frames == 0) return cudaSuccess;
-    const uint32_t tiles_per_block = RT_BLOCK_THREADS / 64;
-    dim3 grid((lp.n_tiles_local + tiles_per_block - 1) / tiles_per_block), block(RT_BLOCK_THREADS);
-    if (brute) {
-        if (detail) trace_kernel<true, true><<<grid, block, 0, stream>>>(sc, cam, lp, accum, primary_ids, counters);
-        else trace_kernel<true, false><<<grid, block, 0, stream>>>(sc, cam, lp, accum, primary_ids, counters);
-    } else {
-        if (detail) trace_kernel<false, true><<<grid, block, 0, stream>>>(sc, cam, lp, accum, primary_ids, counters);
-        else trace_kernel<false, false><<<grid, block, 0, stream>>>(sc, cam, lp, accum, primary_ids, counters);
+    const size_t plane = (size_t)lp.width * lp.height;
+    // thread -> pixel of this rank's 8x8 tiles, row-major inside the tile
+    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t n_local = (size_t)lp.n_warp_tiles * 32u;
+    if (idx >= n_local) return;
+    const uint32_t lt = (uint32_t)(idx >> 6), in_tile = (uint32_t)(idx & 63u);
+    const uint32_t t = lt * lp.tile_world + lp.tile_rank;
+    const uint32_t px = (t % lp.tiles_x) * 8u + (in_tile & 7u), py = (t / lp.tiles_x) * 8u + (in_tile >> 3);
+    if (px >= lp.width || py >= lp.height) return;
+    const size_t pix = (size_t)py * lp.width + px;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    bool loaded = false;
+    for (uint32_t fi = 0; fi < lp.n_frames; fi++) {
+        const int32_t frames = lp.first_frame + (int32_t)(fi * lp.frame_world);
+        const int32_t blend = (frames >= 0) ? (int32_t)((uint32_t)frames / lp.frame_world) : frames;
+        const float4 fr = staging[(size_t)fi * plane + pix];
+        if (blend >= 1) {                                                   // wgsl:59-63
+            if (!loaded) { acc = accum[pix]; loaded = true; }
+            float weight = 1.0f / (float)(blend + 1);
+            float om = 1.0f - weight;
+            acc = make_float4(acc.x * om + fr.x * weight, acc.y * om + fr.y * weight,
+                              acc.z * om + fr.z * weight, acc.w * om + fr.w * weight);
+        } else {                                                            // wgsl:64-66
+            acc = fr; loaded = true;
+        }
     }
+    accum[pix] = acc;
+}
+
+int trace_blocks_per_sm(bool brute, bool detail)
+{
+    int n = 0;
+    cudaError_t e;
+    if (brute) e = detail ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, trace_kernel<true, true>, RT_BLOCK_THREADS, 0)
+                          : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, trace_kernel<true, false>, RT_BLOCK_THREADS, 0);
+    else e = detail ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, trace_kernel<false, true>, RT_BLOCK_THREADS, 0)
+                    : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, trace_kernel<false, false>, RT_BLOCK_THREADS, 0);
+    return (e == cudaSuccess && n > 0) ? n : 1;
+}
+
+cudaError_t launch_trace(const SceneDev& sc, const CameraDev& cam, const LaunchParams& lp, float4* staging, float4* accum,
+                         uint32_t* primary_ids, unsigned long long* counters, unsigned long long* queue,
+                         bool brute, bool detail, int n_sms, cudaStream_t stream)
+{
+    if (lp.n_warp_tiles == 0 || lp.n_frames == 0) return cudaSuccess;
+    cudaError_t e = cudaMemsetAsync(queue, 0, sizeof(unsigned long long), stream);
+    if (e != cudaSuccess) return e;
+    const uint64_t warps_needed = ((uint64_t)lp.n_warp_tiles * lp.n_frames * 32ull + RT_QUEUE_CHUNK - 1) / RT_QUEUE_CHUNK;
+    uint64_t blocks = (uint64_t)n_sms * trace_blocks_per_sm(brute, detail);
+    const uint64_t cap = (warps_needed + RT_BLOCK_THREADS / 32 - 1) / (RT_BLOCK_THREADS / 32);
+    if (blocks > cap) blocks = cap;
+    dim3 grid((unsigned)blocks), block(RT_BLOCK_THREADS);
+    if (brute) {
+        if (detail) trace_kernel<true, true><<<grid, block, 0, stream>>>(sc, cam, lp, staging, primary_ids, counters, queue);
+        else trace_kernel<true, false><<<grid, block, 0, stream>>>(sc, cam, lp, staging, primary_ids, counters, queue);
+    } else {
+        if (detail) trace_kernel<false, true><<<grid, block, 0, stream>>>(sc, cam, lp, staging, primary_ids, counters, queue);
+        else trace_kernel<false, false><<<grid, block, 0, stream>>>(sc, cam, lp, staging, primary_ids, counters, queue);
+    }
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    const size_t n_local = (size_t)lp.n_warp_tiles * 32u;
+    blend_kernel<<<(unsigned)((n_local + 255) / 256), 256, 0, stream>>>(lp, staging, accum);
     return cudaGetLastError();
 }
 
