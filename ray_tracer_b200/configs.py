@@ -114,11 +114,11 @@ def build(name, width=None, height=None):
         scene = Scene(cam, light, vs, ix, ms)
     elif name == "c3_teapot":
         vs, ix, ms = load_fixture("teapot")            # 2 meshes at x = 0 and x = 3, raw (Z-up, +-82 unit) coordinates
-        cam = Camera((120.0, -120.0, 90.0), (5.0, 0.0, 35.0), (0, 0, 1), 45.0, aspect, 0.1, 100.0, 0.0, 1.0)
+        cam = Camera((40.0, -130.0, 75.0), (5.0, 0.0, 38.0), (0, 0, 1), 45.0, aspect, 0.1, 100.0, 0.0, 1.0)
         scene = Scene(cam, no_sph, vs, ix, ms)
     elif name == "c4_tree":
         vs, ix, ms = load_fixture("tree")              # 11 meshes at x = 0,3,...,30; node transforms ignored (resource.rs:228)
-        cam = Camera((15.0, 2.0, 26.0), (15.0, 0.8, 0.5), (0, 1, 0), 45.0, aspect, 0.1, 100.0, 0.0, 1.0)
+        cam = Camera((-3.0, 2.0, 3.0), (8.0, 1.0, 0.0), (0, 1, 0), 45.0, aspect, 0.1, 100.0, 0.0, 1.0)
         scene = Scene(cam, no_sph, vs, ix, ms)
     elif name == "c5_stress":
         vs, ix, base = load_fixture("teapot")
