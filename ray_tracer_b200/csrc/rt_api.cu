@@ -34,6 +34,7 @@ struct rt_ctx {
     uint32_t staging_frames = 0;
     int n_sms = 148;
     int64_t opt_staging_bytes = 2ll << 30;
+    int64_t opt_sched = 8 | (1 << 8) | (22 << 16);     // node loop runs while >= 8 lanes can step; shade once >= 22 lanes wait (swept on C3/C5)
     rt::SceneBuffers scene;
     bool has_scene = false, has_camera = false, has_params = false;
     rt_params params{};
@@ -138,6 +139,7 @@ int launch(rt_ctx* c, int32_t first_frame, uint32_t n_frames, bool want_ids)
     const uint32_t tiles = lp.tiles_x * ((c->height + 7) / 8);
     lp.n_warp_tiles = 2u * (tiles > c->tile_rank ? (tiles - c->tile_rank + c->tile_world - 1) / c->tile_world : 0);
     lp.seed_mode = (int32_t)c->opt_seed_mode;
+    lp.sched_n_stay = (int32_t)(c->opt_sched & 0xff); if (lp.sched_n_stay < 1) lp.sched_n_stay = 1; lp.sched_l_stay = (int32_t)((c->opt_sched >> 8) & 0xff); lp.sched_s_min = (int32_t)((c->opt_sched >> 16) & 0xff);
 
     { int rc = ensure_staging(c, n_frames); if (rc != RT_OK) return rc; }
     std::pair<cudaEvent_t, cudaEvent_t> ev;
@@ -358,6 +360,7 @@ int rt_set_option(rt_ctx* c, int option, int64_t value)
     case RT_OPT_DETAIL_COUNTERS: c->opt_detail = value != 0; return RT_OK;
     case RT_OPT_FRAMES_PER_LAUNCH: if (value < 1 || value > (1 << 20)) break; c->opt_frames_per_launch = value; return RT_OK;
     case RT_OPT_LEAF_SIZE: if (value < 1 || value > 8) break; c->opt_leaf_size = value; return RT_OK;
+    case RT_OPT_SCHED: c->opt_sched = value & 0xffffff; return RT_OK;
     default: return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_set_option: unknown option");
     }
     return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_set_option: value out of range");
@@ -373,6 +376,7 @@ int rt_get_option(const rt_ctx* c, int option, int64_t* value)
     case RT_OPT_DETAIL_COUNTERS: *value = c->opt_detail; return RT_OK;
     case RT_OPT_FRAMES_PER_LAUNCH: *value = c->opt_frames_per_launch; return RT_OK;
     case RT_OPT_LEAF_SIZE: *value = c->opt_leaf_size; return RT_OK;
+    case RT_OPT_SCHED: *value = c->opt_sched; return RT_OK;
     default: return RT_ERR_INVALID_ARGUMENT;
     }
 }

@@ -51,6 +51,7 @@ struct LaunchParams {
     uint32_t frame_world;      // stride between frames rendered by this rank
     uint32_t tiles_x, n_warp_tiles;  // 8x8 shard tiles per row; 8x4 warp tiles owned by this rank (2 per shard tile)
     int32_t seed_mode;
+    int32_t sched_n_stay, sched_l_stay, sched_s_min;   // warp scheduler thresholds (lanes)
 };
 
 // ---- vector helpers (the fused forms are the arithmetic contract's) -----

@@ -6,6 +6,10 @@
 #include "../../include/rt_b200.h"
 
 #define RT_BLOCK_THREADS 128
+#ifndef RT_SMEM_STACK
+#define RT_SMEM_STACK 0
+#endif
+#define RT_STACK 64                 // traversal stack entries per lane (BVH depth limit checked at upload)
 
 namespace rt {
 
