@@ -158,7 +158,7 @@ def run_ours(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
     import ray_tracer_b200 as rt
-    from ray_tracer_b200 import configs, _lib
+    from ray_tracer_b200 import configs, _lib, sharding
     import ctypes as C
 
     if not torch.cuda.is_available():
@@ -182,15 +182,13 @@ def run_ours(args, rank, world, local_rank):
     stream = torch.cuda.ExternalStream(tr.cuda_stream, device=dev)
     accum_t = torch.as_tensor(_DevArray(tr.accum_device_ptr, (H, W, 4)), device="cuda:%d" % dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda:%d" % dev)
-    inv_world = 1.0 / world
 
     def step():
         tr.render_frames(0, D * world)           # this rank renders D of the D*world frames
         if world > 1:
             cur = torch.cuda.current_stream()
             cur.wait_stream(stream)
-            dist.all_reduce(accum_t)             # combine the per-GPU running means over NVLink
-            accum_t.mul_(inv_world)
+            sharding.combine_sample_shards(accum_t, D, D * world)   # NCCL all-reduce of the per-GPU running means over NVLink
             stream.wait_stream(cur)
 
     def barrier():

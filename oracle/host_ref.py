@@ -16,6 +16,16 @@ from .rt_oracle import CAMERA_DT, MESH_DT, SPHERE_DT, VERTEX_DT
 
 f32 = np.float32
 
+# Rust's f32::tan lowers to the platform libm's tanf (glibc here), which is faithfully but
+# not always correctly rounded — call the same routine so the uniform is bit-identical.
+import ctypes as _C
+_libm = _C.CDLL("libm.so.6")
+_libm.tanf.argtypes, _libm.tanf.restype = [_C.c_float], _C.c_float
+
+
+def _tanf(x):
+    return f32(_libm.tanf(_C.c_float(float(x))))
+
 
 def _v(a):
     return np.asarray(a, dtype=np.float32)
@@ -40,7 +50,7 @@ def camera_to_uniform(origin, look_at, view_up, fov, aspect, near, far, aperture
     origin, look_at, view_up = _v(origin), _v(look_at), _v(view_up)
     fov, aspect, focus_dist, aperture = f32(fov), f32(aspect), f32(focus_dist), f32(aperture)
     theta = f32(fov * f32(f32(math.pi) / f32(180.0)))
-    height = f32(f32(2.0) * f32(math.tan(float(f32(theta / f32(2.0))))))
+    height = f32(f32(2.0) * _tanf(f32(theta / f32(2.0))))
     width = f32(aspect * height)
     w = _normalize(origin - look_at)
     u = _normalize(_cross(view_up, w))

@@ -1,0 +1,56 @@
+"""Freezes small oracle renders as golden vectors:  python tests/golden/make_oracle_goldens.py
+
+The reference cannot be run (no Rust / WGSL / graphics stack), so these are outputs of the
+CPU oracle itself; they pin the oracle against compiler / flag / host-CPU drift and give the
+GPU tests a fixture that does not depend on the oracle being built on the box.
+"""
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(HERE, "..", ".."))
+
+# name -> (scene kind, w, h, frames, bounces, rpp, skybox, first_frame)
+CASES = {
+    "balls": ("builtin", 32, 32, 2, 3, 1, 1, 0),
+    "balls_nosky_startup": ("builtin:balls", 24, 24, 2, 4, 1, 0, 1),
+    "room": ("builtin", 32, 24, 2, 4, 1, 0, 0),
+    "metal": ("builtin", 32, 24, 2, 6, 2, 1, 0),
+    "random_balls": ("builtin", 24, 16, 1, 4, 1, 1, 0),
+    "c2_cube": ("config", 32, 18, 1, 8, 1, 1, 0),
+    "c3_teapot": ("config", 32, 18, 1, 8, 1, 1, 0),
+    "c4_tree": ("config", 32, 18, 1, 8, 1, 1, 0),
+}
+
+
+def scene_for(name, kind, w, h):
+    from oracle import host_ref as hr, rt_oracle as ro
+    if kind.startswith("builtin"):
+        fn = kind.split(":")[1] if ":" in kind else name
+        return getattr(hr, "scene_" + fn)(np.float32(w) / np.float32(h))
+    from ray_tracer_b200 import configs
+    t = configs.build(name, w, h)[0].as_tuple()
+    return (t[0].view(ro.CAMERA_DT), t[1].view(ro.SPHERE_DT), t[2].view(ro.VERTEX_DT), t[3], t[4].view(ro.MESH_DT))
+
+
+def render_case(name):
+    from oracle import rt_oracle as ro
+    kind, w, h, frames, bounces, rpp, sky, first = CASES[name]
+    ids = np.full((h, w), 0xFFFFFFFF, np.uint32)
+    ctr = np.zeros(3, np.uint64)
+    img = ro.render(scene_for(name, kind, w, h), w, h, frames, bounces, rpp, sky, first, ids, ctr)
+    return img, ids, int(ctr[0])
+
+
+if __name__ == "__main__":
+    out = {}
+    for name in CASES:
+        img, ids, rays = render_case(name)
+        out[name + "/image_bits"] = img.view(np.uint32)
+        out[name + "/ids"] = ids
+        out[name + "/rays"] = np.array([rays], np.uint64)
+        print(name, img.shape, "rays", rays, "hit pixels", int((ids != 0xFFFFFFFF).sum()))
+    np.savez_compressed(os.path.join(HERE, "oracle_goldens.npz"), **out)
+    print("wrote", os.path.getsize(os.path.join(HERE, "oracle_goldens.npz")), "bytes")
