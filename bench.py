@@ -109,11 +109,15 @@ def cpu_sample(scene, params, first_frame, n_dispatches, stride):
     from oracle import rt_oracle as ro
     sc = oracle_scene(scene)
     ctr = np.zeros(3, np.uint64)
+    try:
+        threads = len(os.sched_getaffinity(0))      # all host cores, even when torchrun exports OMP_NUM_THREADS=1
+    except AttributeError:
+        threads = os.cpu_count() or 1
     t0 = time.perf_counter()
     ro.render(sc, params["width"], params["height"], n_dispatches, params["number_of_bounces"],
-              params["rays_per_pixel"], params["skybox"], first_frame, None, ctr, stride, stride, 0)
+              params["rays_per_pixel"], params["skybox"], first_frame, None, ctr, stride, stride, threads)
     dt = time.perf_counter() - t0
-    return float(ctr[0]) / dt / 1e6, int(ctr[0]), dt, ro.max_threads()
+    return float(ctr[0]) / dt / 1e6, int(ctr[0]), dt, threads
 
 
 def run_reference(args, rank, world):
