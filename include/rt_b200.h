@@ -115,8 +115,10 @@ enum {
     RT_OPT_PRIMARY_IDS = 3,      /* 1 = record the primary-hit AOV on the next render call */
     RT_OPT_DETAIL_COUNTERS = 4,  /* 1 = count node visits / primitive tests (slower kernel) */
     RT_OPT_FRAMES_PER_LAUNCH = 5,/* max reference dispatches fused into one kernel launch (default 64; 1 = one launch per dispatch like the reference) */
-    RT_OPT_LEAF_SIZE = 6,        /* max primitives per BVH leaf (1..8, default 4); takes effect at the next rt_upload_scene */
-    RT_OPT_SCHED = 7             /* tuning: warp scheduler thresholds in lanes, node_loop_min | (shade_min << 16); results do not depend on it */
+    RT_OPT_LEAF_SIZE = 6,        /* max primitives per BVH leaf (1..8, default 2); takes effect at the next rt_upload_scene */
+    RT_OPT_SCHED = 7,            /* tuning: warp scheduler thresholds in lanes, node_loop_min | (shade_min << 16); results do not depend on it */
+    RT_OPT_BUILDER = 8,          /* hierarchy over the Morton order: 0 = PLOC (default), 1 = radix tree (Karras 2012); takes effect at the next rt_upload_scene; results do not depend on it */
+    RT_OPT_PLOC_RADIUS = 9       /* PLOC search window, clusters to either side (1..16, default 3) */
 };
 
 typedef struct rt_ctx rt_ctx;

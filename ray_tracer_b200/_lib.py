@@ -11,7 +11,7 @@ import subprocess
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "librt_b200.so")
+LIB_PATH = os.environ.get("RT_B200_LIB") or os.path.join(_HERE, "librt_b200.so")   # override: tuning builds only
 CSRC = os.path.join(_HERE, "csrc")
 
 # record dtypes, byte-identical to include/rt_b200.h (and to the reference's #[repr(C)] structs)
@@ -47,6 +47,7 @@ class Counters(C.Structure):
 
 RT_OPT_TRAVERSAL, RT_OPT_SEED_MODE, RT_OPT_PRIMARY_IDS, RT_OPT_DETAIL_COUNTERS = 1, 2, 3, 4
 RT_OPT_FRAMES_PER_LAUNCH, RT_OPT_LEAF_SIZE, RT_OPT_SCHED = 5, 6, 7
+RT_OPT_BUILDER, RT_OPT_PLOC_RADIUS = 8, 9
 RT_OK, RT_ERR_INVALID_ARGUMENT, RT_ERR_CUDA, RT_ERR_NO_SCENE = 0, -1, -2, -3
 RT_ERR_OUT_OF_MEMORY, RT_ERR_BAD_INDEX, RT_ERR_UNSUPPORTED = -4, -5, -6
 MISS = 0xFFFFFFFF

@@ -40,7 +40,7 @@ struct rt_ctx {
     rt_params params{};
     rt_camera_uniform camera{};
     uint32_t tile_rank = 0, tile_world = 1, frame_rank = 0, frame_world = 1;
-    int64_t opt_traversal = 0, opt_seed_mode = 0, opt_primary_ids = 0, opt_detail = 0, opt_frames_per_launch = 64, opt_leaf_size = 4;
+    int64_t opt_traversal = 0, opt_seed_mode = 0, opt_primary_ids = 0, opt_detail = 0, opt_frames_per_launch = 64, opt_leaf_size = 2, opt_builder = 0, opt_ploc_radius = 3;
     uint64_t dispatches = 0, launches = 0;
     double kernel_ms = 0.0;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> pending, pool;
@@ -249,7 +249,7 @@ int rt_upload_scene(rt_ctx* c, const rt_sphere* spheres, uint32_t ns, const rt_v
     DeviceGuard g(c->device);
     CU(c, cudaStreamSynchronize(c->stream));
     uint32_t leaf = (uint32_t)(c->opt_leaf_size < 1 ? 1 : (c->opt_leaf_size > 8 ? 8 : c->opt_leaf_size));
-    cudaError_t e = rt::build_scene(c->scene, spheres, ns, vertices, nv, indices, ni, meshes, nm, leaf, c->stream);
+    cudaError_t e = rt::build_scene(c->scene, spheres, ns, vertices, nv, indices, ni, meshes, nm, leaf, (int)c->opt_builder, (int)c->opt_ploc_radius, c->stream);
     if (e != cudaSuccess) { c->has_scene = false; return cuda_fail(c, e, "scene build"); }
     if (c->scene.max_depth > 62) {
         c->has_scene = false; c->scene.release();
@@ -361,6 +361,8 @@ int rt_set_option(rt_ctx* c, int option, int64_t value)
     case RT_OPT_FRAMES_PER_LAUNCH: if (value < 1 || value > (1 << 20)) break; c->opt_frames_per_launch = value; return RT_OK;
     case RT_OPT_LEAF_SIZE: if (value < 1 || value > 8) break; c->opt_leaf_size = value; return RT_OK;
     case RT_OPT_SCHED: c->opt_sched = value & 0xffffff; return RT_OK;
+    case RT_OPT_BUILDER: if (value != 0 && value != 1) break; c->opt_builder = value; return RT_OK;
+    case RT_OPT_PLOC_RADIUS: if (value < 1 || value > 16) break; c->opt_ploc_radius = value; return RT_OK;
     default: return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_set_option: unknown option");
     }
     return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_set_option: value out of range");
@@ -377,6 +379,8 @@ int rt_get_option(const rt_ctx* c, int option, int64_t* value)
     case RT_OPT_FRAMES_PER_LAUNCH: *value = c->opt_frames_per_launch; return RT_OK;
     case RT_OPT_LEAF_SIZE: *value = c->opt_leaf_size; return RT_OK;
     case RT_OPT_SCHED: *value = c->opt_sched; return RT_OK;
+    case RT_OPT_BUILDER: *value = c->opt_builder; return RT_OK;
+    case RT_OPT_PLOC_RADIUS: *value = c->opt_ploc_radius; return RT_OK;
     default: return RT_ERR_INVALID_ARGUMENT;
     }
 }

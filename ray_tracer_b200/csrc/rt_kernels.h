@@ -6,6 +6,9 @@
 #include "../../include/rt_b200.h"
 
 #define RT_BLOCK_THREADS 128
+#ifndef RT_MIN_BLOCKS
+#define RT_MIN_BLOCKS 8            // resident blocks per SM the trace kernel is compiled for (64 registers per thread)
+#endif
 #ifndef RT_SMEM_STACK
 #define RT_SMEM_STACK 0
 #endif
@@ -29,6 +32,7 @@ struct SceneBuffers {
     float4* nodes = nullptr;
     uint32_t n_prims = 0, n_spheres = 0, n_tris = 0, n_mats = 0, n_nodes = 0, max_depth = 0;
     int32_t root = -1;
+    int builder = 0;               // hierarchy actually built: 0 = PLOC, 1 = radix tree
     float max_abs = 0.0f;
     void release();
 };
@@ -37,7 +41,7 @@ struct SceneBuffers {
 // validated). Synchronous with respect to `stream` on return.
 cudaError_t build_scene(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns, const rt_vertex* vertices,
                         uint32_t nv, const uint32_t* indices, uint32_t ni, const rt_mesh* meshes, uint32_t nm,
-                        uint32_t leaf_size, cudaStream_t stream);
+                        uint32_t leaf_size, int builder, int ploc_radius, cudaStream_t stream);
 
 cudaError_t launch_tonemap(const float4* accum, uint8_t* rgba8, size_t n_pixels, cudaStream_t stream);
 

@@ -178,7 +178,7 @@ __device__ __forceinline__ void shade_hit(const SceneDev& sc, const HitRec& hit,
 #define RT_EMPTY 0x7fffffff                        // "no current node": traversal stack exhausted
 
 template <bool BRUTE, bool DETAIL>
-__global__ void __launch_bounds__(RT_BLOCK_THREADS)
+__global__ void __launch_bounds__(RT_BLOCK_THREADS, RT_MIN_BLOCKS)
 trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ staging,
              uint32_t* __restrict__ primary_ids, unsigned long long* __restrict__ counters,
              unsigned long long* __restrict__ queue)

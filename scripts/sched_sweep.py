@@ -1,4 +1,4 @@
-"""Sweep the warp scheduler thresholds on one config: python scripts/sched_sweep.py c3_teapot 32"""
+"""Sweep the warp scheduler thresholds on one config: python scripts/sched_sweep.py c3_teapot 32 [combos "n,s;n,s"]"""
 import sys
 sys.path.insert(0, ".")
 import ray_tracer_b200 as rt
@@ -9,7 +9,9 @@ p = meta["params"]
 tr = rt.RayTracer(0, p["width"], p["height"])
 tr.upload_scene(*scene.arrays()); tr.set_camera(scene.camera_uniform()); tr.set_params(**p)
 tr.set_option(rt._lib.RT_OPT_FRAMES_PER_LAUNCH, frames)
-combos = [(n, 1, s) for n in (2, 4, 8, 12) for s in (20, 24, 28, 30, 32)]
+combos = [(n, 1, s) for n in (4, 8, 12, 16) for s in (16, 20, 22, 24, 28)]
+if len(sys.argv) > 3:
+    combos = [(int(c.split(",")[0]), 1, int(c.split(",")[1])) for c in sys.argv[3].split(";")]
 for n, l, s in combos:
     tr.set_option(rt._lib.RT_OPT_SCHED, n | (l << 8) | (s << 16))
     tr.render_frames(0, frames); tr.sync(); tr.reset_counters()

@@ -9,11 +9,15 @@ from util import assert_bits_equal
 pytestmark = pytest.mark.gpu
 
 
-def _gpu(rt, scene, w, h, frames, bounces, sky, brute=False, leaf=None):
+def _gpu(rt, scene, w, h, frames, bounces, sky, brute=False, leaf=None, builder=None, radius=None):
     cam, sp, vs, ix, ms = scene.as_tuple()
     tr = rt.RayTracer(0, w, h)
     if leaf is not None:
         tr.set_option(rt._lib.RT_OPT_LEAF_SIZE, leaf)
+    if builder is not None:
+        tr.set_option(rt._lib.RT_OPT_BUILDER, builder)
+    if radius is not None:
+        tr.set_option(rt._lib.RT_OPT_PLOC_RADIUS, radius)
     tr.upload_scene(sp, vs, ix, ms)
     tr.set_camera(cam)
     tr.set_params(number_of_bounces=bounces, rays_per_pixel=1, skybox=sky, frames=0)
@@ -66,6 +70,36 @@ def test_leaf_size_is_result_invisible(rtlib, leaf):
     b, bid, bc, _ = _gpu(rtlib, scene, 192, 108, 2, 8, 1, leaf=leaf)
     assert np.array_equal(aid, bid) and ac["rays"] == bc["rays"]
     assert_bits_equal(a, b, "leaf size %d" % leaf)
+
+
+@pytest.mark.parametrize("builder,radius", [(1, None), (0, 1), (0, 4), (0, 16)])
+def test_builder_is_result_invisible(rtlib, builder, radius):
+    """PLOC (any window) and the radix tree give the same image, ids and ray count."""
+    from ray_tracer_b200 import configs
+    for name in ("c3_teapot", "c4_tree"):
+        scene, meta = configs.build(name, 192, 108)
+        a, aid, ac, sa = _gpu(rtlib, scene, 192, 108, 2, 8, 1)
+        b, bid, bc, sb = _gpu(rtlib, scene, 192, 108, 2, 8, 1, builder=builder, radius=radius)
+        assert sa["n_prims"] == sb["n_prims"] and sa["n_nodes"] == sb["n_nodes"]
+        assert np.array_equal(aid, bid) and ac["rays"] == bc["rays"]
+        assert_bits_equal(a, b, "%s builder %d radius %s" % (name, builder, radius))
+
+
+def test_degenerate_scenes_build(rtlib, oracle):
+    """Identical and coincident primitives (all union areas tie): the build terminates, stays
+    within the traversal stack, and the tie rule still picks the first primitive."""
+    from ray_tracer_b200 import host
+    scene = host.Scene.balls(np.float32(1.0))
+    cam, sp, vs, ix, ms = scene.as_tuple()
+    sp = np.repeat(sp[:1], 3000)                       # 3000 copies of one sphere
+    scene2 = host.Scene(scene.camera, sp, vs, ix, ms)
+    a, aid, ac, st = _gpu(rtlib, scene2, 64, 64, 1, 2, 1)
+    assert st["n_prims"] == 3000 and st["max_depth"] <= 62
+    hit = aid != 0xFFFFFFFF
+    assert hit.any() and (aid[hit] == 0).all()
+    b, bid, bc, _ = _gpu(rtlib, scene2, 64, 64, 1, 2, 1, brute=True)
+    assert np.array_equal(aid, bid) and ac["rays"] == bc["rays"]
+    assert_bits_equal(a, b, "identical spheres")
 
 
 def test_stress_scene_builds_and_matches_brute_force_on_a_crop(rtlib):
