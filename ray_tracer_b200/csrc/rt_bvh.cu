@@ -343,6 +343,16 @@ __global__ void identity_slots(uint32_t n, uint32_t* new_slot)
     if (k < n) new_slot[k] = k;
 }
 
+// Boxes are emitted as centre / half extent (the traversal's slab test is then select-free).
+// The half extent is rounded outward so that [c - h, c + h] contains [lo, hi].
+__device__ __forceinline__ float3 box_centre(float4 lo, float4 hi) { return f3(0.5f * lo.x + 0.5f * hi.x, 0.5f * lo.y + 0.5f * hi.y, 0.5f * lo.z + 0.5f * hi.z); }
+__device__ __forceinline__ float half_up(float lo, float hi, float c)
+{
+    float h = fmaxf(hi - c, c - lo);
+    return __fmaf_ru(h, 1.1920929e-07f, h);          // one ulp-scale step outward covers the rounding of the two differences
+}
+__device__ __forceinline__ float3 box_half(float4 lo, float4 hi, float3 c) { return f3(half_up(lo.x, hi.x, c.x), half_up(lo.y, hi.y, c.y), half_up(lo.z, hi.z, c.z)); }
+
 // child link of an emitted node: inner index, or leaf ~((first_slot << 3) | (count - 1))
 __device__ __forceinline__ int encode_child(int c, const int2* ranges, const uint32_t* new_slot, int leaf_size)
 {
@@ -363,19 +373,20 @@ __global__ void emit_nodes(int n_inner, const int2* children, const int2* ranges
     float4 alo = ch.x >= 0 ? imin[ch.x] : lmin[~ch.x], ahi = ch.x >= 0 ? imax[ch.x] : lmax[~ch.x];
     float4 blo = ch.y >= 0 ? imin[ch.y] : lmin[~ch.y], bhi = ch.y >= 0 ? imax[ch.y] : lmax[~ch.y];
     int el = encode_child(ch.x, ranges, new_slot, leaf_size), er = encode_child(ch.y, ranges, new_slot, leaf_size);
-    nodes[4 * (size_t)i + 0] = make_float4(alo.x, alo.y, alo.z, ahi.x);
-    nodes[4 * (size_t)i + 1] = make_float4(ahi.y, ahi.z, blo.x, blo.y);
-    nodes[4 * (size_t)i + 2] = make_float4(blo.z, bhi.x, bhi.y, bhi.z);
+    const float3 ac = box_centre(alo, ahi), ah = box_half(alo, ahi, ac), bc = box_centre(blo, bhi), bh = box_half(blo, bhi, bc);
+    nodes[4 * (size_t)i + 0] = make_float4(ac.x, ac.y, ac.z, ah.x);
+    nodes[4 * (size_t)i + 1] = make_float4(ah.y, ah.z, bc.x, bc.y);
+    nodes[4 * (size_t)i + 2] = make_float4(bc.z, bh.x, bh.y, bh.z);
     nodes[4 * (size_t)i + 3] = make_float4(__int_as_float(el), __int_as_float(er), 0.f, 0.f);
 }
 
 __global__ void emit_single(const float4* lmin, const float4* lmax, float4* nodes)
 {
     float4 lo = lmin[0], hi = lmax[0];
-    const float big = 3.0e38f;
-    nodes[0] = make_float4(lo.x, lo.y, lo.z, hi.x);
-    nodes[1] = make_float4(hi.y, hi.z, big, big);
-    nodes[2] = make_float4(big, -big, -big, -big);
+    const float3 c = box_centre(lo, hi), h = box_half(lo, hi, c);
+    nodes[0] = make_float4(c.x, c.y, c.z, h.x);
+    nodes[1] = make_float4(h.y, h.z, 0.f, 0.f);
+    nodes[2] = make_float4(0.f, -INFINITY, -INFINITY, -INFINITY);     // right child: empty box (never hit)
     nodes[3] = make_float4(__int_as_float(~0), __int_as_float(~0), 0.f, 0.f);
 }
 

@@ -15,8 +15,9 @@
 //  materials, indexed by material index (sphere i -> i, mesh m -> S + m):
 //    m0 = color, m1 = emission_color * emission_strength, m2.x = smoothness
 //  BVH nodes, 64 B each (both children's boxes live in the parent, one fetch = two tests):
-//    n[4*i+0] = (L.min.xyz, L.max.x)  n[4*i+1] = (L.max.yz, R.min.xy)
-//    n[4*i+2] = (R.min.z, R.max.xyz)  n[4*i+3] = (left, right, 0, 0) as int bits
+//    boxes as centre c / half extent h (rounded outward), which makes the slab test select-free:
+//    n[4*i+0] = (L.c.xyz, L.h.x)  n[4*i+1] = (L.h.yz, R.c.xy)
+//    n[4*i+2] = (R.c.z, R.h.xyz)  n[4*i+3] = (left, right, 0, 0) as int bits
 //    child >= 0: inner node index; child < 0: leaf, ~child = (first_slot << 3) | (count - 1)
 #pragma once
 #include <cuda_runtime.h>

@@ -22,140 +22,9 @@
 // Build: -fmad=false (no implicit contraction), IEEE div/sqrt, no fast-math.
 #include "rt_device.cuh"
 #include "rt_kernels.h"
+#include "rt_shade.cuh"
 
 namespace rt {
-
-#define RT_MISS 0xFFFFFFFFu
-#define RT_FLT_MAX 3.40282346638528859812e+38f
-
-struct HitRec {
-    float dst, u, v;
-    uint32_t id;
-};
-
-// wgsl:106-123 on slot data. Updates `best` under the tie rule of wgsl:154 (strict '<' in
-// the reference's scan order == smaller id wins on equal distance).
-__device__ __forceinline__ void test_sphere(float3 o, float3 d, float4 q0, float4 q1, uint32_t id, HitRec& best)
-{
-    float3 oc = o - xyz(q0);
-    float a = dot3(d, d);
-    float b = 2.0f * dot3(oc, d);
-    float c = dot3(oc, oc) - q1.y;                       // q1.y = radius*radius
-    float disc = __fmaf_rn(b, b, -((4.0f * a) * c));
-    if (disc >= 0.0f) {
-        float dst = (-b - sqrtf(disc)) / (2.0f * a);
-        if (dst >= 0.0f && (dst < best.dst || (dst == best.dst && id < best.id && dst != RT_FLT_MAX))) {
-            best.dst = dst; best.id = id;
-        }
-    }
-}
-
-// wgsl:125-147 on slot data (A pre-translated, e1 = B-A, e2 = C-A).
-__device__ __forceinline__ void test_triangle(float3 o, float3 d, float4 q0, float4 q1, float4 q2, uint32_t id, HitRec& best)
-{
-    float3 e1 = f3(q1.x, q1.y, q1.z);
-    float3 e2 = f3(q1.w, q2.x, q2.y);
-    float3 n = cross3(e1, e2);
-    float det = -dot3(d, n);
-    if (!(det >= 1e-6f)) return;
-    float3 ao = o - xyz(q0);
-    float3 dao = cross3(ao, d);
-    float inv = 1.0f / det;
-    float dst = dot3(ao, n) * inv;
-    float u = dot3(e2, dao) * inv;
-    float v = -(dot3(e1, dao) * inv);
-    float w = (1.0f - u) - v;
-    if (dst >= 0.0f && u >= 0.0f && v >= 0.0f && w >= 0.0f &&
-        (dst < best.dst || (dst == best.dst && id < best.id && dst != RT_FLT_MAX))) {
-        best.dst = dst; best.u = u; best.v = v; best.id = id;
-    }
-}
-
-// wgsl:284-288
-__device__ __forceinline__ float reflectance(float cosine, float ratio)
-{
-    float r0 = (1.0f - ratio) / (1.0f + ratio);
-    r0 = r0 * r0;
-    float x = 1.0f - cosine;
-    float x2 = x * x;
-    return r0 + (1.0f - r0) * ((x2 * x2) * x);
-}
-// wgsl:290-295 (length, not length squared — kept)
-__device__ __forceinline__ float3 refract3(float3 uv, float3 n, float ratio)
-{
-    float cos_theta = fminf(dot3(-uv, n), 1.0f);
-    float3 perp = fma3(n, cos_theta, uv) * ratio;
-    float k = -sqrtf(fabsf(1.0f - length3(perp)));
-    return fma3(n, k, perp);
-}
-// wgsl:199-203
-__device__ __forceinline__ float rand_normal_dist(uint32_t& rng)
-{
-    float theta = 6.2831852f * rand01(rng);
-    float rho = sqrtf(-2.0f * spec_logf(rand01(rng)));
-    return rho * spec_cosf(theta);
-}
-// wgsl:297-304
-__device__ __forceinline__ float4 environment_light(float3 d)
-{
-    float sky_t = spec_powf(smoothstep1(0.0f, 0.4f, d.y), 0.35f);
-    float g2s = smoothstep1(-0.01f, 0.0f, d.y);
-    float sun = spec_powf(fmaxf(0.0f, dot3(d, f3(0.1f, 1.0f, 0.1f))), 500.0f) * 0.1f;
-    float s = sun * ((g2s >= 1.0f) ? 1.0f : 0.0f);
-    float4 sky = make_float4(mix1(1.0f, 0.0788092f, sky_t), mix1(1.0f, 0.36480793f, sky_t), mix1(1.0f, 0.7264151f, sky_t), mix1(0.0f, 0.0f, sky_t));
-    return make_float4(mix1(0.35f, sky.x, g2s) + s, mix1(0.3f, sky.y, g2s) + s, mix1(0.35f, sky.z, g2s) + s, mix1(0.0f, sky.w, g2s) + s);
-}
-
-// wgsl:307-308; strict mode saturates the f32->u32 conversion (WGSL rule)
-__device__ __forceinline__ uint32_t pixel_seed(uint32_t x, uint32_t y, uint32_t w, uint32_t h, int32_t frames)
-{
-    float px = (float)x * (float)w;
-    float py = (float)y * (float)h;
-    float lin = py * (float)w + px;
-    uint32_t af = (frames < 0) ? (0u - (uint32_t)frames) : (uint32_t)frames;
-    return __float2uint_rz(lin) + af * 71939u;
-}
-
-// One path segment's shading (wgsl:236-273). Consumes RNG exactly as the reference does and
-// replaces the ray by the bounce ray.
-__device__ __forceinline__ void shade_hit(const SceneDev& sc, const HitRec& hit, float3& ro, float3& rd, uint32_t& rng,
-                                          float4& incoming, float4& color)
-{
-    float3 hp = fma3(rd, hit.dst, ro);
-    float4 k0 = __ldg(sc.c0 + hit.id);
-    float3 normal;
-    if (hit.id < sc.n_spheres) {
-        normal = normalize3(hp - xyz(k0));
-    } else {
-        float4 k1 = __ldg(sc.c1 + hit.id), k2 = __ldg(sc.c2 + hit.id);
-        float w = (1.0f - hit.u) - hit.v;
-        normal = normalize3(fma3(xyz(k2), hit.v, fma3(xyz(k1), hit.u, xyz(k0) * w)));
-    }
-    const uint32_t mi = __float_as_uint(k0.w);
-    float4 mcolor = __ldg(sc.m0 + mi), emitted = __ldg(sc.m1 + mi);
-    const float smooth = __ldg(sc.m2 + mi).x;
-    float3 unit_dir = normalize3(rd);
-    float3 nd;
-    if (smooth == -1.0f) {                       // glass, wgsl:240-264
-        mcolor = make_float4(1.f, 1.f, 1.f, 1.f);
-        bool front_face = !(dot3(rd, normal) > 0.0f);
-        float ratio = front_face ? (1.0f / 1.5f) : 1.5f;
-        float cos_theta = fminf(dot3(-unit_dir, normal), 1.0f);
-        float sin_theta = sqrtf(1.0f - cos_theta * cos_theta);
-        bool cannot_refract = ratio * sin_theta > 1.0f;
-        if (cannot_refract || reflectance(cos_theta, ratio) > rand01(rng)) nd = reflect3(unit_dir, normal);
-        else nd = refract3(unit_dir, normal, ratio);
-    } else {                                     // wgsl:265-269
-        float gx = rand_normal_dist(rng), gy = rand_normal_dist(rng), gz = rand_normal_dist(rng);
-        float3 dir = normalize3(f3(gx, gy, gz));
-        float3 diffuse = dir * sign1(dot3(normal, dir));
-        float3 spec = reflect3(unit_dir, normal);
-        nd = f3(mix1(diffuse.x, spec.x, smooth), mix1(diffuse.y, spec.y, smooth), mix1(diffuse.z, spec.z, smooth));
-    }
-    ro = hp; rd = nd;
-    incoming = incoming + emitted * color;         // wgsl:271-272
-    color = color * mcolor;                        // wgsl:273
-}
 
 // ---- the trace kernel ---------------------------------------------------------------------
 // Work item = one (pixel, dispatch) pair: the rpp+1 camera paths of one pixel in one
@@ -198,11 +67,18 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
     bool shading = true;                           // lane is between rays (else: mid-traversal)
     bool idle = false;                             // no item and the queue is empty
     bool has_item = false, traced = false;         // traced: a finished traversal awaits shading
-    uint32_t pix = 0, fi = 0, rng = 0;
+    uint32_t rng = 0;
     int32_t j = 0, seg = 0;
-    float4 total = make_float4(0.f, 0.f, 0.f, 0.f), incoming = total, color = total;
+    float4 incoming = make_float4(0.f, 0.f, 0.f, 0.f), color = incoming;
     float3 ro = f3(0.f, 0.f, 0.f), rd = ro;        // current ray
-    float3 inv = ro, on = ro, of = ro;             // slab setup of the current ray
+    float3 inv = ro, noi = ro, ainv = ro, pi = ro; // slab setup of the current ray: 1/d, -o/d, |1/d|, pad*|1/d|
+    // item state touched once per camera path lives in shared memory (keeps the traversal loops at 64 registers)
+    __shared__ float4 s_total[RT_BLOCK_THREADS];   // sum of the item's finished paths (wgsl:323)
+    __shared__ uint2 s_item[RT_BLOCK_THREADS];     // (pixel index, dispatch index within the launch)
+    float4& total = s_total[threadIdx.x];
+    uint32_t& pix = s_item[threadIdx.x].x;
+    uint32_t& fi = s_item[threadIdx.x].y;
+    total = make_float4(0.f, 0.f, 0.f, 0.f); pix = 0; fi = 0;
     HitRec best; best.dst = RT_FLT_MAX; best.u = best.v = 0.f; best.id = RT_MISS;
     int node = RT_EMPTY, sp = 0;                   // current node (inner >= 0, leaf < 0, or RT_EMPTY) / stack height
     uint32_t leaf_first = 0, leaf_count = 0;       // parked leaf primitives
@@ -308,13 +184,14 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
                 } else if (sc.root < 0) {
                     traced = true;                                // empty scene: immediate miss
                 } else {
-                    // slab setup: t = plane*inv - (o*inv +/- pad*|inv|); not parity-relevant
+                    // slab setup for boxes stored as centre c / half extent h: along each axis the ray is
+                    // inside the padded slab for t in [a - b, a + b], a = (c - o)/d, b = (h + pad)/|d|.
+                    // Not parity-relevant (conservative culling only).
                     inv = f3(__fdividef(1.0f, rd.x), __fdividef(1.0f, rd.y), __fdividef(1.0f, rd.z));
                     const float pad = sc.pad_scale * fmaxf(fmaxf(sc.max_abs, fabsf(ro.x)), fmaxf(fabsf(ro.y), fabsf(ro.z)));
-                    const float3 oi = f3(ro.x * inv.x, ro.y * inv.y, ro.z * inv.z);
-                    const float3 pi = f3(pad * fabsf(inv.x), pad * fabsf(inv.y), pad * fabsf(inv.z));
-                    on = f3(-(oi.x + pi.x), -(oi.y + pi.y), -(oi.z + pi.z));   // near-plane offset
-                    of = f3(-(oi.x - pi.x), -(oi.y - pi.y), -(oi.z - pi.z));   // far-plane offset
+                    ainv = f3(fabsf(inv.x), fabsf(inv.y), fabsf(inv.z));
+                    noi = f3(-(ro.x * inv.x), -(ro.y * inv.y), -(ro.z * inv.z));
+                    pi = f3(pad * ainv.x, pad * ainv.y, pad * ainv.z);
                     node = sc.root;
                     traced = true; shading = false;
                 }
@@ -333,18 +210,18 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
                     const float4* np = sc.nodes + 4 * (size_t)node;
                     const float4 n0 = __ldg(np + 0), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3);
                     if (DETAIL) n_nodes++;
-                    const bool sx = inv.x >= 0.0f, sy = inv.y >= 0.0f, sz = inv.z >= 0.0f;
-                    // left box: min (n0.x,n0.y,n0.z) max (n0.w,n1.x,n1.y); right: min (n1.z,n1.w,n2.x) max (n2.y,n2.z,n2.w)
-                    const float lnx = sx ? n0.x : n0.w, lfx = sx ? n0.w : n0.x;
-                    const float lny = sy ? n0.y : n1.x, lfy = sy ? n1.x : n0.y;
-                    const float lnz = sz ? n0.z : n1.y, lfz = sz ? n1.y : n0.z;
-                    const float rnx = sx ? n1.z : n2.y, rfx = sx ? n2.y : n1.z;
-                    const float rny = sy ? n1.w : n2.z, rfy = sy ? n2.z : n1.w;
-                    const float rnz = sz ? n2.x : n2.w, rfz = sz ? n2.w : n2.x;
-                    const float ltn = fmaxf(fmaxf(__fmaf_rn(lnx, inv.x, on.x), __fmaf_rn(lny, inv.y, on.y)), fmaxf(__fmaf_rn(lnz, inv.z, on.z), 0.0f));
-                    const float ltf = fminf(fminf(__fmaf_rn(lfx, inv.x, of.x), __fmaf_rn(lfy, inv.y, of.y)), fminf(__fmaf_rn(lfz, inv.z, of.z), best.dst));
-                    const float rtn = fmaxf(fmaxf(__fmaf_rn(rnx, inv.x, on.x), __fmaf_rn(rny, inv.y, on.y)), fmaxf(__fmaf_rn(rnz, inv.z, on.z), 0.0f));
-                    const float rtf = fminf(fminf(__fmaf_rn(rfx, inv.x, of.x), __fmaf_rn(rfy, inv.y, of.y)), fminf(__fmaf_rn(rfz, inv.z, of.z), best.dst));
+                    // left: centre (n0.x,n0.y,n0.z) half (n0.w,n1.x,n1.y); right: centre (n1.z,n1.w,n2.x) half (n2.y,n2.z,n2.w).
+                    // 12 FFMA + 12 FADD on the fma pipe, 4 three-input min/max on the alu pipe (no sign selects).
+                    const float lax = __fmaf_rn(n0.x, inv.x, noi.x), lbx = __fmaf_rn(n0.w, ainv.x, pi.x);
+                    const float lay = __fmaf_rn(n0.y, inv.y, noi.y), lby = __fmaf_rn(n1.x, ainv.y, pi.y);
+                    const float laz = __fmaf_rn(n0.z, inv.z, noi.z), lbz = __fmaf_rn(n1.y, ainv.z, pi.z);
+                    const float rax = __fmaf_rn(n1.z, inv.x, noi.x), rbx = __fmaf_rn(n2.y, ainv.x, pi.x);
+                    const float ray_ = __fmaf_rn(n1.w, inv.y, noi.y), rby = __fmaf_rn(n2.z, ainv.y, pi.y);
+                    const float raz = __fmaf_rn(n2.x, inv.z, noi.z), rbz = __fmaf_rn(n2.w, ainv.z, pi.z);
+                    const float ltn = fmaxf(fmaxf(lax - lbx, lay - lby), fmaxf(laz - lbz, 0.0f));
+                    const float ltf = fminf(fminf(lax + lbx, lay + lby), fminf(laz + lbz, best.dst));
+                    const float rtn = fmaxf(fmaxf(rax - rbx, ray_ - rby), fmaxf(raz - rbz, 0.0f));
+                    const float rtf = fminf(fminf(rax + rbx, ray_ + rby), fminf(raz + rbz, best.dst));
                     const bool hl = ltn <= ltf, hr = rtn <= rtf;
                     const int cl = __float_as_int(n3.x), cr = __float_as_int(n3.y);
                     if (hl && hr) {
