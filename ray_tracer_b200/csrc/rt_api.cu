@@ -126,7 +126,7 @@ int launch(rt_ctx* c, int32_t first_frame, uint32_t n_frames, bool want_ids)
 {
     rt::SceneDev sd{};
     const rt::SceneBuffers& s = c->scene;
-    sd.g0 = s.g0; sd.g1 = s.g1; sd.g2 = s.g2; sd.c0 = s.c0; sd.c1 = s.c1; sd.c2 = s.c2;
+    sd.prims = s.prims; sd.c0 = s.c0; sd.c1 = s.c1; sd.c2 = s.c2;
     sd.m0 = s.m0; sd.m1 = s.m1; sd.m2 = s.m2; sd.nodes = s.nodes;
     sd.n_prims = s.n_prims; sd.n_spheres = s.n_spheres; sd.root = s.root;
     sd.max_abs = s.max_abs; sd.pad_scale = 1.52587890625e-05f;   // 2^-16

@@ -38,7 +38,7 @@ __device__ __forceinline__ int fenc(float f) { int i = __float_as_int(f); return
 __device__ __forceinline__ float fdec(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7fffffff); }
 
 // one thread per primitive id: hot/cold records in id order, exact bounds, scene bounds
-__global__ void setup_prims(RawScene rs, float4* h0, float4* h1, float4* h2, float4* c0, float4* c1, float4* c2,
+__global__ void setup_prims(RawScene rs, float4* hot /*4 per id*/, float4* c0, float4* c1, float4* c2,
                             float4* bmin, float4* bmax, int* scene_bounds /*[6] encoded*/)
 {
     uint32_t id = blockIdx.x * blockDim.x + threadIdx.x;
@@ -49,9 +49,9 @@ __global__ void setup_prims(RawScene rs, float4* h0, float4* h1, float4* h2, flo
             const rt_sphere& s = rs.spheres[id];
             float r = s.radius;
             float3 c = f3(s.position[0], s.position[1], s.position[2]);
-            h0[id] = make_float4(c.x, c.y, c.z, __uint_as_float(id));
-            h1[id] = make_float4(r, r * r, 0.f, 0.f);
-            h2[id] = make_float4(0.f, 0.f, 0.f, 0.f);
+            hot[4 * (size_t)id + 0] = make_float4(c.x, c.y, c.z, __uint_as_float(id));
+            hot[4 * (size_t)id + 1] = make_float4(r, r * r, 0.f, 0.f);
+            hot[4 * (size_t)id + 2] = hot[4 * (size_t)id + 3] = make_float4(0.f, 0.f, 0.f, 0.f);
             c0[id] = make_float4(c.x, c.y, c.z, __uint_as_float(id));
             c1[id] = c2[id] = make_float4(0.f, 0.f, 0.f, 0.f);
             float ar = fabsf(r);
@@ -70,9 +70,11 @@ __global__ void setup_prims(RawScene rs, float4* h0, float4* h1, float4* h2, flo
             float3 B = f3(vb.pos[0], vb.pos[1], vb.pos[2]) + mp;
             float3 C = f3(vc.pos[0], vc.pos[1], vc.pos[2]) + mp;
             float3 e1 = B - A, e2 = C - A;                              // wgsl:127-128
-            h0[id] = make_float4(A.x, A.y, A.z, __uint_as_float(id));
-            h1[id] = make_float4(e1.x, e1.y, e1.z, e2.x);
-            h2[id] = make_float4(e2.y, e2.z, 0.f, 0.f);
+            float3 nrm = cross3(e1, e2);                                // wgsl:129
+            hot[4 * (size_t)id + 0] = make_float4(nrm.x, nrm.y, nrm.z, __uint_as_float(id));
+            hot[4 * (size_t)id + 1] = make_float4(A.x, A.y, A.z, e1.x);
+            hot[4 * (size_t)id + 2] = make_float4(e1.y, e1.z, e2.x, e2.y);
+            hot[4 * (size_t)id + 3] = make_float4(e2.z, 0.f, 0.f, 0.f);
             c0[id] = make_float4(va.normal[0], va.normal[1], va.normal[2], __uint_as_float(rs.ns + a));
             c1[id] = make_float4(vb.normal[0], vb.normal[1], vb.normal[2], 0.f);
             c2[id] = make_float4(vc.normal[0], vc.normal[1], vc.normal[2], 0.f);
@@ -145,13 +147,13 @@ __global__ void gather_boxes(uint32_t n, const uint32_t* sorted_ids, const float
 }
 
 // hot records into their final slots (Morton slot k -> new_slot[k])
-__global__ void gather_slots(uint32_t n, const uint32_t* sorted_ids, const uint32_t* new_slot, const float4* h0, const float4* h1, const float4* h2,
-                             float4* g0, float4* g1, float4* g2)
+__global__ void gather_slots(uint32_t n, const uint32_t* sorted_ids, const uint32_t* new_slot, const float4* hot, float4* prims)
 {
-    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;     // one thread per float4 of a record
+    uint32_t k = t >> 2, q = t & 3u;
     if (k >= n) return;
     uint32_t id = sorted_ids[k], s = new_slot[k];
-    g0[s] = h0[id]; g1[s] = h1[id]; g2[s] = h2[id];
+    prims[4 * (size_t)s + q] = hot[4 * (size_t)id + q];
 }
 
 __device__ __forceinline__ int delta(const uint64_t* keys, int n, int i, int j)
@@ -397,7 +399,7 @@ cudaError_t dalloc(T** p, size_t n) { return cudaMalloc((void**)p, (n ? n : 1) *
 
 void SceneBuffers::release()
 {
-    float4** ps[] = {&g0, &g1, &g2, &c0, &c1, &c2, &m0, &m1, &m2, &nodes};
+    float4** ps[] = {&prims, &c0, &c1, &c2, &m0, &m1, &m2, &nodes};
     for (auto p : ps) { if (*p) cudaFree(*p); *p = nullptr; }
     n_prims = n_spheres = n_tris = n_mats = n_nodes = max_depth = 0; root = -1; max_abs = 0.f;
 }
@@ -419,7 +421,7 @@ cudaError_t build_scene(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns
 
     rt_sphere* d_sph = nullptr; rt_vertex* d_vtx = nullptr; uint32_t* d_idx = nullptr; rt_mesh* d_mesh = nullptr;
     uint32_t* d_tstart = nullptr;
-    float4 *h0 = nullptr, *h1 = nullptr, *h2 = nullptr, *bmin = nullptr, *bmax = nullptr, *lmin = nullptr, *lmax = nullptr, *imin = nullptr, *imax = nullptr;
+    float4 *hot = nullptr, *bmin = nullptr, *bmax = nullptr, *lmin = nullptr, *lmax = nullptr, *imin = nullptr, *imax = nullptr;
     int* d_bounds = nullptr; uint64_t *keys = nullptr, *keys2 = nullptr; uint32_t *ids = nullptr, *ids2 = nullptr, *new_slot = nullptr;
     int2 *children = nullptr, *ranges = nullptr; int *pin = nullptr, *plf = nullptr, *flags = nullptr, *d_depth = nullptr;
     int *cidA = nullptr, *cidB = nullptr, *nn = nullptr; float4 *cloA = nullptr, *chiA = nullptr, *cloB = nullptr, *chiB = nullptr;
@@ -437,7 +439,7 @@ cudaError_t build_scene(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns
     if (nm) RT_TRY(cudaMemcpyAsync(d_mesh, meshes, nm * sizeof(rt_mesh), cudaMemcpyHostToDevice, stream));
     RT_TRY(cudaMemcpyAsync(d_tstart, tri_start.data(), (nm + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice, stream));
 
-    RT_TRY(dalloc(&out.g0, n)); RT_TRY(dalloc(&out.g1, n)); RT_TRY(dalloc(&out.g2, n));
+    RT_TRY(dalloc(&out.prims, 4 * (size_t)n));
     RT_TRY(dalloc(&out.c0, n)); RT_TRY(dalloc(&out.c1, n)); RT_TRY(dalloc(&out.c2, n));
     RT_TRY(dalloc(&out.m0, nmat)); RT_TRY(dalloc(&out.m1, nmat)); RT_TRY(dalloc(&out.m2, nmat));
     out.n_prims = n; out.n_spheres = ns; out.n_tris = nt; out.n_mats = nmat;
@@ -446,7 +448,7 @@ cudaError_t build_scene(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns
         if (nmat) setup_materials<<<(nmat + T - 1) / T, T, 0, stream>>>(rs, out.m0, out.m1, out.m2);
         if (n == 0) { RT_TRY(cudaStreamSynchronize(stream)); goto done; }
 
-        RT_TRY(dalloc(&h0, n)); RT_TRY(dalloc(&h1, n)); RT_TRY(dalloc(&h2, n)); RT_TRY(dalloc(&bmin, n)); RT_TRY(dalloc(&bmax, n));
+        RT_TRY(dalloc(&hot, 4 * (size_t)n)); RT_TRY(dalloc(&bmin, n)); RT_TRY(dalloc(&bmax, n));
         RT_TRY(dalloc(&lmin, n)); RT_TRY(dalloc(&lmax, n)); RT_TRY(dalloc(&imin, n)); RT_TRY(dalloc(&imax, n));
         RT_TRY(dalloc(&d_bounds, 6)); RT_TRY(dalloc(&keys, n)); RT_TRY(dalloc(&keys2, n)); RT_TRY(dalloc(&ids, n)); RT_TRY(dalloc(&ids2, n));
         RT_TRY(dalloc(&children, n)); RT_TRY(dalloc(&ranges, n)); RT_TRY(dalloc(&pin, n)); RT_TRY(dalloc(&plf, n)); RT_TRY(dalloc(&flags, n));
@@ -454,7 +456,7 @@ cudaError_t build_scene(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns
         RT_TRY(cudaMemcpyAsync(d_bounds, h_init, sizeof(h_init), cudaMemcpyHostToDevice, stream));
 
         const int nb = (n + T - 1) / T;
-        setup_prims<<<nb, T, 0, stream>>>(rs, h0, h1, h2, out.c0, out.c1, out.c2, bmin, bmax, d_bounds);
+        setup_prims<<<nb, T, 0, stream>>>(rs, hot, out.c0, out.c1, out.c2, bmin, bmax, d_bounds);
         morton_keys<<<nb, T, 0, stream>>>(n, bmin, bmax, d_bounds, keys, ids);
         RT_TRY(cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, keys, keys2, ids, ids2, (int)n, 0, 63, stream));
         RT_TRY(cudaMalloc(&cub_tmp, cub_bytes ? cub_bytes : 1));
@@ -510,7 +512,7 @@ cudaError_t build_scene(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns
             emit_nodes<<<nb, T, 0, stream>>>((int)n - 1, children, ranges, new_slot, lmin, lmax, imin, imax, (int)leaf_size, out.nodes);
             out.n_nodes = n - 1; out.root = root; out.builder = use_ploc ? 0 : 1;
         }
-        gather_slots<<<nb, T, 0, stream>>>(n, ids2, new_slot, h0, h1, h2, out.g0, out.g1, out.g2);
+        gather_slots<<<(4 * n + T - 1) / T, T, 0, stream>>>(n, ids2, new_slot, hot, out.prims);
         RT_TRY(cudaMemcpyAsync(hb, d_bounds, sizeof(hb), cudaMemcpyDeviceToHost, stream));
         RT_TRY(cudaStreamSynchronize(stream));
         RT_TRY(cudaGetLastError());
@@ -524,7 +526,7 @@ cudaError_t build_scene(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns
     }
 done:
     {
-        void* tmp[] = {d_sph, d_vtx, d_idx, d_mesh, d_tstart, h0, h1, h2, bmin, bmax, lmin, lmax, imin, imax, d_bounds,
+        void* tmp[] = {d_sph, d_vtx, d_idx, d_mesh, d_tstart, hot, bmin, bmax, lmin, lmax, imin, imax, d_bounds,
                        keys, keys2, ids, ids2, children, ranges, pin, plf, flags, d_depth, cub_tmp, new_slot,
                        cidA, cidB, nn, cloA, chiA, cloB, chiB, pflags, ppos, d_tot, scan_tmp};
         for (void* p : tmp) if (p) cudaFree(p);

@@ -2,13 +2,17 @@
 //
 // HBM layout (all arrays 16-byte aligned, read through the read-only path as 128-bit loads):
 //
-//  hot, indexed by BVH slot k (primitives in Morton order):
-//    g0[k] = (A.x, A.y, A.z, id)        triangle: A = a.pos + mesh.pos   | sphere: centre
-//    g1[k] = (e1.x, e1.y, e1.z, e2.x)   e1 = B - A                        | (radius, radius^2, 0, 0)
-//    g2[k] = (e2.y, e2.z, 0, 0)         e2 = C - A
+//  hot, one 64-byte record (4 x float4) per BVH slot k, primitives in tree order:
+//    p[4k+0] = (n.x, n.y, n.z, id)       triangle: n = cross(e1, e2)        | sphere: (centre, id)
+//    p[4k+1] = (A.x, A.y, A.z, e1.x)     A = a.pos + mesh.pos, e1 = B - A   | (radius, radius^2, 0, 0)
+//    p[4k+2] = (e1.y, e1.z, e2.x, e2.y)  e2 = C - A
+//    p[4k+3] = (e2.z, 0, 0, 0)
+//    The first 16 bytes decide most tests alone: `id` tells the kinds apart (id < S) and n gives the
+//    back-face reject of wgsl:131,143 (about half of all triangle tests); the record is one
+//    64-byte-aligned pair of sectors, so the survivors' three further loads hit the same L1 line.
 //    `id` = global primitive order index of the reference's brute-force loop
 //    (wgsl:149-185): spheres 0..S-1 in array order, then triangles mesh by mesh; it is
-//    the tie-break key and tells the two primitive kinds apart (id < S).
+//    the tie-break key.
 //  cold, indexed by id, fetched once per path segment for the winning hit only:
 //    c0[id] = (nA.xyz, material index)  | sphere: (centre, material index)
 //    c1[id] = (nB.xyz, 0)  c2[id] = (nC.xyz, 0)
@@ -27,7 +31,7 @@
 namespace rt {
 
 struct SceneDev {
-    const float4* g0; const float4* g1; const float4* g2;
+    const float4* prims;
     const float4* c0; const float4* c1; const float4* c2;
     const float4* m0; const float4* m1; const float4* m2;
     const float4* nodes;

@@ -26,7 +26,7 @@ cudaError_t launch_trace(const SceneDev& sc, const CameraDev& cam, const LaunchP
 
 // Device-resident scene: SoA primitive arrays + LBVH, built on the GPU from the AoS records.
 struct SceneBuffers {
-    float4 *g0 = nullptr, *g1 = nullptr, *g2 = nullptr;
+    float4* prims = nullptr;
     float4 *c0 = nullptr, *c1 = nullptr, *c2 = nullptr;
     float4 *m0 = nullptr, *m1 = nullptr, *m2 = nullptr;
     float4* nodes = nullptr;

@@ -34,15 +34,18 @@ __device__ __forceinline__ void test_sphere(float3 o, float3 d, float4 q0, float
     }
 }
 
-// wgsl:125-147 on slot data (A pre-translated, e1 = B-A, e2 = C-A).
-__device__ __forceinline__ void test_triangle(float3 o, float3 d, float4 q0, float4 q1, float4 q2, uint32_t id, HitRec& best)
+// wgsl:125-147 on slot data.  `n` = cross(e1, e2) is precomputed at upload with the very
+// operations the reference performs per test (wgsl:129), so the back-face / parallel reject
+// of wgsl:131,143 needs only the first 16 bytes of the record; the caller fetches the rest
+// (A pre-translated, e1 = B-A, e2 = C-A) for the survivors.
+__device__ __forceinline__ bool triangle_faces_ray(float3 d, float3 n, float& det)
 {
-    float3 e1 = f3(q1.x, q1.y, q1.z);
-    float3 e2 = f3(q1.w, q2.x, q2.y);
-    float3 n = cross3(e1, e2);
-    float det = -dot3(d, n);
-    if (!(det >= 1e-6f)) return;
-    float3 ao = o - xyz(q0);
+    det = -dot3(d, n);
+    return det >= 1e-6f;
+}
+__device__ __forceinline__ void test_triangle(float3 o, float3 d, float3 n, float det, float3 A, float3 e1, float3 e2, uint32_t id, HitRec& best)
+{
+    float3 ao = o - A;
     float3 dao = cross3(ao, d);
     float inv = 1.0f / det;
     float dst = dot3(ao, n) * inv;

@@ -241,16 +241,19 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
             // ---- leaf loop: test parked primitives, one per lane per step ----
             while (__ballot_sync(0xffffffffu, !shading && leaf_count != 0u)) {
                 if (!shading && leaf_count != 0u) {
-                    const float4 q0 = __ldg(sc.g0 + leaf_first);
-                    const float4 q1 = __ldg(sc.g1 + leaf_first);
+                    const float4* pr = sc.prims + 4 * (size_t)leaf_first;
+                    const float4 q0 = __ldg(pr);
                     const uint32_t id = __float_as_uint(q0.w);
                     if (id < sc.n_spheres) {
                         if (DETAIL) n_sph++;
-                        test_sphere(ro, rd, q0, q1, id, best);
+                        test_sphere(ro, rd, q0, __ldg(pr + 1), id, best);
                     } else {
                         if (DETAIL) n_tri++;
-                        const float4 q2 = __ldg(sc.g2 + leaf_first);
-                        test_triangle(ro, rd, q0, q1, q2, id, best);
+                        float det;
+                        if (triangle_faces_ray(rd, xyz(q0), det)) {
+                            const float4 q1 = __ldg(pr + 1), q2 = __ldg(pr + 2), q3 = __ldg(pr + 3);
+                            test_triangle(ro, rd, xyz(q0), det, xyz(q1), f3(q1.w, q2.x, q2.y), f3(q2.z, q2.w, q3.x), id, best);
+                        }
                     }
                     leaf_first++;
                     if (--leaf_count == 0u && node < 0) {        // a second leaf was waiting in `node`
