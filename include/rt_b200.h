@@ -65,23 +65,37 @@ typedef struct rt_mesh {
     uint32_t first;
     uint32_t triangles;
     uint32_t offset;
-    float _padding;
+    uint32_t diffuse_tex;       /* Rust `_padding: f32` (always 0.0 upstream). Texture extension: 0 = none, k = texture k-1 of rt_upload_textures */
     float pos[3];
     float _padding2;
     float color[4];
     float emission_color[4];
     float emission_strength;
     float specular;             /* WGSL: material.smoothness */
-    float _padding3[2];
+    uint32_t normal_tex;        /* Rust `_padding3[0]`. Texture extension: tangent-space normal map, same encoding */
+    uint32_t _padding3;
 } rt_mesh;
 
 /* src/core/scene.rs:79-86 `Vertex` (32 B); wgsl:22-25. */
 typedef struct rt_vertex {
     float pos[3];
-    float _padding1;
+    float tu;                   /* Rust `_padding1` (0.0 upstream). Texture extension: texture coordinate u */
     float normal[3];
-    float _padding2;
+    float tv;                   /* Rust `_padding2`. Texture extension: texture coordinate v */
 } rt_vertex;
+
+/* Texture extension (no reference counterpart: upstream has no UVs and loads no images,
+ * scene.rs:81-86, texture.rs; SURVEY.md 8(a')).  Tightly packed RGBA8, row 0 first.
+ * Sampling: bilinear, repeat addressing, texel centres at (i+0.5)/size, channel = byte/255,
+ * no sRGB decode; diffuse: material colour *= texel; normal map: n = 2*rgb-1 in the
+ * Gram-Schmidt tangent frame of the UV mapping around the interpolated vertex normal.
+ * The arithmetic is specified by oracle/rt_oracle.cpp (sample_texture, apply_textures).
+ * Records whose padding words are all zero render exactly as the reference does. */
+typedef struct rt_texture {
+    uint32_t width;
+    uint32_t height;
+    const uint8_t* rgba8;
+} rt_texture;
 
 /* Device-side counters since the last rt_reset_counters(). A "ray" is one call of
  * calculate_ray_collions (wgsl:234), i.e. one path segment, primary included. */
@@ -146,6 +160,11 @@ int rt_upload_scene(rt_ctx* ctx,
                     const rt_vertex* vertices, uint32_t n_vertices,
                     const uint32_t* indices, uint32_t n_indices,
                     const rt_mesh* meshes, uint32_t n_meshes);
+
+/* Texture extension: replaces the context's texture table (n = 0 clears it). Pixels are copied
+ * into CUDA arrays bound to texture objects; handles in rt_mesh address this table (handles
+ * above n are treated as "none"). Independent of rt_upload_scene order. */
+int rt_upload_textures(rt_ctx* ctx, const rt_texture* textures, uint32_t n_textures);
 
 /* queue.write_buffer(camera.buffer, uniform) — context.rs:185. */
 int rt_set_camera(rt_ctx* ctx, const rt_camera_uniform* camera);

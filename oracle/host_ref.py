@@ -214,11 +214,13 @@ def _loader_mesh(n_meshes, n_indices, first, offset):
     return m
 
 
-def load_model_obj(text, vertices, indices, meshes):
+def load_model_obj(text, vertices, indices, meshes, keep_uv=False):
     """resource.rs:47-107 via tobj 3.2.5 with triangulate + single_index: one model per
     o/g group, faces fan-triangulated, one output vertex per distinct (v,vt,vn) triple in
-    order of first use.  Appends to the three lists (of numpy record arrays)."""
-    pos, nrm, models, cur = [], [], [], None
+    order of first use.  Appends to the three lists (of numpy record arrays).
+    keep_uv (texture extension; the reference drops `vt`): store (u, 1 - v) — image row 0 is
+    the top row — in the vertex padding words."""
+    pos, nrm, tex, models, cur = [], [], [], [], None
 
     def flush():
         nonlocal cur
@@ -238,23 +240,26 @@ def load_model_obj(text, vertices, indices, meshes):
             pos.append([float(x) for x in t[1:4]])
         elif t[0] == "vn":
             nrm.append([float(x) for x in t[1:4]])
+        elif t[0] == "vt":
+            tex.append([float(x) for x in t[1:3]])
         elif t[0] in ("o", "g"):
             flush()
-            cur = {"map": {}, "p": [], "n": [], "idx": []}
+            cur = {"map": {}, "p": [], "n": [], "t": [], "idx": []}
         elif t[0] == "f":
             if cur is None:
-                cur = {"map": {}, "p": [], "n": [], "idx": []}
+                cur = {"map": {}, "p": [], "n": [], "t": [], "idx": []}
             corner = []
             for c in t[1:]:
                 parts = c.split("/")
                 vi = fix(parts[0], len(pos))
-                ti = fix(parts[1], 0) if len(parts) > 1 and parts[1] else -1
+                ti = fix(parts[1], len(tex)) if len(parts) > 1 and parts[1] else -1
                 ni = fix(parts[2], len(nrm)) if len(parts) > 2 and parts[2] else -1
                 key = (vi, ti, ni)
                 if key not in cur["map"]:
                     cur["map"][key] = len(cur["p"])
                     cur["p"].append(pos[vi])
                     cur["n"].append(nrm[ni])          # reference indexes normals unconditionally
+                    cur["t"].append(tex[ti] if 0 <= ti < len(tex) else [0.0, 1.0])
                 corner.append(cur["map"][key])
             for k in range(1, len(corner) - 1):
                 cur["idx"] += [corner[0], corner[k], corner[k + 1]]
@@ -267,6 +272,10 @@ def load_model_obj(text, vertices, indices, meshes):
         n_meshes += 1
         vs = np.zeros(len(mdl["p"]), VERTEX_DT)
         vs["pos"], vs["normal"] = np.asarray(mdl["p"], np.float32), np.asarray(mdl["n"], np.float32)
+        if keep_uv:
+            uv = np.asarray(mdl["t"], np.float32)
+            vs[vs.dtype.names[1]] = uv[:, 0]
+            vs[vs.dtype.names[3]] = np.float32(1.0) - uv[:, 1]
         vertices.append(vs)
         indices.append(np.asarray(mdl["idx"], np.uint32))
 

@@ -16,6 +16,13 @@
  * struct offsets, analytic intersections) => "parity unpinned" against the reference's
  * own GPU output, as DESIGN.md states.
  *
+ * EXTENSION (no reference counterpart, SURVEY.md §8(a')): diffuse / tangent-space normal-map
+ * textures.  UVs ride in the two padding floats of `Vertex`, 1-based texture handles in
+ * padding words of `Mesh`; all-zero padding (what the reference's constructors write) means
+ * "no texture" and leaves every result unchanged.  The sampling and tangent-frame
+ * arithmetic is specified here (sample_texture / apply_textures) and is what the CUDA path
+ * must reproduce bit for bit; it is pinned by nothing upstream.
+ *
  * Arithmetic contract (DESIGN.md §"Arithmetic contract"): binary32, RNE, denormals kept,
  * no implicit contraction (-ffp-contract=off); fused multiply-adds appear only where
  * fmaf() is written: dot3, cross, ray point o+d*t, reflect, mix, normal interpolation
@@ -56,23 +63,31 @@ struct rto_sphere {            /* src/core/scene.rs:11-21 ; wgsl:9-20 */
     float emission_strength, smoothness, _pad[2];
 };
 struct rto_mesh {              /* src/core/scene.rs:23-37 ; wgsl:27-33 */
-    uint32_t first, triangles, offset; float _p0;
+    uint32_t first, triangles, offset;
+    uint32_t diffuse_tex;      /* Rust `_padding`: extension, 0 = none, k = texture k-1 */
     float pos[3], _p1;
     float color[4], emission_color[4];
-    float emission_strength, smoothness /* Rust: specular */, _p2[2];
+    float emission_strength, smoothness /* Rust: specular */;
+    uint32_t normal_tex;       /* Rust `_padding3[0]`: extension, same encoding */
+    uint32_t _p2;
 };
 struct rto_vertex {            /* src/core/scene.rs:79-86 ; wgsl:22-25 */
-    float pos[3], _p0;
-    float normal[3], _p1;
+    float pos[3], tu;          /* Rust `_padding1`: extension, texture coordinate u */
+    float normal[3], tv;       /* Rust `_padding2`: extension, texture coordinate v */
+};
+struct rto_texture {           /* extension: tightly packed RGBA8, row 0 first */
+    uint32_t width, height;
+    const uint8_t* rgba8;
 };
 
 static_assert(sizeof(rto_params) == 28, "Params");
 static_assert(sizeof(rto_camera) == 128 && offsetof(rto_camera, w) == 80 &&
               offsetof(rto_camera, lens_radius) == 124, "CameraUniform");
 static_assert(sizeof(rto_sphere) == 64 && offsetof(rto_sphere, smoothness) == 52, "Sphere");
-static_assert(sizeof(rto_mesh) == 80 && offsetof(rto_mesh, pos) == 16 &&
-              offsetof(rto_mesh, smoothness) == 68, "Mesh");
-static_assert(sizeof(rto_vertex) == 32 && offsetof(rto_vertex, normal) == 16, "Vertex");
+static_assert(sizeof(rto_mesh) == 80 && offsetof(rto_mesh, pos) == 16 && offsetof(rto_mesh, diffuse_tex) == 12 &&
+              offsetof(rto_mesh, smoothness) == 68 && offsetof(rto_mesh, normal_tex) == 72, "Mesh");
+static_assert(sizeof(rto_vertex) == 32 && offsetof(rto_vertex, normal) == 16 && offsetof(rto_vertex, tu) == 12 &&
+              offsetof(rto_vertex, tv) == 28, "Vertex");
 
 } /* extern "C" */
 
@@ -121,6 +136,10 @@ struct Hit {
     bool hit = false; float dst = 0.0f; V3 hit_point{0, 0, 0}; V3 normal{0, 0, 0};
     Material material{{0, 0, 0, 0}, {0, 0, 0, 0}, 0.0f, 0.0f};
     uint32_t prim = 0xFFFFFFFFu;   /* AOV only: global primitive order index */
+    /* texture extension: barycentrics, world-space edges, per-vertex UVs, handles */
+    float bu = 0.0f, bv = 0.0f, bw = 0.0f; V3 e1{0, 0, 0}, e2{0, 0, 0};
+    float uva[2] = {0, 0}, uvb[2] = {0, 0}, uvc[2] = {0, 0};
+    uint32_t diffuse_tex = 0, normal_tex = 0;
 };
 
 struct SceneView {
@@ -128,6 +147,7 @@ struct SceneView {
     const rto_vertex* vertices; uint32_t nv;
     const uint32_t* indices; uint32_t ni;
     const rto_mesh* meshes; uint32_t nm;
+    const rto_texture* textures; uint32_t ntex;
 };
 
 /* wgsl:205-210 */
@@ -213,7 +233,61 @@ inline Hit ray_triangle(const Ray& ray, const Vtx& a, const Vtx& b, const Vtx& c
     V3 nsum = fma3(c.normal, v, fma3(b.normal, u, a.normal * w));
     hit.normal = normalize3(nsum);
     hit.dst = dst;
+    hit.bu = u; hit.bv = v; hit.bw = w; hit.e1 = edge_ab; hit.e2 = edge_ac;
     return hit;
+}
+
+/* ---- texture extension --------------------------------------------------------------
+ * Bilinear, repeat addressing, texel centres at (i + 0.5) / size, channel = byte * (1/255).
+ * Written out so that a GPU implementation can fetch the four texels with point sampling
+ * and reproduce the interpolation exactly. */
+inline int wrap_index(int i, int n) { int r = i % n; return r < 0 ? r + n : r; }
+inline V4 texel(const rto_texture& t, int ix, int iy) {
+    const uint8_t* p = t.rgba8 + ((size_t)iy * t.width + (size_t)ix) * 4;
+    const float k = 0.003921568859368563f;          /* f32(1/255) */
+    return V4{(float)p[0] * k, (float)p[1] * k, (float)p[2] * k, (float)p[3] * k};
+}
+inline V4 sample_texture(const rto_texture& t, float u, float v) {
+    float x = fmaf(u, (float)t.width, -0.5f), y = fmaf(v, (float)t.height, -0.5f);
+    float x0 = floorf(x), y0 = floorf(y);
+    float fx = x - x0, fy = y - y0;
+    if (!(fabsf(x0) <= 1.0e9f)) { x0 = 0.0f; fx = 0.0f; }     /* non-finite / absurd coordinates */
+    if (!(fabsf(y0) <= 1.0e9f)) { y0 = 0.0f; fy = 0.0f; }
+    int ix0 = wrap_index((int)x0, (int)t.width), iy0 = wrap_index((int)y0, (int)t.height);
+    int ix1 = (ix0 + 1 == (int)t.width) ? 0 : ix0 + 1, iy1 = (iy0 + 1 == (int)t.height) ? 0 : iy0 + 1;
+    V4 top = mix4(texel(t, ix0, iy0), texel(t, ix1, iy0), fx);
+    V4 bot = mix4(texel(t, ix0, iy1), texel(t, ix1, iy1), fx);
+    return mix4(top, bot, fy);
+}
+/* Applied to the closest triangle hit before shading: material.color *= diffuse texel;
+ * normal = normalize(T*n.x + B*n.y + N*n.z) with n = 2*texel.rgb - 1 and (T, B) the
+ * Gram-Schmidt tangent frame of the UV mapping around the interpolated normal N. */
+inline void apply_textures(const SceneView& sc, Hit& hit) {
+    if (hit.diffuse_tex == 0u && hit.normal_tex == 0u) return;
+    float tu = fmaf(hit.uvc[0], hit.bv, fmaf(hit.uvb[0], hit.bu, hit.uva[0] * hit.bw));
+    float tv = fmaf(hit.uvc[1], hit.bv, fmaf(hit.uvb[1], hit.bu, hit.uva[1] * hit.bw));
+    if (hit.normal_tex != 0u && hit.normal_tex <= sc.ntex) {
+        float du1 = hit.uvb[0] - hit.uva[0], dv1 = hit.uvb[1] - hit.uva[1];
+        float du2 = hit.uvc[0] - hit.uva[0], dv2 = hit.uvc[1] - hit.uva[1];
+        float det = fmaf(du1, dv2, -(du2 * dv1));
+        if (det != 0.0f && det == det) {
+            float sg = sign1(det);
+            V3 N = hit.normal;
+            V3 Traw = fma3(hit.e2, -dv1, hit.e1 * dv2) * sg;
+            V3 Braw = fma3(hit.e1, -du2, hit.e2 * du1) * sg;
+            V3 T = fma3(N, -dot3(N, Traw), Traw);
+            if (dot3(T, T) > 0.0f) {
+                T = normalize3(T);
+                V3 Bt = cross3(N, T);
+                Bt = Bt * sign1(dot3(Bt, Braw));
+                V4 tx = sample_texture(sc.textures[hit.normal_tex - 1u], tu, tv);
+                float nx = fmaf(tx.x, 2.0f, -1.0f), ny = fmaf(tx.y, 2.0f, -1.0f), nz = fmaf(tx.z, 2.0f, -1.0f);
+                hit.normal = normalize3(fma3(N, nz, fma3(Bt, ny, T * nx)));
+            }
+        }
+    }
+    if (hit.diffuse_tex != 0u && hit.diffuse_tex <= sc.ntex)
+        hit.material.color = hit.material.color * sample_texture(sc.textures[hit.diffuse_tex - 1u], tu, tv);
 }
 
 inline Material sphere_material(const rto_sphere& s) {
@@ -257,11 +331,15 @@ inline Hit calculate_ray_collions(const SceneView& sc, const Ray& ray, Counters*
                 closest_hit = hit;
                 closest_hit.material = mesh_material(mesh);
                 closest_hit.prim = tri_base + i;
+                closest_hit.uva[0] = r1.tu; closest_hit.uva[1] = r1.tv; closest_hit.uvb[0] = r2.tu; closest_hit.uvb[1] = r2.tv;
+                closest_hit.uvc[0] = r3.tu; closest_hit.uvc[1] = r3.tv;
+                closest_hit.diffuse_tex = mesh.diffuse_tex; closest_hit.normal_tex = mesh.normal_tex;
             }
         }
         tri_base += mesh.triangles;
     }
     if (ctr) { ctr->segments++; ctr->sphere_tests += sc.ns; ctr->tri_tests += tri_base - sc.ns; }
+    if (closest_hit.hit && sc.ntex != 0u) apply_textures(sc, closest_hit);   /* extension; no-op without handles */
     return closest_hit;
 }
 
@@ -389,6 +467,15 @@ extern "C" {
  *   nthreads   : OpenMP threads (<=0: all).
  * Returns 0, or -1 on bad arguments.
  */
+int rto_dispatch_tex(const rto_params* params, const rto_camera* camera,
+                     const rto_sphere* spheres, uint32_t ns,
+                     const rto_vertex* vertices, uint32_t nv,
+                     const uint32_t* indices, uint32_t ni,
+                     const rto_mesh* meshes, uint32_t nm,
+                     const rto_texture* textures, uint32_t ntex,
+                     float* accum, uint32_t* primary_ids, uint64_t* counters,
+                     int x_step, int y_step, int nthreads);
+
 int rto_dispatch(const rto_params* params, const rto_camera* camera,
                  const rto_sphere* spheres, uint32_t ns,
                  const rto_vertex* vertices, uint32_t nv,
@@ -397,11 +484,26 @@ int rto_dispatch(const rto_params* params, const rto_camera* camera,
                  float* accum, uint32_t* primary_ids, uint64_t* counters,
                  int x_step, int y_step, int nthreads)
 {
+    return rto_dispatch_tex(params, camera, spheres, ns, vertices, nv, indices, ni, meshes, nm, nullptr, 0,
+                            accum, primary_ids, counters, x_step, y_step, nthreads);
+}
+
+/* The same dispatch with the texture extension: `textures` are addressed by the 1-based
+ * handles in the Mesh records (handles above ntex are ignored). */
+int rto_dispatch_tex(const rto_params* params, const rto_camera* camera,
+                     const rto_sphere* spheres, uint32_t ns,
+                     const rto_vertex* vertices, uint32_t nv,
+                     const uint32_t* indices, uint32_t ni,
+                     const rto_mesh* meshes, uint32_t nm,
+                     const rto_texture* textures, uint32_t ntex,
+                     float* accum, uint32_t* primary_ids, uint64_t* counters,
+                     int x_step, int y_step, int nthreads)
+{
     if (!params || !camera || !accum) return -1;
     if (x_step < 1) x_step = 1;
     if (y_step < 1) y_step = 1;
     const uint32_t W = params->width, H = params->height;
-    SceneView sc{spheres, ns, vertices, nv, indices, ni, meshes, nm};
+    SceneView sc{spheres, ns, vertices, nv, indices, ni, meshes, nm, textures, ntex};
     uint64_t tot_seg = 0, tot_sph = 0, tot_tri = 0;
 #ifdef _OPENMP
     if (nthreads <= 0) nthreads = omp_get_max_threads();
@@ -483,5 +585,8 @@ void rto_refract(const float* uv, const float* n, float ratio, float* out) {
     V3 r = refract3(v3(uv), v3(n), ratio); out[0] = r.x; out[1] = r.y; out[2] = r.z;
 }
 float rto_reflectance(float c, float ratio) { return reflectance(c, ratio); }
+void rto_sample_texture(const rto_texture* t, float u, float v, float* out) {
+    V4 c = sample_texture(*t, u, v); out[0] = c.x; out[1] = c.y; out[2] = c.z; out[3] = c.w;
+}
 
 } /* extern "C" */

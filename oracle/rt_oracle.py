@@ -29,15 +29,32 @@ CAMERA_DT = np.dtype([("origin", "<f4", 3), ("_p1", "<f4"),
 SPHERE_DT = np.dtype([("position", "<f4", 3), ("radius", "<f4"), ("color", "<f4", 4),
                       ("emission_color", "<f4", 4), ("emission_strength", "<f4"),
                       ("smoothness", "<f4"), ("_pad", "<f4", 2)])
-MESH_DT = np.dtype([("first", "<u4"), ("triangles", "<u4"), ("offset", "<u4"), ("_p0", "<f4"),
+# the padding words carry the texture extension (0 = reference behaviour): Mesh.diffuse_tex /
+# normal_tex are 1-based texture handles, Vertex.tu / tv the texture coordinates
+MESH_DT = np.dtype([("first", "<u4"), ("triangles", "<u4"), ("offset", "<u4"), ("diffuse_tex", "<u4"),
                     ("pos", "<f4", 3), ("_p1", "<f4"), ("color", "<f4", 4),
                     ("emission_color", "<f4", 4), ("emission_strength", "<f4"),
-                    ("specular", "<f4"), ("_p2", "<f4", 2)])
-VERTEX_DT = np.dtype([("pos", "<f4", 3), ("_p0", "<f4"), ("normal", "<f4", 3), ("_p1", "<f4")])
+                    ("specular", "<f4"), ("normal_tex", "<u4"), ("_p2", "<u4")])
+VERTEX_DT = np.dtype([("pos", "<f4", 3), ("tu", "<f4"), ("normal", "<f4", 3), ("tv", "<f4")])
 assert (PARAMS_DT.itemsize, CAMERA_DT.itemsize, SPHERE_DT.itemsize, MESH_DT.itemsize,
         VERTEX_DT.itemsize) == (28, 128, 64, 80, 32)
 
 MISS = 0xFFFFFFFF
+
+
+class Texture(C.Structure):
+    _fields_ = [("width", C.c_uint32), ("height", C.c_uint32), ("rgba8", C.c_void_p)]
+
+
+def _texture_table(textures):
+    """list of (H, W, 4) uint8 arrays -> (ctypes array of rto_texture, keep-alive list)"""
+    keep = [np.ascontiguousarray(t, dtype=np.uint8) for t in (textures or [])]
+    for t in keep:
+        assert t.ndim == 3 and t.shape[2] == 4
+    arr = (Texture * max(1, len(keep)))()
+    for i, t in enumerate(keep):
+        arr[i] = Texture(t.shape[1], t.shape[0], t.ctypes.data)
+    return arr, keep
 
 
 def build(force=False):
@@ -60,6 +77,9 @@ def lib():
         vp, u32, i32, f32 = C.c_void_p, C.c_uint32, C.c_int32, C.c_float
         L.rto_dispatch.argtypes = [vp, vp, vp, u32, vp, u32, vp, u32, vp, u32, vp, vp, vp, C.c_int, C.c_int, C.c_int]
         L.rto_dispatch.restype = C.c_int
+        L.rto_dispatch_tex.argtypes = [vp, vp, vp, u32, vp, u32, vp, u32, vp, u32, vp, u32, vp, vp, vp, C.c_int, C.c_int, C.c_int]
+        L.rto_dispatch_tex.restype = C.c_int
+        L.rto_sample_texture.argtypes = [vp, f32, f32, vp]
         L.rto_max_threads.restype = C.c_int
         L.rto_next_random_number.argtypes = [C.POINTER(u32)]
         L.rto_next_random_number.restype = u32
@@ -97,7 +117,7 @@ def max_threads():
 
 
 def dispatch(params, camera, spheres, vertices, indices, meshes, accum, primary_ids=None,
-             counters=None, x_step=1, y_step=1, nthreads=0):
+             counters=None, x_step=1, y_step=1, nthreads=0, textures=None):
     """One dispatch of the reference's compute entry over `accum` (H, W, 4) f32 in place."""
     params = np.ascontiguousarray(params, dtype=PARAMS_DT).reshape(1)
     camera = np.ascontiguousarray(camera, dtype=CAMERA_DT).reshape(1)
@@ -111,19 +131,20 @@ def dispatch(params, camera, spheres, vertices, indices, meshes, accum, primary_
         assert primary_ids.dtype == np.uint32 and primary_ids.flags.c_contiguous and primary_ids.size == H * W
     if counters is not None:
         assert counters.dtype == np.uint64 and counters.size >= 3
-    rc = lib().rto_dispatch(_ptr(params), _ptr(camera), _ptr(spheres), spheres.size,
-                            _ptr(vertices), vertices.size, _ptr(indices), indices.size,
-                            _ptr(meshes), meshes.size, _ptr(accum),
-                            _ptr(primary_ids) if primary_ids is not None else None,
-                            _ptr(counters) if counters is not None else None,
-                            int(x_step), int(y_step), int(nthreads))
+    tex, keep = _texture_table(textures)
+    rc = lib().rto_dispatch_tex(_ptr(params), _ptr(camera), _ptr(spheres), spheres.size,
+                                _ptr(vertices), vertices.size, _ptr(indices), indices.size,
+                                _ptr(meshes), meshes.size, C.cast(tex, C.c_void_p), len(keep), _ptr(accum),
+                                _ptr(primary_ids) if primary_ids is not None else None,
+                                _ptr(counters) if counters is not None else None,
+                                int(x_step), int(y_step), int(nthreads))
     if rc != 0:
         raise RuntimeError("rto_dispatch failed: %d" % rc)
     return accum
 
 
 def render(scene, width, height, frames, bounces, rpp=1, toggle=0, first_frame=0, primary_ids=None,
-           counters=None, x_step=1, y_step=1, nthreads=0, accum=None):
+           counters=None, x_step=1, y_step=1, nthreads=0, accum=None, textures=None):
     """`frames` progressive dispatches with params.frames = first_frame .. first_frame+frames-1
     (host increments `frames` like Context::update, context.rs:176-187)."""
     cam, spheres, vertices, indices, meshes = scene
@@ -135,7 +156,7 @@ def render(scene, width, height, frames, bounces, rpp=1, toggle=0, first_frame=0
     for f in range(first_frame, first_frame + frames):
         p["frames"] = f
         dispatch(p, cam, spheres, vertices, indices, meshes, accum,
-                 primary_ids if f == first_frame else None, counters, x_step, y_step, nthreads)
+                 primary_ids if f == first_frame else None, counters, x_step, y_step, nthreads, textures)
     return accum
 
 
@@ -165,6 +186,14 @@ def ray_triangle(o, d, tri):
     out = np.zeros(8, np.float32)
     o, d, tri = _f32(o), _f32(d), _f32(tri).reshape(18)
     lib().rto_ray_triangle(_ptr(o), _ptr(d), _ptr(tri), _ptr(out))
+    return out
+
+
+def sample_texture(tex, u, v):
+    """tex: (H, W, 4) uint8 -> bilinear RGBA f32 under the extension's sampling rule."""
+    arr, keep = _texture_table([tex])
+    out = np.zeros(4, np.float32)
+    lib().rto_sample_texture(C.cast(arr, C.c_void_p), float(u), float(v), _ptr(out))
     return out
 
 

@@ -29,13 +29,18 @@ CAMERA_DT = np.dtype([("origin", "<f4", 3), ("_padding1", "<f4"),
 SPHERE_DT = np.dtype([("position", "<f4", 3), ("radius", "<f4"), ("color", "<f4", 4),
                       ("emission_color", "<f4", 4), ("emission_strength", "<f4"),
                       ("smoothness", "<f4"), ("_padding", "<f4", 2)])
-MESH_DT = np.dtype([("first", "<u4"), ("triangles", "<u4"), ("offset", "<u4"), ("_padding", "<f4"),
+# texture extension: the reference's padding words carry 1-based texture handles / UVs (0 = none)
+MESH_DT = np.dtype([("first", "<u4"), ("triangles", "<u4"), ("offset", "<u4"), ("diffuse_tex", "<u4"),
                     ("pos", "<f4", 3), ("_padding2", "<f4"), ("color", "<f4", 4),
                     ("emission_color", "<f4", 4), ("emission_strength", "<f4"),
-                    ("specular", "<f4"), ("_padding3", "<f4", 2)])
-VERTEX_DT = np.dtype([("pos", "<f4", 3), ("_padding1", "<f4"), ("normal", "<f4", 3), ("_padding2", "<f4")])
+                    ("specular", "<f4"), ("normal_tex", "<u4"), ("_padding3", "<u4")])
+VERTEX_DT = np.dtype([("pos", "<f4", 3), ("tu", "<f4"), ("normal", "<f4", 3), ("tv", "<f4")])
 assert (PARAMS_DT.itemsize, CAMERA_DT.itemsize, SPHERE_DT.itemsize, MESH_DT.itemsize,
         VERTEX_DT.itemsize) == (28, 128, 64, 80, 32)
+
+
+class Texture(C.Structure):
+    _fields_ = [("width", C.c_uint32), ("height", C.c_uint32), ("rgba8", C.c_void_p)]
 
 
 class Counters(C.Structure):
@@ -60,6 +65,7 @@ SYMBOLS = {
     "rt_create": (C.c_int, [C.POINTER(_vp), C.c_int, _u32, _u32]),
     "rt_destroy": (None, [_vp]),
     "rt_upload_scene": (C.c_int, [_vp, _vp, _u32, _vp, _u32, _vp, _u32, _vp, _u32]),
+    "rt_upload_textures": (C.c_int, [_vp, _vp, _u32]),
     "rt_set_camera": (C.c_int, [_vp, _vp]),
     "rt_set_params": (C.c_int, [_vp, _vp]),
     "rt_dispatch": (C.c_int, [_vp]),

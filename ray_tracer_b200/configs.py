@@ -20,19 +20,22 @@ FIXTURES = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests
 # name -> (width, height, spp, bounces, skybox)
 CONFIGS = {
     "c1_balls": (800, 800, 16, 4, 0),
-    "c2_cube": (1920, 1080, 64, 8, 1),
+    "c2_cube": (1920, 1080, 64, 8, 1),          # cobble diffuse + normal map bound (texture extension)
+    "c2_cube_plain": (1920, 1080, 64, 8, 1),    # the loader's untextured records, as the reference would render them
     "c3_teapot": (1920, 1080, 256, 8, 1),
     "c4_tree": (3840, 2160, 1024, 8, 1),
     "c5_stress": (3840, 2160, 64, 8, 1),
 }
 
 
-def load_fixture(name, mesh_base=0, first_base=0, offset_base=0):
+def load_fixture(name, mesh_base=0, first_base=0, offset_base=0, uv=False):
     """(vertices, indices, meshes) exactly as load_model appends them after `mesh_base`
     meshes / `first_base` indices / `offset_base` vertices already in the scene."""
     z = np.load(os.path.join(FIXTURES, name + ".npz"))
     vs = np.zeros(len(z["pos"]), VERTEX_DT)
     vs["pos"], vs["normal"] = z["pos"], z["normal"]
+    if uv and "uv" in z:
+        vs["tu"], vs["tv"] = z["uv"][:, 0], z["uv"][:, 1]
     ms = []
     for k in range(len(z["first"])):
         ms.append(loader_mesh(mesh_base + k, int(z["triangles"][k]) * 3, first_base + int(z["first"][k]),
@@ -107,11 +110,19 @@ def build(name, width=None, height=None):
     no_sph = np.zeros(0, SPHERE_DT)
     if name == "c1_balls":
         scene = Scene.balls(aspect)
-    elif name == "c2_cube":
-        vs, ix, ms = load_fixture("cube_obj")
+    elif name in ("c2_cube", "c2_cube_plain"):
+        textured = name == "c2_cube"
+        vs, ix, ms = load_fixture("cube_obj", uv=textured)
         light = _sphere((-7.44, -0.72, 20.0), 15.0, (0.1, 0.1, 0.1, 0.0), (1, 1, 1, 1), 2.0, 0.0)   # balls' light, scene.rs:423-428
         cam = Camera((3.0, 2.0, 4.0), (0.0, 0.0, 0.0), (0, 1, 0), 45.0, aspect, 0.1, 100.0, 0.0, 1.0)
-        scene = Scene(cam, light, vs, ix, ms)
+        tex = []
+        if textured:                                   # cobble-diffuse / cobble-normal, box-filtered to 256^2 (make_fixtures.py)
+            z = np.load(os.path.join(FIXTURES, "cobble_256.npz"))
+            tex = [z["diffuse"], z["normal"]]
+            ms["diffuse_tex"], ms["normal_tex"] = 1, 2
+            ms["color"] = (1.0, 1.0, 1.0, 1.0)         # the texture supplies the albedo
+            ms["specular"] = 0.0
+        scene = Scene(cam, light, vs, ix, ms, tex)
     elif name == "c3_teapot":
         vs, ix, ms = load_fixture("teapot")            # 2 meshes at x = 0 and x = 3, raw (Z-up, +-82 unit) coordinates
         cam = Camera((40.0, -130.0, 75.0), (5.0, 0.0, 38.0), (0, 0, 1), 45.0, aspect, 0.1, 100.0, 0.0, 1.0)

@@ -17,6 +17,8 @@ static_assert(sizeof(rt_camera_uniform) == 128 && offsetof(rt_camera_uniform, lo
 static_assert(sizeof(rt_sphere) == 64 && offsetof(rt_sphere, radius) == 12 && offsetof(rt_sphere, color) == 16 &&
               offsetof(rt_sphere, emission_color) == 32 && offsetof(rt_sphere, emission_strength) == 48 &&
               offsetof(rt_sphere, smoothness) == 52, "Sphere layout (scene.rs:11-21)");
+static_assert(offsetof(rt_mesh, diffuse_tex) == 12 && offsetof(rt_mesh, normal_tex) == 72 && offsetof(rt_vertex, tu) == 12 &&
+              offsetof(rt_vertex, tv) == 28, "texture extension lives in the padding words");
 static_assert(sizeof(rt_mesh) == 80 && offsetof(rt_mesh, pos) == 16 && offsetof(rt_mesh, color) == 32 &&
               offsetof(rt_mesh, emission_color) == 48 && offsetof(rt_mesh, emission_strength) == 64 &&
               offsetof(rt_mesh, specular) == 68, "Mesh layout (scene.rs:23-37)");
@@ -36,6 +38,9 @@ struct rt_ctx {
     int64_t opt_staging_bytes = 2ll << 30;
     int64_t opt_sched = 8 | (1 << 8) | (22 << 16);     // node loop runs while >= 8 lanes can step; shade once >= 22 lanes wait (swept on C3/C5)
     rt::SceneBuffers scene;
+    struct Tex { cudaArray_t arr; cudaTextureObject_t obj; uint32_t w, h; };
+    std::vector<Tex> textures;                    // texture extension: CUDA arrays + texture objects
+    rt::TexDev* d_tex = nullptr;                  // device table of (object, width, height)
     bool has_scene = false, has_camera = false, has_params = false;
     rt_params params{};
     rt_camera_uniform camera{};
@@ -126,7 +131,8 @@ int launch(rt_ctx* c, int32_t first_frame, uint32_t n_frames, bool want_ids)
 {
     rt::SceneDev sd{};
     const rt::SceneBuffers& s = c->scene;
-    sd.prims = s.prims; sd.c0 = s.c0; sd.c1 = s.c1; sd.c2 = s.c2;
+    sd.prims = s.prims; sd.c0 = s.c0; sd.c1 = s.c1; sd.c2 = s.c2; sd.c3 = s.c3; sd.c4 = s.c4; sd.c5 = s.c5;
+    sd.tex = c->d_tex; sd.n_tex = (uint32_t)c->textures.size();
     sd.m0 = s.m0; sd.m1 = s.m1; sd.m2 = s.m2; sd.nodes = s.nodes;
     sd.n_prims = s.n_prims; sd.n_spheres = s.n_spheres; sd.root = s.root;
     sd.max_abs = s.max_abs; sd.pad_scale = 1.52587890625e-05f;   // 2^-16
@@ -155,6 +161,13 @@ int launch(rt_ctx* c, int32_t first_frame, uint32_t n_frames, bool want_ids)
     c->launches++;
     c->dispatches += n_frames;
     return RT_OK;
+}
+
+void free_textures(rt_ctx* c)
+{
+    for (auto& t : c->textures) { if (t.obj) cudaDestroyTextureObject(t.obj); if (t.arr) cudaFreeArray(t.arr); }
+    c->textures.clear();
+    if (c->d_tex) { cudaFree(c->d_tex); c->d_tex = nullptr; }
 }
 
 int check_ready(rt_ctx* c)
@@ -211,6 +224,7 @@ void rt_destroy(rt_ctx* c)
     drain_events(c);
     for (auto& p : c->pool) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
     c->scene.release();
+    free_textures(c);
     if (c->accum) cudaFree(c->accum);
     if (c->primary_ids) cudaFree(c->primary_ids);
     if (c->d_counters) cudaFree(c->d_counters);
@@ -256,6 +270,48 @@ int rt_upload_scene(rt_ctx* c, const rt_sphere* spheres, uint32_t ns, const rt_v
         return fail(c, RT_ERR_UNSUPPORTED, "rt_upload_scene: BVH deeper than the traversal stack");
     }
     c->has_scene = true;
+    return RT_OK;
+}
+
+int rt_upload_textures(rt_ctx* c, const rt_texture* tex, uint32_t n)
+{
+    if (!c) return RT_ERR_INVALID_ARGUMENT;
+    if (n && !tex) return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_upload_textures: NULL array with non-zero count");
+    for (uint32_t i = 0; i < n; i++)
+        if (tex[i].width == 0 || tex[i].height == 0 || tex[i].width > 32768u || tex[i].height > 32768u || !tex[i].rgba8) {
+            char b[128]; snprintf(b, sizeof b, "rt_upload_textures: texture %u has no pixels or a side of 0 / more than 32768", i);
+            return fail(c, RT_ERR_INVALID_ARGUMENT, b);
+        }
+    DeviceGuard g(c->device);
+    CU(c, cudaStreamSynchronize(c->stream));
+    free_textures(c);
+    std::vector<rt::TexDev> table(n);
+    for (uint32_t i = 0; i < n; i++) {
+        rt_ctx::Tex t{nullptr, 0, tex[i].width, tex[i].height};
+        cudaChannelFormatDesc fd = cudaCreateChannelDesc(8, 8, 8, 8, cudaChannelFormatKindUnsigned);
+        cudaError_t e = cudaMallocArray(&t.arr, &fd, t.w, t.h);
+        if (e == cudaSuccess) e = cudaMemcpy2DToArray(t.arr, 0, 0, tex[i].rgba8, (size_t)t.w * 4, (size_t)t.w * 4, t.h, cudaMemcpyHostToDevice);
+        if (e == cudaSuccess) {
+            cudaResourceDesc rd; memset(&rd, 0, sizeof rd);
+            rd.resType = cudaResourceTypeArray; rd.res.array.array = t.arr;
+            cudaTextureDesc td; memset(&td, 0, sizeof td);
+            td.addressMode[0] = td.addressMode[1] = cudaAddressModeClamp;   // wrap is done in the kernel (exact integer arithmetic)
+            td.filterMode = cudaFilterModePoint;                            // bilinear weights are applied in the kernel
+            td.readMode = cudaReadModeElementType; td.normalizedCoords = 0;
+            e = cudaCreateTextureObject(&t.obj, &rd, &td, nullptr);
+        }
+        if (e != cudaSuccess) {
+            if (t.arr) cudaFreeArray(t.arr);
+            free_textures(c);
+            return cuda_fail(c, e, "rt_upload_textures");
+        }
+        c->textures.push_back(t);
+        table[i].obj = t.obj; table[i].width = t.w; table[i].height = t.h;
+    }
+    if (n) {
+        CU(c, cudaMalloc((void**)&c->d_tex, n * sizeof(rt::TexDev)));
+        CU(c, cudaMemcpy(c->d_tex, table.data(), n * sizeof(rt::TexDev), cudaMemcpyHostToDevice));
+    }
     return RT_OK;
 }
 

@@ -38,7 +38,7 @@ __device__ __forceinline__ int fenc(float f) { int i = __float_as_int(f); return
 __device__ __forceinline__ float fdec(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7fffffff); }
 
 // one thread per primitive id: hot/cold records in id order, exact bounds, scene bounds
-__global__ void setup_prims(RawScene rs, float4* hot /*4 per id*/, float4* c0, float4* c1, float4* c2,
+__global__ void setup_prims(RawScene rs, float4* hot /*4 per id*/, float4* c0, float4* c1, float4* c2, float4* c3, float4* c4, float4* c5,
                             float4* bmin, float4* bmax, int* scene_bounds /*[6] encoded*/)
 {
     uint32_t id = blockIdx.x * blockDim.x + threadIdx.x;
@@ -54,6 +54,7 @@ __global__ void setup_prims(RawScene rs, float4* hot /*4 per id*/, float4* c0, f
             hot[4 * (size_t)id + 2] = hot[4 * (size_t)id + 3] = make_float4(0.f, 0.f, 0.f, 0.f);
             c0[id] = make_float4(c.x, c.y, c.z, __uint_as_float(id));
             c1[id] = c2[id] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (c3) c3[id] = c4[id] = c5[id] = make_float4(0.f, 0.f, 0.f, 0.f);
             float ar = fabsf(r);
             lo = f3(c.x - ar, c.y - ar, c.z - ar); hi = f3(c.x + ar, c.y + ar, c.z + ar);
         } else {
@@ -78,6 +79,11 @@ __global__ void setup_prims(RawScene rs, float4* hot /*4 per id*/, float4* c0, f
             c0[id] = make_float4(va.normal[0], va.normal[1], va.normal[2], __uint_as_float(rs.ns + a));
             c1[id] = make_float4(vb.normal[0], vb.normal[1], vb.normal[2], 0.f);
             c2[id] = make_float4(vc.normal[0], vc.normal[1], vc.normal[2], 0.f);
+            if (c3) {                                                   // texture extension: uvs + edges for the tangent frame
+                c3[id] = make_float4(va.tu, va.tv, vb.tu, vb.tv);
+                c4[id] = make_float4(vc.tu, vc.tv, e1.x, e1.y);
+                c5[id] = make_float4(e1.z, e2.x, e2.y, e2.z);
+            }
             lo = f3(fminf(A.x, fminf(B.x, C.x)), fminf(A.y, fminf(B.y, C.y)), fminf(A.z, fminf(B.z, C.z)));
             hi = f3(fmaxf(A.x, fmaxf(B.x, C.x)), fmaxf(A.y, fmaxf(B.y, C.y)), fmaxf(A.z, fmaxf(B.z, C.z)));
         }
@@ -100,12 +106,12 @@ __global__ void setup_materials(RawScene rs, float4* m0, float4* m1, float4* m2)
 {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= rs.ns + rs.nm) return;
-    const float* col; const float* emi; float str, smooth;
+    const float* col; const float* emi; float str, smooth; uint32_t dtex = 0, ntex = 0;
     if (i < rs.ns) { const rt_sphere& s = rs.spheres[i]; col = s.color; emi = s.emission_color; str = s.emission_strength; smooth = s.smoothness; }
-    else { const rt_mesh& m = rs.meshes[i - rs.ns]; col = m.color; emi = m.emission_color; str = m.emission_strength; smooth = m.specular; }
+    else { const rt_mesh& m = rs.meshes[i - rs.ns]; col = m.color; emi = m.emission_color; str = m.emission_strength; smooth = m.specular; dtex = m.diffuse_tex; ntex = m.normal_tex; }
     m0[i] = make_float4(col[0], col[1], col[2], col[3]);
     m1[i] = make_float4(emi[0] * str, emi[1] * str, emi[2] * str, emi[3] * str);   // wgsl:271
-    m2[i] = make_float4(smooth, 0.f, 0.f, 0.f);
+    m2[i] = make_float4(smooth, __uint_as_float(dtex), __uint_as_float(ntex), 0.f);
 }
 
 __device__ __forceinline__ uint64_t spread21(uint32_t v)
@@ -399,9 +405,9 @@ cudaError_t dalloc(T** p, size_t n) { return cudaMalloc((void**)p, (n ? n : 1) *
 
 void SceneBuffers::release()
 {
-    float4** ps[] = {&prims, &c0, &c1, &c2, &m0, &m1, &m2, &nodes};
+    float4** ps[] = {&prims, &c0, &c1, &c2, &c3, &c4, &c5, &m0, &m1, &m2, &nodes};
     for (auto p : ps) { if (*p) cudaFree(*p); *p = nullptr; }
-    n_prims = n_spheres = n_tris = n_mats = n_nodes = max_depth = 0; root = -1; max_abs = 0.f;
+    n_prims = n_spheres = n_tris = n_mats = n_nodes = max_depth = 0; root = -1; max_abs = 0.f; has_tex = false;
 }
 
 #define RT_TRY(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { err = e_; goto done; } } while (0)
@@ -443,6 +449,8 @@ cudaError_t build_scene(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns
     RT_TRY(dalloc(&out.c0, n)); RT_TRY(dalloc(&out.c1, n)); RT_TRY(dalloc(&out.c2, n));
     RT_TRY(dalloc(&out.m0, nmat)); RT_TRY(dalloc(&out.m1, nmat)); RT_TRY(dalloc(&out.m2, nmat));
     out.n_prims = n; out.n_spheres = ns; out.n_tris = nt; out.n_mats = nmat;
+    for (uint32_t m = 0; m < nm; m++) if (meshes[m].triangles && (meshes[m].diffuse_tex | meshes[m].normal_tex)) out.has_tex = true;
+    if (out.has_tex) { RT_TRY(dalloc(&out.c3, n)); RT_TRY(dalloc(&out.c4, n)); RT_TRY(dalloc(&out.c5, n)); }
     {
         RawScene rs{d_sph, d_vtx, d_idx, d_mesh, d_tstart, ns, nm, nt};
         if (nmat) setup_materials<<<(nmat + T - 1) / T, T, 0, stream>>>(rs, out.m0, out.m1, out.m2);
@@ -456,7 +464,7 @@ cudaError_t build_scene(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns
         RT_TRY(cudaMemcpyAsync(d_bounds, h_init, sizeof(h_init), cudaMemcpyHostToDevice, stream));
 
         const int nb = (n + T - 1) / T;
-        setup_prims<<<nb, T, 0, stream>>>(rs, hot, out.c0, out.c1, out.c2, bmin, bmax, d_bounds);
+        setup_prims<<<nb, T, 0, stream>>>(rs, hot, out.c0, out.c1, out.c2, out.c3, out.c4, out.c5, bmin, bmax, d_bounds);
         morton_keys<<<nb, T, 0, stream>>>(n, bmin, bmax, d_bounds, keys, ids);
         RT_TRY(cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, keys, keys2, ids, ids2, (int)n, 0, 63, stream));
         RT_TRY(cudaMalloc(&cub_tmp, cub_bytes ? cub_bytes : 1));

@@ -16,8 +16,14 @@
 //  cold, indexed by id, fetched once per path segment for the winning hit only:
 //    c0[id] = (nA.xyz, material index)  | sphere: (centre, material index)
 //    c1[id] = (nB.xyz, 0)  c2[id] = (nC.xyz, 0)
+//    texture extension (allocated only when a mesh carries a texture handle):
+//    c3[id] = (uvA.xy, uvB.xy)  c4[id] = (uvC.xy, e1.xy)  c5[id] = (e1.z, e2.xyz)
 //  materials, indexed by material index (sphere i -> i, mesh m -> S + m):
-//    m0 = color, m1 = emission_color * emission_strength, m2.x = smoothness
+//    m0 = color, m1 = emission_color * emission_strength,
+//    m2 = (smoothness, diffuse texture handle, normal-map handle, 0) (handles as int bits, 0 = none)
+//  textures: table of (cudaTextureObject_t, width, height); RGBA8 CUDA arrays fetched with
+//    point sampling through the texture path, bilinear weights applied in the kernel so the
+//    result is reproducible bit for bit (rt_shade.cuh).
 //  BVH nodes, 64 B each (both children's boxes live in the parent, one fetch = two tests):
 //    boxes as centre c / half extent h (rounded outward), which makes the slab test select-free:
 //    n[4*i+0] = (L.c.xyz, L.h.x)  n[4*i+1] = (L.h.yz, R.c.xy)
@@ -30,9 +36,13 @@
 
 namespace rt {
 
+struct TexDev { cudaTextureObject_t obj; uint32_t width, height; };
+
 struct SceneDev {
     const float4* prims;
     const float4* c0; const float4* c1; const float4* c2;
+    const float4* c3; const float4* c4; const float4* c5;   // texture extension, may be null
+    const struct TexDev* tex; uint32_t n_tex;
     const float4* m0; const float4* m1; const float4* m2;
     const float4* nodes;
     uint32_t n_prims;      // slots

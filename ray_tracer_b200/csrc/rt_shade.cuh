@@ -103,8 +103,71 @@ __device__ __forceinline__ uint32_t pixel_seed(uint32_t x, uint32_t y, uint32_t 
     return __float2uint_rz(lin) + af * 71939u;
 }
 
+// ---- texture extension (no reference counterpart; arithmetic specified by the oracle's
+// sample_texture / apply_textures) ----------------------------------------------------------
+// The four texels come through the texture path (CUDA array + texture object, point
+// sampling, unnormalised coordinates); wrap and the bilinear weights are computed here with
+// the contract's mix(), so the result does not depend on the texture unit's fixed-point
+// filtering.
+__device__ __forceinline__ int wrap_index(int i, int n) { int r = i % n; return r < 0 ? r + n : r; }
+__device__ __forceinline__ float4 fetch_texel(const TexDev& t, int ix, int iy)
+{
+    const uchar4 p = tex2D<uchar4>(t.obj, (float)ix + 0.5f, (float)iy + 0.5f);
+    const float k = 0.003921568859368563f;           // f32(1/255)
+    return make_float4((float)p.x * k, (float)p.y * k, (float)p.z * k, (float)p.w * k);
+}
+__device__ __forceinline__ float4 mix4(float4 a, float4 b, float t)
+{
+    return make_float4(mix1(a.x, b.x, t), mix1(a.y, b.y, t), mix1(a.z, b.z, t), mix1(a.w, b.w, t));
+}
+__device__ __forceinline__ float4 sample_texture(const TexDev& t, float u, float v)
+{
+    float x = __fmaf_rn(u, (float)t.width, -0.5f), y = __fmaf_rn(v, (float)t.height, -0.5f);
+    float x0 = floorf(x), y0 = floorf(y);
+    float fx = x - x0, fy = y - y0;
+    if (!(fabsf(x0) <= 1.0e9f)) { x0 = 0.0f; fx = 0.0f; }
+    if (!(fabsf(y0) <= 1.0e9f)) { y0 = 0.0f; fy = 0.0f; }
+    const int ix0 = wrap_index((int)x0, (int)t.width), iy0 = wrap_index((int)y0, (int)t.height);
+    const int ix1 = (ix0 + 1 == (int)t.width) ? 0 : ix0 + 1, iy1 = (iy0 + 1 == (int)t.height) ? 0 : iy0 + 1;
+    const float4 top = mix4(fetch_texel(t, ix0, iy0), fetch_texel(t, ix1, iy0), fx);
+    const float4 bot = mix4(fetch_texel(t, ix0, iy1), fetch_texel(t, ix1, iy1), fx);
+    return mix4(top, bot, fy);
+}
+// diffuse: mcolor *= texel; normal map: normal = normalize(T*n.x + B*n.y + N*n.z), n = 2*rgb - 1
+__device__ __noinline__ void apply_textures(const SceneDev& sc, uint32_t id, float bu, float bv, uint32_t dtex, uint32_t ntex,
+                                            float3& normal, float4& mcolor)
+{
+    const float4 k3 = __ldg(sc.c3 + id), k4 = __ldg(sc.c4 + id);
+    const float bw = (1.0f - bu) - bv;
+    const float tu = __fmaf_rn(k4.x, bv, __fmaf_rn(k3.z, bu, k3.x * bw));
+    const float tv = __fmaf_rn(k4.y, bv, __fmaf_rn(k3.w, bu, k3.y * bw));
+    if (ntex != 0u && ntex <= sc.n_tex) {
+        const float du1 = k3.z - k3.x, dv1 = k3.w - k3.y, du2 = k4.x - k3.x, dv2 = k4.y - k3.y;
+        const float det = __fmaf_rn(du1, dv2, -(du2 * dv1));
+        if (det != 0.0f && det == det) {
+            const float4 k5 = __ldg(sc.c5 + id);
+            const float3 e1 = f3(k4.z, k4.w, k5.x), e2 = f3(k5.y, k5.z, k5.w);
+            const float sg = sign1(det);
+            const float3 N = normal;
+            const float3 Traw = fma3(e2, -dv1, e1 * dv2) * sg;
+            const float3 Braw = fma3(e1, -du2, e2 * du1) * sg;
+            float3 T = fma3(N, -dot3(N, Traw), Traw);
+            if (dot3(T, T) > 0.0f) {
+                T = normalize3(T);
+                float3 Bt = cross3(N, T);
+                Bt = Bt * sign1(dot3(Bt, Braw));
+                const float4 tx = sample_texture(sc.tex[ntex - 1u], tu, tv);
+                const float nx = __fmaf_rn(tx.x, 2.0f, -1.0f), ny = __fmaf_rn(tx.y, 2.0f, -1.0f), nz = __fmaf_rn(tx.z, 2.0f, -1.0f);
+                normal = normalize3(fma3(N, nz, fma3(Bt, ny, T * nx)));
+            }
+        }
+    }
+    if (dtex != 0u && dtex <= sc.n_tex) mcolor = mcolor * sample_texture(sc.tex[dtex - 1u], tu, tv);
+}
+
 // One path segment's shading (wgsl:236-273). Consumes RNG exactly as the reference does and
 // replaces the ray by the bounce ray.
+template <bool TEX>
 __device__ __forceinline__ void shade_hit(const SceneDev& sc, const HitRec& hit, float3& ro, float3& rd, uint32_t& rng,
                                           float4& incoming, float4& color)
 {
@@ -120,7 +183,12 @@ __device__ __forceinline__ void shade_hit(const SceneDev& sc, const HitRec& hit,
     }
     const uint32_t mi = __float_as_uint(k0.w);
     float4 mcolor = __ldg(sc.m0 + mi), emitted = __ldg(sc.m1 + mi);
-    const float smooth = __ldg(sc.m2 + mi).x;
+    const float4 mat2 = __ldg(sc.m2 + mi);
+    const float smooth = mat2.x;
+    if (TEX && hit.id >= sc.n_spheres) {
+        const uint32_t dtex = __float_as_uint(mat2.y), ntex = __float_as_uint(mat2.z);
+        if ((dtex | ntex) != 0u) apply_textures(sc, hit.id, hit.u, hit.v, dtex, ntex, normal, mcolor);
+    }
     float3 unit_dir = normalize3(rd);
     float3 nd;
     if (smooth == -1.0f) {                       // glass, wgsl:240-264

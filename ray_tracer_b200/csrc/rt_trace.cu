@@ -46,7 +46,7 @@ namespace rt {
 // others keep their traversal state (node, stack, closest hit) across the switch.
 #define RT_EMPTY 0x7fffffff                        // "no current node": traversal stack exhausted
 
-template <bool BRUTE, bool DETAIL>
+template <bool BRUTE, bool DETAIL, bool TEX>
 __global__ void __launch_bounds__(RT_BLOCK_THREADS, RT_MIN_BLOCKS)
 trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ staging,
              uint32_t* __restrict__ primary_ids, unsigned long long* __restrict__ counters,
@@ -95,7 +95,7 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
                     bool done;
                     if (best.id != RT_MISS) {
                         if (DETAIL) n_hits++;
-                        shade_hit(sc, best, ro, rd, rng, incoming, color);
+                        shade_hit<TEX>(sc, best, ro, rd, rng, incoming, color);
                         seg++;
                         done = seg > lp.bounces;
                     } else {
@@ -322,16 +322,21 @@ __global__ void blend_kernel(LaunchParams lp, const float4* __restrict__ staging
     accum[pix] = acc;
 }
 
-static const size_t kTraceSmem = 0;
+namespace {
+typedef void (*TraceFn)(SceneDev, CameraDev, LaunchParams, float4*, uint32_t*, unsigned long long*, unsigned long long*);
+TraceFn trace_variant(bool brute, bool detail, bool tex)
+{
+    static const TraceFn table[8] = {
+        trace_kernel<false, false, false>, trace_kernel<false, false, true>, trace_kernel<false, true, false>, trace_kernel<false, true, true>,
+        trace_kernel<true, false, false>,  trace_kernel<true, false, true>,  trace_kernel<true, true, false>,  trace_kernel<true, true, true>};
+    return table[(brute ? 4 : 0) | (detail ? 2 : 0) | (tex ? 1 : 0)];
+}
+} // namespace
 
-int trace_blocks_per_sm(bool brute, bool detail)
+int trace_blocks_per_sm(bool brute, bool detail, bool tex)
 {
     int n = 0;
-    cudaError_t e;
-    if (brute) e = detail ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, trace_kernel<true, true>, RT_BLOCK_THREADS, kTraceSmem)
-                          : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, trace_kernel<true, false>, RT_BLOCK_THREADS, kTraceSmem);
-    else e = detail ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, trace_kernel<false, true>, RT_BLOCK_THREADS, kTraceSmem)
-                    : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, trace_kernel<false, false>, RT_BLOCK_THREADS, kTraceSmem);
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, trace_variant(brute, detail, tex), RT_BLOCK_THREADS, 0);
     return (e == cudaSuccess && n > 0) ? n : 1;
 }
 
@@ -342,18 +347,13 @@ cudaError_t launch_trace(const SceneDev& sc, const CameraDev& cam, const LaunchP
     if (lp.n_warp_tiles == 0 || lp.n_frames == 0) return cudaSuccess;
     cudaError_t e = cudaMemsetAsync(queue, 0, sizeof(unsigned long long), stream);
     if (e != cudaSuccess) return e;
+    const bool tex = sc.c3 != nullptr && sc.n_tex != 0u;       // texture code only when the scene carries handles and a table is bound
     const uint64_t warps_needed = ((uint64_t)lp.n_warp_tiles * lp.n_frames * 32ull + RT_QUEUE_CHUNK - 1) / RT_QUEUE_CHUNK;
-    uint64_t blocks = (uint64_t)n_sms * trace_blocks_per_sm(brute, detail);
+    uint64_t blocks = (uint64_t)n_sms * trace_blocks_per_sm(brute, detail, tex);
     const uint64_t cap = (warps_needed + RT_BLOCK_THREADS / 32 - 1) / (RT_BLOCK_THREADS / 32);
     if (blocks > cap) blocks = cap;
     dim3 grid((unsigned)blocks), block(RT_BLOCK_THREADS);
-    if (brute) {
-        if (detail) trace_kernel<true, true><<<grid, block, kTraceSmem, stream>>>(sc, cam, lp, staging, primary_ids, counters, queue);
-        else trace_kernel<true, false><<<grid, block, kTraceSmem, stream>>>(sc, cam, lp, staging, primary_ids, counters, queue);
-    } else {
-        if (detail) trace_kernel<false, true><<<grid, block, kTraceSmem, stream>>>(sc, cam, lp, staging, primary_ids, counters, queue);
-        else trace_kernel<false, false><<<grid, block, kTraceSmem, stream>>>(sc, cam, lp, staging, primary_ids, counters, queue);
-    }
+    trace_variant(brute, detail, tex)<<<grid, block, 0, stream>>>(sc, cam, lp, staging, primary_ids, counters, queue);
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
     const size_t n_local = (size_t)lp.n_warp_tiles * 32u;
     blend_kernel<<<(unsigned)((n_local + 255) / 256), 256, 0, stream>>>(lp, staging, accum);

@@ -106,8 +106,9 @@ class Camera:
 class Scene:
     """scene.rs:94-100: camera uniform + the four arrays."""
 
-    def __init__(self, camera, spheres, vertices, indices, meshes):
+    def __init__(self, camera, spheres, vertices, indices, meshes, textures=None):
         self.camera = camera            # Camera, or a CAMERA_DT uniform for builtin scenes
+        self.textures = list(textures or [])   # texture extension: (H, W, 4) uint8 arrays, addressed by the 1-based Mesh handles
         self.spheres = np.ascontiguousarray(spheres, dtype=SPHERE_DT).reshape(-1)
         self.vertices = np.ascontiguousarray(vertices, dtype=VERTEX_DT).reshape(-1)
         self.indices = np.ascontiguousarray(indices, dtype=np.uint32).reshape(-1)

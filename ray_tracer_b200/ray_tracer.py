@@ -70,6 +70,21 @@ class RayTracer:
         self._ck(self._L.rt_upload_scene(self._h, _ptr(sp), sp.size, _ptr(vs), vs.size, _ptr(ix), ix.size,
                                          _ptr(ms), ms.size))
 
+    # -- texture extension (no reference counterpart) ------------------------------------
+    def upload_textures(self, textures):
+        """textures: list of (H, W, 4) uint8 arrays (row 0 first); handles in Mesh.diffuse_tex /
+        normal_tex are 1-based indices into this list."""
+        from ._lib import Texture
+        keep = [np.ascontiguousarray(t, dtype=np.uint8) for t in textures]
+        for t in keep:
+            if t.ndim != 3 or t.shape[2] != 4:
+                raise ValueError("textures must be (H, W, 4) uint8")
+        arr = (Texture * max(1, len(keep)))()
+        for i, t in enumerate(keep):
+            arr[i] = Texture(t.shape[1], t.shape[0], t.ctypes.data)
+        import ctypes as C
+        self._ck(self._L.rt_upload_textures(self._h, C.cast(arr, C.c_void_p), len(keep)))
+
     # -- bindings 0,1: uniforms (context.rs:185-186) -----------------------------------
     def set_camera(self, camera_uniform):
         cu = np.ascontiguousarray(camera_uniform, dtype=CAMERA_DT).reshape(1)

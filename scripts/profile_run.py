@@ -9,7 +9,7 @@ h = int(sys.argv[4]) if len(sys.argv) > 4 else None
 scene, meta = configs.build(name, w, h)
 p = meta["params"]
 tr = rt.RayTracer(0, p["width"], p["height"])
-tr.upload_scene(*scene.arrays()); tr.set_camera(scene.camera_uniform()); tr.set_params(**p)
+tr.upload_scene(*scene.arrays()); tr.upload_textures(scene.textures); tr.set_camera(scene.camera_uniform()); tr.set_params(**p)
 tr.set_option(rt._lib.RT_OPT_FRAMES_PER_LAUNCH, frames)
 tr.render_frames(0, frames); tr.sync(); tr.reset_counters()
 tr.render_frames(0, frames); tr.sync()

@@ -7,7 +7,7 @@ name, frames = sys.argv[1], int(sys.argv[2])
 scene, meta = configs.build(name)
 p = meta["params"]
 tr = rt.RayTracer(0, p["width"], p["height"])
-tr.upload_scene(*scene.arrays()); tr.set_camera(scene.camera_uniform()); tr.set_params(**p)
+tr.upload_scene(*scene.arrays()); tr.upload_textures(scene.textures); tr.set_camera(scene.camera_uniform()); tr.set_params(**p)
 tr.set_option(rt._lib.RT_OPT_FRAMES_PER_LAUNCH, frames)
 combos = [(n, 1, s) for n in (4, 8, 12, 16) for s in (16, 20, 22, 24, 28)]
 if len(sys.argv) > 3:

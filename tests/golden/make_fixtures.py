@@ -14,8 +14,10 @@ Sources and licences (credits required by the licences):
   simple_japanese_tree.glb "Simple Japanese Tree" by Leonardo Camilo Ribeiro (sketchfab.com/leoCamilo),
                            CC-BY-4.0, https://sketchfab.com/3d-models/simple-japanese-tree-07073d2c174343ad86b7c53bc30055e0
   cube.obj                 Blender-exported rounded cube shipped with the reference (no licence stated)
-Only positions, normals and indices are kept (no textures); used for non-commercial
-benchmarking and testing.
+  cobble-diffuse.png / cobble-normal.png  1024^2 RGBA textures shipped with the reference (no licence
+                           stated; referenced by nothing upstream), box-filtered to 256^2 -> cobble_256.npz
+Positions, normals and indices are kept; for cube.obj also the texture coordinates (texture
+extension, config C2).  Used for non-commercial benchmarking and testing.
 """
 import hashlib
 import os
@@ -30,11 +32,12 @@ from oracle import host_ref  # noqa: E402
 ASSETS = "/root/reference/assets"
 
 
-def dump(name, vs, ix, ms):
+def dump(name, vs, ix, ms, uv=False):
     v, i, m = host_ref.concat_model(vs, ix, ms)
     out = os.path.join(HERE, name + ".npz")
+    extra = {"uv": np.stack([v[v.dtype.names[1]], v[v.dtype.names[3]]], axis=1)} if uv else {}
     np.savez_compressed(out, pos=v["pos"], normal=v["normal"], indices=i,
-                        first=m["first"], triangles=m["triangles"], offset=m["offset"])
+                        first=m["first"], triangles=m["triangles"], offset=m["offset"], **extra)
     h = hashlib.sha256(v.tobytes() + i.tobytes() + m.tobytes()).hexdigest()[:16]
     print("%s: %d vertices, %d indices, %d meshes, %d triangles, %d bytes, sha256[:16]=%s" %
           (name, len(v), len(i), len(m), int(m["triangles"].sum()), os.path.getsize(out), h))
@@ -46,5 +49,13 @@ if __name__ == "__main__":
         host_ref.load_model_glb(open(os.path.join(ASSETS, fn), "rb").read(), vs, ix, ms)
         dump(name, vs, ix, ms)
     vs, ix, ms = [], [], []
-    host_ref.load_model_obj(open(os.path.join(ASSETS, "cube.obj")).read(), vs, ix, ms)
-    dump("cube_obj", vs, ix, ms)
+    host_ref.load_model_obj(open(os.path.join(ASSETS, "cube.obj")).read(), vs, ix, ms, keep_uv=True)
+    dump("cube_obj", vs, ix, ms, uv=True)
+    from PIL import Image
+    tex = {}
+    for key, fn in (("diffuse", "cobble-diffuse.png"), ("normal", "cobble-normal.png")):
+        im = Image.open(os.path.join(ASSETS, fn)).convert("RGBA").resize((256, 256), Image.BOX)
+        tex[key] = np.asarray(im, np.uint8)
+    out = os.path.join(HERE, "cobble_256.npz")
+    np.savez_compressed(out, **tex)
+    print("cobble_256: %d bytes, sha256[:16]=%s" % (os.path.getsize(out), hashlib.sha256(tex["diffuse"].tobytes() + tex["normal"].tobytes()).hexdigest()[:16]))

@@ -19,7 +19,8 @@ CASES = {
     "room": ("builtin", 32, 24, 2, 4, 1, 0, 0),
     "metal": ("builtin", 32, 24, 2, 6, 2, 1, 0),
     "random_balls": ("builtin", 24, 16, 1, 4, 1, 1, 0),
-    "c2_cube": ("config", 32, 18, 1, 8, 1, 1, 0),
+    "c2_cube": ("config", 32, 18, 1, 8, 1, 1, 0),           # texture extension: cobble diffuse + normal map
+    "c2_cube_plain": ("config", 32, 18, 1, 8, 1, 1, 0),     # (was "c2_cube" before the extension: same bits)
     "c3_teapot": ("config", 32, 18, 1, 8, 1, 1, 0),
     "c4_tree": ("config", 32, 18, 1, 8, 1, 1, 0),
 }
@@ -35,12 +36,19 @@ def scene_for(name, kind, w, h):
     return (t[0].view(ro.CAMERA_DT), t[1].view(ro.SPHERE_DT), t[2].view(ro.VERTEX_DT), t[3], t[4].view(ro.MESH_DT))
 
 
+def textures_for(name, kind):
+    if not kind.startswith("config"):
+        return []
+    from ray_tracer_b200 import configs
+    return configs.build(name, 8, 8)[0].textures
+
+
 def render_case(name):
     from oracle import rt_oracle as ro
     kind, w, h, frames, bounces, rpp, sky, first = CASES[name]
     ids = np.full((h, w), 0xFFFFFFFF, np.uint32)
     ctr = np.zeros(3, np.uint64)
-    img = ro.render(scene_for(name, kind, w, h), w, h, frames, bounces, rpp, sky, first, ids, ctr)
+    img = ro.render(scene_for(name, kind, w, h), w, h, frames, bounces, rpp, sky, first, ids, ctr, textures=textures_for(name, kind))
     return img, ids, int(ctr[0])
 
 

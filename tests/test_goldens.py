@@ -30,6 +30,7 @@ def test_cuda_reproduces_goldens(rtlib, name):
     cam, sp, vs, ix, ms = gold.scene_for(name, kind, w, h)
     tr = rtlib.RayTracer(0, w, h)
     tr.upload_scene(sp, vs, ix, ms)
+    tr.upload_textures(gold.textures_for(name, kind))
     tr.set_camera(cam)
     tr.set_params(number_of_bounces=bounces, rays_per_pixel=rpp, skybox=sky, frames=first)
     tr.set_option(rtlib._lib.RT_OPT_PRIMARY_IDS, 1)

@@ -19,6 +19,8 @@ def _gpu(rt, scene, w, h, frames, bounces, sky, brute=False, leaf=None, builder=
     if radius is not None:
         tr.set_option(rt._lib.RT_OPT_PLOC_RADIUS, radius)
     tr.upload_scene(sp, vs, ix, ms)
+    if scene.textures:
+        tr.upload_textures(scene.textures)
     tr.set_camera(cam)
     tr.set_params(number_of_bounces=bounces, rays_per_pixel=1, skybox=sky, frames=0)
     tr.set_option(rt._lib.RT_OPT_PRIMARY_IDS, 1)
@@ -34,10 +36,10 @@ def _cpu(oracle, scene, w, h, frames, bounces, sky):
     sc = (cam.view(oracle.CAMERA_DT), sp.view(oracle.SPHERE_DT), vs.view(oracle.VERTEX_DT), ix, ms.view(oracle.MESH_DT))
     ids = np.full((h, w), 0xFFFFFFFF, np.uint32)
     ctr = np.zeros(3, np.uint64)
-    return oracle.render(sc, w, h, frames, bounces, 1, sky, 0, ids, ctr), ids, ctr
+    return oracle.render(sc, w, h, frames, bounces, 1, sky, 0, ids, ctr, textures=scene.textures), ids, ctr
 
 
-@pytest.mark.parametrize("name,w,h,frames", [("c2_cube", 160, 90, 2), ("c3_teapot", 96, 54, 1), ("c4_tree", 96, 54, 1)])
+@pytest.mark.parametrize("name,w,h,frames", [("c2_cube", 160, 90, 2), ("c2_cube_plain", 160, 90, 2), ("c3_teapot", 96, 54, 1), ("c4_tree", 96, 54, 1)])
 def test_config_vs_oracle(rtlib, oracle, name, w, h, frames):
     from ray_tracer_b200 import configs
     scene, meta = configs.build(name, w, h)
