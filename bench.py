@@ -4,7 +4,8 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config c3_teapot]
 
 Metric: Mrays/s (all bounces) on config C3 — the Utah teapot (15,704 triangles), 1920x1080,
-256 spp (= 128 progressive dispatches at rays_per_pixel = 1), 8 bounces, LBVH.  A "ray" is
+256 spp (= 128 progressive dispatches at rays_per_pixel = 1), 8 bounces, GPU-built BVH
+(PLOC over Morton order).  A "ray" is
 one path segment = one call of calculate_ray_collions in the reference (wgsl:234), counted
 on the device.  One step = the whole 256-spp render.  N > 1 (torchrun, one rank per GPU):
 sample-index sharding, every rank renders its own 256 spp (frames = rank mod N, weak
@@ -46,6 +47,19 @@ def peaks():
             return json.load(f), "measured"
     except Exception:
         return {"hbm_gbs": 6650.0, "sm_max_mhz": 1965.0}, "fallback"
+
+
+def ncu_traffic(config):
+    """DRAM bytes (read + write) of one trace-kernel launch from the committed `ncu --set full`
+    capture of this workload (profiles/*_traffic.json), or None when there is none."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "trace_kernel_traffic.json")) as f:
+            t = json.load(f).get(config)
+        return None if t is None else {"dram_bytes_per_launch": t["dram_read_bytes"] + t["dram_write_bytes"],
+                                       "dram_read_bytes": t["dram_read_bytes"], "dram_write_bytes": t["dram_write_bytes"],
+                                       "dispatches_per_launch": t["dispatches_per_launch"], "source": t["source"]}
+    except Exception:
+        return None
 
 
 class ClockSampler:
@@ -180,6 +194,7 @@ def run_ours(args, rank, world, local_rank):
 
     tr = rt.RayTracer(dev, W, H)
     tr.upload_scene(sp, vs, ix, ms)
+    tr.upload_textures(scene.textures)
     tr.set_camera(cam)
     tr.set_params(**p)
     tr.set_shard(0, 1, rank, world)              # sample-index sharding: frames = rank (mod world)
@@ -295,7 +310,7 @@ def run_ours(args, rank, world, local_rank):
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": args.config, "width": W, "height": H, "spp_per_gpu": meta["spp"], "dispatches_per_gpu": D,
                        "bounces": p["number_of_bounces"], "rays_per_pixel": p["rays_per_pixel"], "skybox": p["skybox"],
-                       "triangles": int(ms["triangles"].sum()), "spheres": int(sp.size), "traversal": "lbvh",
+                       "triangles": int(ms["triangles"].sum()), "spheres": int(sp.size), "traversal": "bvh2 (PLOC over 63-bit Morton order, GPU-built)", "textures": len(scene.textures),
                        "parallelism": "sample-index sharding x%d + NCCL all-reduce per step" % world if world > 1 else "single GPU",
                        "l2": "256 MiB write between timed steps (untimed); scene+BVH are L2-resident by design",
                        "spp_per_s": meta["spp"] * world / (ms_total / max(args.steps, 1) * 1e-3)},
@@ -304,10 +319,10 @@ def run_ours(args, rank, world, local_rank):
                     "steps": e2e_steps, "what": "rt_upload_scene (host records -> SoA + LBVH build) + rt_render_frames + rt_read_accum, wall clock"},
             "gpu_launches": int(ctr["launches"]),
             "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak_tf.value, "unit": "TFLOP/s",
-                         "frac": achieved / peak_tf.value if peak_tf.value else None, "traffic": None,
+                         "frac": achieved / peak_tf.value if peak_tf.value else None, "traffic": ncu_traffic(args.config),
                          "peak_source": "FFMA microbenchmark run in this process (rt_measure_fp32_peak); theoretical 148x128x2x%.0f MHz = %.1f" % (
                              pk.get("sm_max_mhz", 1965.0), 148 * 128 * 2 * pk.get("sm_max_mhz", 1965.0) * 1e6 / 1e12),
-                         "kernel": "rt::trace_kernel<false,false>", "launch_ms": launch_s * 1e3,
+                         "kernel": "rt::trace_kernel<BRUTE=false,DETAIL=false,TEX=%s>" % ("true" if scene.textures else "false"), "launch_ms": launch_s * 1e3,
                          "flops_per_launch": flops_step / launches_per_step,
                          "per_ray": {"node_visits": det["node_visits"] / det["rays"], "tri_tests": det["tri_tests"] / det["rays"],
                                      "sphere_tests": det["sphere_tests"] / det["rays"], "hit_fraction": det["hit_segments"] / det["rays"]},

@@ -353,3 +353,54 @@ def concat_model(vertices, indices, meshes):
     def cat(lst, dt):
         return np.concatenate(lst) if lst else np.zeros(0, dt)
     return cat(vertices, VERTEX_DT), cat(indices, np.uint32), cat(meshes, MESH_DT)
+
+
+# ---- fly-cam (camera.rs:122-247) -------------------------------------------------------
+def controller_new(speed=3.0, sensitivity=0.35):
+    """CameraController::new (camera.rs:184-198; Camera::new passes 3.0, 0.35 — :57)."""
+    z = np.float32(0.0)
+    return dict(amount_left=z, amount_right=z, amount_forward=z, amount_backward=z, amount_up=z, amount_down=z,
+                rotate_horizontal=z, rotate_vertical=z, scroll=z, speed=np.float32(speed), sensitivity=np.float32(sensitivity))
+
+
+def process_keyboard(c, key, pressed):
+    """camera.rs:201-232."""
+    amount = np.float32(5.0 if pressed else 0.0)
+    field = {"W": "amount_forward", "Up": "amount_forward", "S": "amount_backward", "Down": "amount_backward",
+             "A": "amount_left", "Left": "amount_left", "D": "amount_right", "Right": "amount_right",
+             "Space": "amount_up", "LShift": "amount_down"}.get(key)
+    if field is None:
+        return False
+    c[field] = amount
+    return True
+
+
+def update_camera(origin, look_at, c, dt):
+    """camera.rs:122-165 in float32; transcendentals through float64 libm rounded to f32 (the
+    Rust f32 methods call the platform libm: last-ulp differences are possible)."""
+    f = np.float32
+    origin, look_at, dt = np.asarray(origin, f).copy(), np.asarray(look_at, f), f(dt)
+    safe_deg = f((f(np.pi / 2) - f(0.0001)) * (f(180.0) / f(np.pi)))
+    d = look_at - origin
+    d = d * (f(1.0) / np.sqrt(f(d[0] * d[0] + d[1] * d[1] + d[2] * d[2])))
+    pitch, yaw = f(np.arcsin(np.float64(d[1]))), f(np.arctan2(np.float64(d[0]), np.float64(d[2])))
+    ys, yc = f(np.sin(np.float64(yaw))), f(np.cos(np.float64(yaw)))
+
+    def unit(v):
+        v = np.asarray(v, f)
+        return v * (f(1.0) / np.sqrt(f(v[0] * v[0] + v[1] * v[1] + v[2] * v[2])))
+    forward, right = unit([ys, 0.0, yc]), unit([yc, 0.0, -ys])
+    origin = origin + forward * (c["amount_forward"] - c["amount_backward"]) * c["speed"] * dt
+    origin = origin + right * (c["amount_right"] - c["amount_left"]) * c["speed"] * dt
+    ps, pc = f(np.sin(np.float64(pitch))), f(np.cos(np.float64(pitch)))
+    scrollward = unit([pc * yc, ps, pc * ys])                       # x/z swapped upstream (camera.rs:141)
+    origin = origin - scrollward * c["scroll"] * c["speed"] * c["sensitivity"] * dt
+    c["scroll"] = f(0.0)
+    origin[1] = origin[1] + (c["amount_up"] - c["amount_down"]) * c["speed"] * dt
+    yaw = f(yaw + c["rotate_horizontal"] * c["sensitivity"] * dt)
+    pitch = f(pitch + -c["rotate_vertical"] * c["sensitivity"] * dt)
+    c["rotate_horizontal"] = c["rotate_vertical"] = f(0.0)
+    pitch = min(max(pitch, -safe_deg), safe_deg)                   # never fires: radians vs a degrees constant
+    cp, sp_, sy, cy = (f(np.cos(np.float64(pitch))), f(np.sin(np.float64(pitch))), f(np.sin(np.float64(yaw))), f(np.cos(np.float64(yaw))))
+    look_at = origin + np.array([cp * sy, sp_, cp * cy], f)
+    return origin.astype(f), look_at.astype(f)

@@ -203,6 +203,10 @@ int rt_create(rt_ctx** out, int device, uint32_t width, uint32_t height)
     int rc = RT_OK;
     do {
         if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) { rc = cuda_fail(nullptr, e, "cudaStreamCreate"); break; }
+        {   // scene uploads allocate stream-ordered from the default pool: keep freed blocks cached for the next upload
+            cudaMemPool_t pool; unsigned long long keep = ~0ull;
+            if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        }
         if ((e = cudaMalloc((void**)&c->d_counters, 6 * sizeof(unsigned long long))) != cudaSuccess) { rc = cuda_fail(nullptr, e, "cudaMalloc counters"); break; }
         if ((e = cudaMemsetAsync(c->d_counters, 0, 6 * sizeof(unsigned long long), c->stream)) != cudaSuccess) { rc = cuda_fail(nullptr, e, "memset counters"); break; }
         if ((e = cudaMalloc((void**)&c->d_queue, sizeof(unsigned long long))) != cudaSuccess) { rc = cuda_fail(nullptr, e, "cudaMalloc queue"); break; }

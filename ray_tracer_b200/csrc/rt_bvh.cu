@@ -398,15 +398,18 @@ __global__ void emit_single(const float4* lmin, const float4* lmax, float4* node
     nodes[3] = make_float4(__int_as_float(~0), __int_as_float(~0), 0.f, 0.f);
 }
 
+// Stream-ordered allocation from the device's default pool (rt_create raises its release
+// threshold, so repeated uploads reuse the same blocks instead of paying cudaMalloc/cudaFree).
+static thread_local cudaStream_t g_alloc_stream = nullptr;
 template <typename T>
-cudaError_t dalloc(T** p, size_t n) { return cudaMalloc((void**)p, (n ? n : 1) * sizeof(T)); }
+cudaError_t dalloc(T** p, size_t n) { return cudaMallocAsync((void**)p, (n ? n : 1) * sizeof(T), g_alloc_stream); }
 
 } // namespace
 
 void SceneBuffers::release()
 {
     float4** ps[] = {&prims, &c0, &c1, &c2, &c3, &c4, &c5, &m0, &m1, &m2, &nodes};
-    for (auto p : ps) { if (*p) cudaFree(*p); *p = nullptr; }
+    for (auto p : ps) { if (*p) cudaFreeAsync(*p, stream); *p = nullptr; }
     n_prims = n_spheres = n_tris = n_mats = n_nodes = max_depth = 0; root = -1; max_abs = 0.f; has_tex = false;
 }
 
@@ -417,6 +420,8 @@ cudaError_t build_scene(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns
                         uint32_t leaf_size, int builder, int ploc_radius, cudaStream_t stream)
 {
     out.release();
+    out.stream = stream;
+    g_alloc_stream = stream;
     cudaError_t err = cudaSuccess;
     std::vector<uint32_t> tri_start(nm + 1, 0);
     for (uint32_t m = 0; m < nm; m++) tri_start[m + 1] = tri_start[m] + meshes[m].triangles;
@@ -467,7 +472,7 @@ cudaError_t build_scene(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns
         setup_prims<<<nb, T, 0, stream>>>(rs, hot, out.c0, out.c1, out.c2, out.c3, out.c4, out.c5, bmin, bmax, d_bounds);
         morton_keys<<<nb, T, 0, stream>>>(n, bmin, bmax, d_bounds, keys, ids);
         RT_TRY(cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, keys, keys2, ids, ids2, (int)n, 0, 63, stream));
-        RT_TRY(cudaMalloc(&cub_tmp, cub_bytes ? cub_bytes : 1));
+        RT_TRY(cudaMallocAsync(&cub_tmp, cub_bytes ? cub_bytes : 1, stream));
         RT_TRY(cub::DeviceRadixSort::SortPairs(cub_tmp, cub_bytes, keys, keys2, ids, ids2, (int)n, 0, 63, stream));
         gather_boxes<<<nb, T, 0, stream>>>(n, ids2, bmin, bmax, lmin, lmax);
         if (n == 1) {
@@ -484,7 +489,7 @@ cudaError_t build_scene(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns
                 RT_TRY(dalloc(&cloA, n)); RT_TRY(dalloc(&chiA, n)); RT_TRY(dalloc(&cloB, n)); RT_TRY(dalloc(&chiB, n));
                 RT_TRY(dalloc(&pflags, n)); RT_TRY(dalloc(&ppos, n)); RT_TRY(dalloc(&d_tot, 2));
                 RT_TRY(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, pflags, ppos, (int)n, stream));
-                RT_TRY(cudaMalloc(&scan_tmp, scan_bytes ? scan_bytes : 1));
+                RT_TRY(cudaMallocAsync(&scan_tmp, scan_bytes ? scan_bytes : 1, stream));
                 ploc_init<<<nb, T, 0, stream>>>((int)n, lmin, lmax, cidA, cloA, chiA);
                 int m = (int)n, node_base = 0, force = 0;
                 while (m > 1) {
@@ -537,7 +542,7 @@ done:
         void* tmp[] = {d_sph, d_vtx, d_idx, d_mesh, d_tstart, hot, bmin, bmax, lmin, lmax, imin, imax, d_bounds,
                        keys, keys2, ids, ids2, children, ranges, pin, plf, flags, d_depth, cub_tmp, new_slot,
                        cidA, cidB, nn, cloA, chiA, cloB, chiB, pflags, ppos, d_tot, scan_tmp};
-        for (void* p : tmp) if (p) cudaFree(p);
+        for (void* p : tmp) if (p) cudaFreeAsync(p, stream);
     }
     if (err != cudaSuccess) out.release();
     return err;

@@ -30,6 +30,7 @@ struct SceneBuffers {
     float4 *c0 = nullptr, *c1 = nullptr, *c2 = nullptr;
     float4 *c3 = nullptr, *c4 = nullptr, *c5 = nullptr;   // texture extension (uvs + edges), only when has_tex
     bool has_tex = false;
+    cudaStream_t stream = nullptr;  // the arrays are stream-ordered allocations on this stream
     float4 *m0 = nullptr, *m1 = nullptr, *m2 = nullptr;
     float4* nodes = nullptr;
     uint32_t n_prims = 0, n_spheres = 0, n_tris = 0, n_mats = 0, n_nodes = 0, max_depth = 0;

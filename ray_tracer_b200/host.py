@@ -60,6 +60,29 @@ def hostlib():
         L.rth_context_read_texture.argtypes = [vp, vp, C.c_size_t]
         L.rth_context_handle.argtypes = [vp]
         L.rth_context_handle.restype = vp
+        # fly-cam / input / display (camera.rs:122-247, context.rs:148-175, render.wgsl)
+        L.rth_context_update_dt.argtypes = [vp, f32]
+        L.rth_context_input_key.argtypes = [vp, C.c_int, C.c_int]
+        L.rth_context_input_scroll_lines.argtypes = [vp, f32]
+        L.rth_context_input_mouse_button.argtypes = [vp, C.c_int]
+        L.rth_context_input_other.argtypes = [vp]
+        L.rth_context_mouse_motion.argtypes = [vp, C.c_double, C.c_double]
+        L.rth_context_get_camera.argtypes = [vp, vp]
+        L.rth_context_save_png.argtypes = [vp, C.c_char_p, C.c_int]
+        L.rth_camera_update.argtypes = [vp, f32]
+        L.rth_controller_key.argtypes = [vp, C.c_int, C.c_int]
+        # texture-extension loaders and PNG i/o
+        L.rth_scene_from_model_uv.argtypes = [C.c_char_p]
+        L.rth_scene_from_model_uv.restype = vp
+        L.rth_png_load.argtypes = [C.c_char_p, C.POINTER(u32), C.POINTER(u32)]
+        L.rth_png_load.restype = vp
+        L.rth_image_copy.argtypes = [vp, vp]
+        L.rth_image_free.argtypes = [vp]
+        L.rth_png_write.argtypes = [C.c_char_p, vp, u32, u32]
+        L.rth_glb_images.argtypes = [C.c_char_p, C.POINTER(u32)]
+        L.rth_glb_images.restype = vp
+        L.rth_glb_image.argtypes = [vp, u32, C.POINTER(u32), C.POINTER(u32), vp]
+        L.rth_glb_images_free.argtypes = [vp]
         _hl = L
     return _hl
 
@@ -163,6 +186,70 @@ def load_model(path):
     return s.vertices, s.indices, s.meshes
 
 
+def load_model_uv(path):
+    """Texture extension: load_model that keeps `vt` / TEXCOORD_0 in the Vertex padding words."""
+    s = Scene._from_handle(hostlib().rth_scene_from_model_uv(os.fsencode(path)))
+    return s.vertices, s.indices, s.meshes
+
+
+def load_png(path):
+    """-> (H, W, 4) uint8, row 0 = top row (C++ decoder over zlib; no interlace)."""
+    L = hostlib()
+    w, h = C.c_uint32(), C.c_uint32()
+    im = L.rth_png_load(os.fsencode(path), C.byref(w), C.byref(h))
+    if not im:
+        raise _err()
+    try:
+        out = np.empty((h.value, w.value, 4), np.uint8)
+        L.rth_image_copy(im, _ptr(out))
+    finally:
+        L.rth_image_free(im)
+    return out
+
+
+def write_png(path, rgba):
+    rgba = np.ascontiguousarray(rgba, dtype=np.uint8)
+    assert rgba.ndim == 3 and rgba.shape[2] == 4
+    if hostlib().rth_png_write(os.fsencode(path), _ptr(rgba), rgba.shape[1], rgba.shape[0]) != 0:
+        raise _err()
+
+
+def load_glb_images(path):
+    """PNG images embedded in a .glb, in `images[]` order ((0, 0, 4) arrays for non-PNG entries)."""
+    L = hostlib()
+    n = C.c_uint32()
+    lst = L.rth_glb_images(os.fsencode(path), C.byref(n))
+    if not lst:
+        raise _err()
+    out = []
+    try:
+        for k in range(n.value):
+            w, h = C.c_uint32(), C.c_uint32()
+            L.rth_glb_image(lst, k, C.byref(w), C.byref(h), None)
+            a = np.empty((h.value, w.value, 4), np.uint8)
+            L.rth_glb_image(lst, k, C.byref(w), C.byref(h), _ptr(a))
+            out.append(a)
+    finally:
+        L.rth_glb_images_free(lst)
+    return out
+
+
+KEYS = {"W": 0, "S": 1, "A": 2, "D": 3, "Up": 4, "Down": 5, "Left": 6, "Right": 7, "Space": 8, "LShift": 9, "Other": 10}
+
+
+def camera_update(origin, look_at, controller, dt):
+    """camera.rs:122-165 on explicit state (C++ mirror): controller = dict of the 11 CameraController
+    fields. -> (origin, look_at, controller after the step)."""
+    names = ("amount_left", "amount_right", "amount_forward", "amount_backward", "amount_up", "amount_down",
+             "rotate_horizontal", "rotate_vertical", "scroll", "speed", "sensitivity")
+    st = np.zeros(17, np.float32)
+    st[0:3], st[3:6] = origin, look_at
+    st[6:17] = [controller.get(n, {"speed": 3.0, "sensitivity": 0.35}.get(n, 0.0)) for n in names]
+    if hostlib().rth_camera_update(_ptr(st), float(dt)) != 0:
+        raise _err()
+    return st[0:3].copy(), st[3:6].copy(), dict(zip(names, (float(x) for x in st[6:17])))
+
+
 def loader_mesh(mesh_count, n_indices, first, offset):
     out = np.zeros(1, MESH_DT)
     hostlib().rth_loader_mesh(mesh_count, n_indices, first, offset, _ptr(out))
@@ -211,6 +298,39 @@ class Context:
 
     def render(self):
         self._ck(self._L.rth_context_render(self._h))
+
+    # -- interactive path: fly-cam step, window events (every one resets the accumulation) --
+    def update_dt(self, dt):
+        """context.rs:176-187 with the camera step: update_camera(dt), to_uniform, frames += 1."""
+        self._ck(self._L.rth_context_update_dt(self._h, float(dt)))
+
+    def input_key(self, key, pressed):
+        r = self._L.rth_context_input_key(self._h, KEYS[key], int(bool(pressed)))
+        if r < 0:
+            raise _err()
+        return bool(r)
+
+    def input_scroll_lines(self, lines):
+        return bool(self._L.rth_context_input_scroll_lines(self._h, float(lines)))
+
+    def input_mouse_button(self, pressed):
+        return bool(self._L.rth_context_input_mouse_button(self._h, int(bool(pressed))))
+
+    def input_other(self):
+        return bool(self._L.rth_context_input_other(self._h))
+
+    def mouse_motion(self, dx, dy):
+        self._ck(self._L.rth_context_mouse_motion(self._h, float(dx), float(dy)))
+
+    @property
+    def camera(self):
+        q = np.zeros(6, np.float32)
+        self._L.rth_context_get_camera(self._h, _ptr(q))
+        return q[:3].copy(), q[3:].copy()
+
+    def save_png(self, path, mirror_x=False):
+        """What the blit + sRGB swapchain show (clamp, OETF, 8 bit), top row first."""
+        self._ck(self._L.rth_context_save_png(self._h, os.fsencode(path), int(bool(mirror_x))))
 
     def run_frames(self, n):
         self._ck(self._L.rth_context_run_frames(self._h, int(n)))

@@ -58,6 +58,29 @@ void Context::update()
     check(rt_set_params(ctx_, &params), "rt_set_params");      // :186
 }
 
+void Context::update(float dt)
+{
+    scene.camera.update_camera(dt);                            // context.rs:178
+    update();
+}
+
+bool Context::input_key(Key key, bool pressed) { clear_accululation(); return scene.camera.controller.process_keyboard(key, pressed); }
+bool Context::input_scroll_lines(float lines) { clear_accululation(); return scene.camera.controller.process_scroll_lines(lines); }
+bool Context::input_mouse_button(bool left_pressed) { clear_accululation(); mouse_pressed = left_pressed; return true; }
+bool Context::input_other() { clear_accululation(); return false; }                       // context.rs:149: any window event resets
+void Context::mouse_motion(double dx, double dy) { if (mouse_pressed) scene.camera.controller.process_mouse(dx, dy); }
+
+void Context::save_png(const std::string& path, bool mirror_x)
+{
+    const uint32_t W = params.width, H = params.height;
+    std::vector<uint8_t> px((size_t)W * H * 4), out((size_t)W * H * 4);
+    check(rt_read_rgba8(ctx_, px.data(), px.size()), "rt_read_rgba8");
+    for (uint32_t y = 0; y < H; y++)                           // texture row 0 is the bottom image row
+        for (uint32_t x = 0; x < W; x++)
+            memcpy(&out[((size_t)(H - 1 - y) * W + (mirror_x ? W - 1 - x : x)) * 4], &px[((size_t)y * W + x) * 4], 4);
+    write_png(path, out.data(), W, H);
+}
+
 void Context::render()
 {
     check(rt_dispatch(ctx_), "rt_dispatch");                   // context.rs:196-208
@@ -136,6 +159,36 @@ void* rth_scene_from_model(const char* path)
         return s;
     } catch (const std::exception& e) { g_err = e.what(); return nullptr; }
 }
+void* rth_scene_from_model_uv(const char* path)               // texture extension: keeps vt / TEXCOORD_0
+{
+    try {
+        rtb::Scene* s = new rtb::Scene();
+        try { rtb::load_model_uv(path, s->vertices, s->indices, s->meshes); } catch (...) { delete s; throw; }
+        return s;
+    } catch (const std::exception& e) { g_err = e.what(); return nullptr; }
+}
+// PNG in / out. rth_png_load returns a handle (NULL on error); *w, *h receive the size.
+void* rth_png_load(const char* path, uint32_t* w, uint32_t* h)
+{
+    try { rtb::Image* im = new rtb::Image(rtb::load_png(path)); *w = im->width; *h = im->height; return im; }
+    catch (const std::exception& e) { g_err = e.what(); return nullptr; }
+}
+void rth_image_copy(const void* im, uint8_t* rgba) { const rtb::Image* i = (const rtb::Image*)im; if (!i->rgba.empty()) memcpy(rgba, i->rgba.data(), i->rgba.size()); }
+void rth_image_free(void* im) { delete (rtb::Image*)im; }
+int rth_png_write(const char* path, const uint8_t* rgba, uint32_t w, uint32_t h) { RTH_TRY(rtb::write_png(path, rgba, w, h)); }
+// images embedded in a .glb: returns a handle to the list, *n = count; rth_glb_image gives entry k (may be 0x0 for non-PNG)
+void* rth_glb_images(const char* path, uint32_t* n)
+{
+    try { auto* v = new std::vector<rtb::Image>(rtb::load_glb_images(path)); *n = (uint32_t)v->size(); return v; }
+    catch (const std::exception& e) { g_err = e.what(); return nullptr; }
+}
+void rth_glb_image(const void* list, uint32_t k, uint32_t* w, uint32_t* h, uint8_t* rgba)
+{
+    const rtb::Image& i = ((const std::vector<rtb::Image>*)list)->at(k);
+    *w = i.width; *h = i.height;
+    if (rgba && !i.rgba.empty()) memcpy(rgba, i.rgba.data(), i.rgba.size());
+}
+void rth_glb_images_free(void* list) { delete (std::vector<rtb::Image>*)list; }
 void rth_scene_free(void* s) { delete (rtb::Scene*)s; }
 void rth_scene_counts(const void* h, uint32_t* ns, uint32_t* nv, uint32_t* ni, uint32_t* nm)
 {
@@ -163,6 +216,41 @@ void* rth_context_new(int device, uint32_t w, uint32_t h)
 }
 void rth_context_free(void* c) { delete (rtb::Context*)c; }
 int rth_context_update(void* c) { RTH_TRY(((rtb::Context*)c)->update()); }
+int rth_context_update_dt(void* c, float dt) { RTH_TRY(((rtb::Context*)c)->update(dt)); }
+int rth_context_input_key(void* c, int key, int pressed) { RTH_TRY(return ((rtb::Context*)c)->input_key((rtb::Key)key, pressed != 0) ? 1 : 0); }
+int rth_context_input_scroll_lines(void* c, float lines) { RTH_TRY(return ((rtb::Context*)c)->input_scroll_lines(lines) ? 1 : 0); }
+int rth_context_input_mouse_button(void* c, int pressed) { RTH_TRY(return ((rtb::Context*)c)->input_mouse_button(pressed != 0) ? 1 : 0); }
+int rth_context_input_other(void* c) { RTH_TRY(return ((rtb::Context*)c)->input_other() ? 1 : 0); }
+int rth_context_mouse_motion(void* c, double dx, double dy) { RTH_TRY(((rtb::Context*)c)->mouse_motion(dx, dy)); }
+void rth_context_get_camera(void* c, float* origin3_look_at3) {
+    const rtb::Camera& k = ((rtb::Context*)c)->scene.camera;
+    origin3_look_at3[0] = k.origin.x; origin3_look_at3[1] = k.origin.y; origin3_look_at3[2] = k.origin.z;
+    origin3_look_at3[3] = k.look_at.x; origin3_look_at3[4] = k.look_at.y; origin3_look_at3[5] = k.look_at.z;
+}
+int rth_context_save_png(void* c, const char* path, int mirror_x) { RTH_TRY(((rtb::Context*)c)->save_png(path, mirror_x != 0)); }
+// stand-alone fly-cam step for CPU tests: state = origin3, look_at3, then the controller's 11 floats
+int rth_camera_update(float* state17, float dt)
+{
+    try {
+        rtb::Camera k; float* q = state17;
+        k.origin.x = q[0]; k.origin.y = q[1]; k.origin.z = q[2]; k.look_at.x = q[3]; k.look_at.y = q[4]; k.look_at.z = q[5];
+        rtb::CameraController& t = k.controller;
+        t.amount_left = q[6]; t.amount_right = q[7]; t.amount_forward = q[8]; t.amount_backward = q[9]; t.amount_up = q[10]; t.amount_down = q[11];
+        t.rotate_horizontal = q[12]; t.rotate_vertical = q[13]; t.scroll = q[14]; t.speed = q[15]; t.sensitivity = q[16];
+        k.update_camera(dt);
+        q[0] = k.origin.x; q[1] = k.origin.y; q[2] = k.origin.z; q[3] = k.look_at.x; q[4] = k.look_at.y; q[5] = k.look_at.z;
+        q[12] = t.rotate_horizontal; q[13] = t.rotate_vertical; q[14] = t.scroll;
+        return 0;
+    } catch (const std::exception& e) { g_err = e.what(); return -1; }
+}
+int rth_controller_key(float* state17, int key, int pressed)
+{
+    rtb::CameraController t; float* q = state17;
+    t.amount_left = q[6]; t.amount_right = q[7]; t.amount_forward = q[8]; t.amount_backward = q[9]; t.amount_up = q[10]; t.amount_down = q[11];
+    bool r = t.process_keyboard((rtb::Key)key, pressed != 0);
+    q[6] = t.amount_left; q[7] = t.amount_right; q[8] = t.amount_forward; q[9] = t.amount_backward; q[10] = t.amount_up; q[11] = t.amount_down;
+    return r ? 1 : 0;
+}
 int rth_context_render(void* c) { RTH_TRY(((rtb::Context*)c)->render()); }
 int rth_context_run_frames(void* c, uint32_t n) { RTH_TRY(((rtb::Context*)c)->run_frames(n)); }
 int rth_context_resize(void* c, uint32_t w, uint32_t h) { RTH_TRY(((rtb::Context*)c)->resize(w, h)); }

@@ -34,10 +34,27 @@ rt_mesh Mesh(Vec3 pos, uint32_t first, uint32_t triangles, uint32_t offset, Vec4
 // scene.rs:88-92 — Vertex::new
 rt_vertex Vertex(Vec3 pos, Vec3 normal);
 
-// camera.rs:31-47 (state) — the controller/fly-cam part is interactive input, out of scope
+// camera.rs:171-247 — key / mouse / scroll state of the fly-cam (winit key codes reduced to
+// the ones process_keyboard matches)
+enum class Key { W, S, A, D, Up, Down, Left, Right, Space, LShift, Other };
+struct CameraController {
+    float amount_left = 0, amount_right = 0, amount_forward = 0, amount_backward = 0, amount_up = 0, amount_down = 0;
+    float rotate_horizontal = 0, rotate_vertical = 0, scroll = 0;
+    float speed = 3.0f, sensitivity = 0.35f;                       // CameraController::new(3.0, 0.35), camera.rs:57
+    bool process_keyboard(Key key, bool pressed);                  // camera.rs:201-232: 5.0 while pressed
+    void process_mouse(double mouse_dx, double mouse_dy);          // :233-236: x3
+    bool process_scroll_lines(float lines);                        // :238-247 LineDelta: -(lines * 10000)
+    bool process_scroll_pixels(double pixels);                     //          PixelDelta: -pixels
+};
+
+// camera.rs:31-47 (state)
 struct Camera {
     Vec3 origin{0, 0, 0}, look_at{0, 0, -1}, view_up{0, 1, 0};
     float fov = 45.0f, aspect = 1.0f, near_ = 0.1f, far_ = 100.0f, aperture = 0.0f, focus_dist = 0.1f;
+    CameraController controller;
+    // camera.rs:122-165 — one fly-cam step of dt seconds: yaw/pitch re-derived from look_at every
+    // call, x/z swapped in the scroll direction and the pitch clamp compared in degrees, as upstream
+    void update_camera(float dt);
     Camera() = default;
     // camera.rs:49-78 — Camera::new(origin, look_at, view_up, fov, aspect, near, far, aperture, focus_dist)
     Camera(Vec3 origin, Vec3 look_at, Vec3 view_up, float fov, float aspect, float near_, float far_, float aperture,
@@ -71,6 +88,16 @@ void load_model(const std::string& path, std::vector<rt_vertex>& vertices, std::
 void load_model_obj(const std::string& path, std::vector<rt_vertex>& v, std::vector<uint32_t>& i, std::vector<rt_mesh>& m);   // :47-107
 void load_model_gltf(const std::string& path, std::vector<rt_vertex>& v, std::vector<uint32_t>& i, std::vector<rt_mesh>& m);  // :109-192
 void load_model_glb(const std::string& path, std::vector<rt_vertex>& v, std::vector<uint32_t>& i, std::vector<rt_mesh>& m);   // :194-278
+// Texture-extension loaders (the reference drops `vt` / TEXCOORD_0 and never opens an image):
+// keep_uv = true stores the texture coordinates in the Vertex padding words (OBJ v flipped so
+// that image row 0 is the top row).
+void load_model_uv(const std::string& path, std::vector<rt_vertex>& vertices, std::vector<uint32_t>& indices,
+                   std::vector<rt_mesh>& meshes);
+struct Image { uint32_t width = 0, height = 0; std::vector<uint8_t> rgba; };
+Image load_png(const std::string& path);                            // 8/16-bit grey, grey+alpha, RGB, RGBA, palette; no interlace
+Image decode_png(const uint8_t* data, size_t size);
+std::vector<Image> load_glb_images(const std::string& path);        // PNG images embedded in a .glb (JPEG entries come back empty)
+void write_png(const std::string& path, const uint8_t* rgba, uint32_t width, uint32_t height);
 // the hard-coded record each loaded primitive gets (resource.rs:73-85)
 rt_mesh loader_mesh(uint32_t mesh_count, uint32_t n_indices, uint32_t first, uint32_t offset);
 
@@ -90,7 +117,19 @@ public:
 
     void resize(uint32_t width, uint32_t height);   // context.rs:126-142
     void clear_accululation();                      // context.rs:143-146 (spelling as upstream)
-    void update();                                  // context.rs:176-187 (camera fly-cam step omitted)
+    void update();                                  // context.rs:176-187 without the fly-cam step (dt = 0 leaves the camera's look_at re-derivation out)
+    void update(float dt);                          // context.rs:176-187: camera.update_camera(dt), to_uniform, frames += 1
+    // context.rs:148-175 — every window event resets the accumulation, then keyboard / wheel /
+    // left button go to the controller; returns what upstream's `input` returns
+    bool input_key(Key key, bool pressed);
+    bool input_scroll_lines(float lines);
+    bool input_mouse_button(bool left_pressed);
+    bool input_other();
+    void mouse_motion(double dx, double dy);        // lib.rs:25-27: only while the left button is held
+    bool mouse_pressed = false;
+    // What the blit pass + sRGB swapchain show (render.wgsl:34-39, context.rs:75-80), written as a PNG:
+    // clamp, sRGB OETF, 8 bit; top row first; mirror_x reproduces the on-screen flip of renderer.rs:35-38
+    void save_png(const std::string& path, bool mirror_x = false);
     void render();                                  // context.rs:196-208 — the compute pass only
     void set_scene(int id);                         // context.rs:259-283
     void set_scene(Scene s);                        // RayTracer::new on a caller-built scene

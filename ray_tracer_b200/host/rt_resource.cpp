@@ -16,11 +16,15 @@
 #include <sstream>
 #include <stdexcept>
 #include <tuple>
+#include <zlib.h>
 #include "rt_host.hpp"
 
 namespace rtb {
 
 namespace {
+
+// texture extension: when set, the loaders keep texture coordinates (load_model_uv)
+thread_local bool g_keep_uv = false;
 
 std::string read_file(const std::string& path, bool binary)
 {
@@ -161,10 +165,17 @@ void append_primitive(const Json& g, const std::vector<std::string>& buffers, co
     meshes.push_back(loader_mesh((uint32_t)meshes.size(), (uint32_t)idx.size(), (uint32_t)indices.size(), (uint32_t)vertices.size()));
     const float scale = (float)meshes.size();                     // resource.rs:180 (after the push)
     size_t n = ap.count < an.count ? ap.count : an.count;         // positions.zip(normals)
+    Accessor at{nullptr, 0, 0, 0, 0};
+    if (g_keep_uv)
+        if (const Json* jt = attrs.get("TEXCOORD_0")) {
+            at = accessor(g, buffers, (long)jt->num);
+            if (at.comp != 5126 || at.ncomp != 2) at.base = nullptr;     // only f32 VEC2 coordinates are kept
+        }
     for (size_t r = 0; r < n; r++) {
         rt_vertex v{};
         memcpy(v.pos, ap.base + r * ap.stride, 12);
         memcpy(v.normal, an.base + r * an.stride, 12);
+        if (at.base && r < at.count) { memcpy(&v.tu, at.base + r * at.stride, 4); memcpy(&v.tv, at.base + r * at.stride + 4, 4); }
         if (scale_by_mesh_count) { v.pos[0] *= scale; v.pos[1] *= scale; v.pos[2] *= scale; }
         vertices.push_back(v);
     }
@@ -194,7 +205,7 @@ void load_model(const std::string& path, std::vector<rt_vertex>& v, std::vector<
 void load_model_obj(const std::string& path, std::vector<rt_vertex>& vertices, std::vector<uint32_t>& indices, std::vector<rt_mesh>& meshes)
 {
     std::istringstream in(read_file(path, false));
-    std::vector<float> pos, nrm;
+    std::vector<float> pos, nrm, tex;
     struct Model { std::map<std::tuple<long, long, long>, uint32_t> map; std::vector<rt_vertex> v; std::vector<uint32_t> idx; };
     std::vector<Model> models;
     std::unique_ptr<Model> cur;
@@ -207,6 +218,7 @@ void load_model_obj(const std::string& path, std::vector<rt_vertex>& vertices, s
         if (!(ls >> tag) || tag[0] == '#') continue;
         if (tag == "v") { float x, y, z; ls >> x >> y >> z; pos.insert(pos.end(), {x, y, z}); }
         else if (tag == "vn") { float x, y, z; ls >> x >> y >> z; nrm.insert(nrm.end(), {x, y, z}); }
+        else if (tag == "vt") { float x = 0, y = 0; ls >> x >> y; tex.insert(tex.end(), {x, y}); }
         else if (tag == "o" || tag == "g") { flush(); cur.reset(new Model()); }
         else if (tag == "f") {
             if (!cur) cur.reset(new Model());
@@ -222,7 +234,7 @@ void load_model_obj(const std::string& path, std::vector<rt_vertex>& vertices, s
                     if (!t.empty()) { ti = atol(t.c_str()); ht = true; }
                     if (s2 != std::string::npos && s2 + 1 < c.size()) { ni = atol(c.substr(s2 + 1).c_str()); hn = true; }
                 }
-                long v0 = fix(vi, pos.size() / 3), t0 = ht ? fix(ti, 0) : -1, n0 = hn ? fix(ni, nrm.size() / 3) : -1;
+                long v0 = fix(vi, pos.size() / 3), t0 = ht ? fix(ti, tex.size() / 2) : -1, n0 = hn ? fix(ni, nrm.size() / 3) : -1;
                 if (v0 < 0 || (size_t)v0 >= pos.size() / 3) throw std::runtime_error("OBJ: vertex index out of range");
                 if (n0 < 0 || (size_t)n0 >= nrm.size() / 3) throw std::runtime_error("OBJ: face without a valid normal (the reference indexes normals unconditionally)");  // resource.rs:96-100
                 auto key = std::make_tuple(v0, t0, n0);
@@ -230,6 +242,11 @@ void load_model_obj(const std::string& path, std::vector<rt_vertex>& vertices, s
                 if (it == cur->map.end()) {
                     rt_vertex vv{};
                     memcpy(vv.pos, &pos[(size_t)v0 * 3], 12); memcpy(vv.normal, &nrm[(size_t)n0 * 3], 12);
+                    if (g_keep_uv) {                             // extension: (u, 1 - v), image row 0 = top row
+                        bool ok = t0 >= 0 && (size_t)t0 < tex.size() / 2;
+                        vv.tu = ok ? tex[(size_t)t0 * 2] : 0.0f;
+                        vv.tv = 1.0f - (ok ? tex[(size_t)t0 * 2 + 1] : 1.0f);
+                    }
                     it = cur->map.emplace(key, (uint32_t)cur->v.size()).first;
                     cur->v.push_back(vv);
                 }
@@ -289,6 +306,126 @@ void load_model_gltf(const std::string& path, std::vector<rt_vertex>& vertices, 
                 for (const Json& prim : g.at("meshes").arr.at((size_t)jm->num).at("primitives").arr)
                     append_primitive(g, buffers, prim, true, vertices, indices, meshes);
             }
+}
+
+// ---- texture extension: UV-keeping load, PNG decode / encode, GLB-embedded images ---------
+void load_model_uv(const std::string& path, std::vector<rt_vertex>& v, std::vector<uint32_t>& i, std::vector<rt_mesh>& m)
+{
+    struct Guard { Guard() { g_keep_uv = true; } ~Guard() { g_keep_uv = false; } } guard;
+    load_model(path, v, i, m);
+}
+
+namespace {
+uint32_t be32(const uint8_t* p) { return ((uint32_t)p[0] << 24) | ((uint32_t)p[1] << 16) | ((uint32_t)p[2] << 8) | p[3]; }
+int paeth(int a, int b, int c) { int p = a + b - c, pa = abs(p - a), pb = abs(p - b), pc = abs(p - c); return (pa <= pb && pa <= pc) ? a : (pb <= pc ? b : c); }
+}
+
+Image decode_png(const uint8_t* d, size_t size)
+{
+    static const uint8_t sig[8] = {0x89, 'P', 'N', 'G', 0x0d, 0x0a, 0x1a, 0x0a};
+    if (size < 8 || memcmp(d, sig, 8) != 0) throw std::runtime_error("PNG: bad signature");
+    uint32_t W = 0, H = 0; int depth = 0, ctype = -1, interlace = 0;
+    std::vector<uint8_t> idat, plte, trns;
+    for (size_t off = 8; off + 12 <= size;) {
+        uint32_t len = be32(d + off);
+        if (off + 12 + (size_t)len > size) throw std::runtime_error("PNG: truncated chunk");
+        const uint8_t* body = d + off + 8;
+        if (!memcmp(d + off + 4, "IHDR", 4) && len >= 13) { W = be32(body); H = be32(body + 4); depth = body[8]; ctype = body[9]; interlace = body[12]; }
+        else if (!memcmp(d + off + 4, "PLTE", 4)) plte.assign(body, body + len);
+        else if (!memcmp(d + off + 4, "tRNS", 4)) trns.assign(body, body + len);
+        else if (!memcmp(d + off + 4, "IDAT", 4)) idat.insert(idat.end(), body, body + len);
+        else if (!memcmp(d + off + 4, "IEND", 4)) break;
+        off += 12 + (size_t)len;
+    }
+    if (!W || !H || W > 32768 || H > 32768) throw std::runtime_error("PNG: missing or absurd IHDR");
+    if (interlace) throw std::runtime_error("PNG: interlaced images are not supported");
+    int ch = ctype == 0 ? 1 : ctype == 2 ? 3 : ctype == 3 ? 1 : ctype == 4 ? 2 : ctype == 6 ? 4 : 0;
+    if (!ch || !(depth == 8 || (depth == 16 && ctype != 3))) throw std::runtime_error("PNG: unsupported colour type / bit depth");
+    const size_t bpp = (size_t)ch * depth / 8, stride = (size_t)W * bpp;
+    std::vector<uint8_t> raw((stride + 1) * H);
+    uLongf out_len = (uLongf)raw.size();
+    if (uncompress(raw.data(), &out_len, idat.data(), (uLong)idat.size()) != Z_OK || out_len != raw.size()) throw std::runtime_error("PNG: inflate failed");
+    std::vector<uint8_t> prev(stride, 0), cur(stride);
+    Image img; img.width = W; img.height = H; img.rgba.resize((size_t)W * H * 4);
+    for (uint32_t y = 0; y < H; y++) {
+        const uint8_t* row = &raw[(stride + 1) * y];
+        const int f = row[0];
+        if (f > 4) throw std::runtime_error("PNG: bad filter type");
+        for (size_t i = 0; i < stride; i++) {
+            int a = i >= bpp ? cur[i - bpp] : 0, b = prev[i], c = i >= bpp ? prev[i - bpp] : 0, x = row[1 + i];
+            cur[i] = (uint8_t)(f == 0 ? x : f == 1 ? x + a : f == 2 ? x + b : f == 3 ? x + ((a + b) >> 1) : x + paeth(a, b, c));
+        }
+        for (uint32_t xx = 0; xx < W; xx++) {
+            const uint8_t* s = &cur[xx * bpp]; const size_t st = depth / 8;      // 16-bit samples: keep the high byte
+            uint8_t* o = &img.rgba[((size_t)y * W + xx) * 4];
+            if (ctype == 0) { o[0] = o[1] = o[2] = s[0]; o[3] = 255; }
+            else if (ctype == 2) { o[0] = s[0]; o[1] = s[st]; o[2] = s[2 * st]; o[3] = 255; }
+            else if (ctype == 3) { size_t k = s[0]; if (3 * k + 2 >= plte.size()) throw std::runtime_error("PNG: palette index out of range");
+                                   o[0] = plte[3 * k]; o[1] = plte[3 * k + 1]; o[2] = plte[3 * k + 2]; o[3] = k < trns.size() ? trns[k] : 255; }
+            else if (ctype == 4) { o[0] = o[1] = o[2] = s[0]; o[3] = s[st]; }
+            else { o[0] = s[0]; o[1] = s[st]; o[2] = s[2 * st]; o[3] = s[3 * st]; }
+        }
+        prev.swap(cur);
+    }
+    return img;
+}
+
+Image load_png(const std::string& path)
+{
+    std::string data = read_file(path, true);
+    return decode_png((const uint8_t*)data.data(), data.size());
+}
+
+void write_png(const std::string& path, const uint8_t* rgba, uint32_t W, uint32_t H)
+{
+    std::vector<uint8_t> raw(((size_t)W * 4 + 1) * H);
+    for (uint32_t y = 0; y < H; y++) { raw[((size_t)W * 4 + 1) * y] = 0; memcpy(&raw[((size_t)W * 4 + 1) * y + 1], rgba + (size_t)y * W * 4, (size_t)W * 4); }
+    uLongf clen = compressBound((uLong)raw.size());
+    std::vector<uint8_t> comp(clen);
+    if (compress2(comp.data(), &clen, raw.data(), (uLong)raw.size(), 6) != Z_OK) throw std::runtime_error("PNG: deflate failed");
+    std::ofstream f(path, std::ios::binary);
+    if (!f) throw std::runtime_error("PNG: cannot open " + path);
+    auto put32 = [](uint8_t* p, uint32_t v) { p[0] = v >> 24; p[1] = v >> 16; p[2] = v >> 8; p[3] = v; };
+    auto chunk = [&](const char* tag, const uint8_t* body, uint32_t len) {
+        std::vector<uint8_t> b(8 + (size_t)len + 4);
+        put32(b.data(), len); memcpy(&b[4], tag, 4); if (len) memcpy(&b[8], body, len);
+        put32(&b[8 + len], (uint32_t)crc32(0L, &b[4], 4 + len));
+        f.write((const char*)b.data(), (std::streamsize)b.size());
+    };
+    static const uint8_t sig[8] = {0x89, 'P', 'N', 'G', 0x0d, 0x0a, 0x1a, 0x0a};
+    f.write((const char*)sig, 8);
+    uint8_t ihdr[13]; put32(ihdr, W); put32(ihdr + 4, H); ihdr[8] = 8; ihdr[9] = 6; ihdr[10] = ihdr[11] = ihdr[12] = 0;
+    chunk("IHDR", ihdr, 13); chunk("IDAT", comp.data(), (uint32_t)clen); chunk("IEND", nullptr, 0);
+    if (!f) throw std::runtime_error("PNG: write failed: " + path);
+}
+
+std::vector<Image> load_glb_images(const std::string& path)
+{
+    std::string data = read_file(path, true);
+    if (data.size() < 20 || memcmp(data.data(), "glTF", 4) != 0) throw std::runtime_error("GLB: bad magic");
+    std::string json, blob;
+    for (size_t off = 12; off + 8 <= data.size();) {
+        uint32_t clen, ctype; memcpy(&clen, &data[off], 4); memcpy(&ctype, &data[off + 4], 4);
+        if (off + 8 + clen > data.size()) throw std::runtime_error("GLB: truncated chunk");
+        if (ctype == 0x4E4F534Au) json.assign(data, off + 8, clen);
+        else if (ctype == 0x004E4942u && blob.empty()) blob.assign(data, off + 8, clen);
+        off += 8 + (size_t)clen;
+    }
+    Json g = parse_json(json);
+    std::vector<Image> out;
+    if (const Json* ji = g.get("images"))
+        for (const Json& im : ji->arr) {
+            Image img;
+            const Json* bv = im.get("bufferView"); const Json* mt = im.get("mimeType");
+            if (bv && mt && mt->str == "image/png") {
+                const Json& v = g.at("bufferViews").arr.at((size_t)bv->num);
+                size_t off = (size_t)v.integer("byteOffset", 0), len = (size_t)v.integer("byteLength", 0);
+                if (off + len > blob.size()) throw std::runtime_error("GLB: image outside the binary chunk");
+                img = decode_png((const uint8_t*)blob.data() + off, len);
+            }
+            out.push_back(std::move(img));
+        }
+    return out;
 }
 
 } // namespace rtb

@@ -70,6 +70,52 @@ rt_camera_uniform Camera::to_uniform() const
     return cu;
 }
 
+// ---- fly-cam (camera.rs:122-247) ---------------------------------------------------------
+bool CameraController::process_keyboard(Key key, bool pressed)
+{
+    float amount = pressed ? 5.0f : 0.0f;
+    switch (key) {
+    case Key::W: case Key::Up: amount_forward = amount; return true;
+    case Key::S: case Key::Down: amount_backward = amount; return true;
+    case Key::A: case Key::Left: amount_left = amount; return true;
+    case Key::D: case Key::Right: amount_right = amount; return true;
+    case Key::Space: amount_up = amount; return true;
+    case Key::LShift: amount_down = amount; return true;
+    default: return false;
+    }
+}
+void CameraController::process_mouse(double dx, double dy) { rotate_horizontal = (float)dx * 3.0f; rotate_vertical = (float)dy * 3.0f; }
+bool CameraController::process_scroll_lines(float lines) { scroll = -(lines * 10000.0f); return true; }
+bool CameraController::process_scroll_pixels(double pixels) { scroll = -(float)pixels; return true; }
+
+static Vec3 operator*(Vec3 a, float s) { return {a.x * s, a.y * s, a.z * s}; }
+
+void Camera::update_camera(float dt)
+{
+    // SAFE_FRAC_PI_2_DEG: (FRAC_PI_2 - 0.0001) * (180/PI), compared against radians (camera.rs:6-7,159-163)
+    const float safe_deg = (1.57079637050628662f - 0.0001f) * (180.0f / 3.14159274101257324f);
+    CameraController& c = controller;
+    Vec3 direction = normalize(look_at - origin);
+    float pitch = std::asin(direction.y);
+    float yaw = std::atan2(direction.x, direction.z);
+    float yaw_sin = std::sin(yaw), yaw_cos = std::cos(yaw);
+    Vec3 forward = normalize(Vec3{yaw_sin, 0.0f, yaw_cos});
+    Vec3 right = normalize(Vec3{yaw_cos, 0.0f, -yaw_sin});
+    origin = origin + ((forward * (c.amount_forward - c.amount_backward)) * c.speed) * dt;
+    origin = origin + ((right * (c.amount_right - c.amount_left)) * c.speed) * dt;
+    float pitch_sin = std::sin(pitch), pitch_cos = std::cos(pitch);
+    Vec3 scrollward = normalize(Vec3{pitch_cos * yaw_cos, pitch_sin, pitch_cos * yaw_sin});
+    origin = origin - (((scrollward * c.scroll) * c.speed) * c.sensitivity) * dt;
+    c.scroll = 0.0f;
+    origin.y += (c.amount_up - c.amount_down) * c.speed * dt;
+    yaw += c.rotate_horizontal * c.sensitivity * dt;
+    pitch += -c.rotate_vertical * c.sensitivity * dt;
+    c.rotate_horizontal = 0.0f; c.rotate_vertical = 0.0f;
+    if (pitch < -safe_deg) pitch = -safe_deg;
+    else if (pitch > safe_deg) pitch = safe_deg;
+    look_at = origin + Vec3{std::cos(pitch) * std::sin(yaw), std::sin(pitch), std::cos(pitch) * std::cos(yaw)};
+}
+
 void Scene::add_dummy_mesh()
 {
     vertices.push_back(Vertex({0.0f, 0.0f, 1.0f}, {2.0f, -3.0f, -1.0f}));
