@@ -197,17 +197,23 @@ def run_ours(args, rank, world, local_rank):
     tr.upload_textures(scene.textures)
     tr.set_camera(cam)
     tr.set_params(**p)
-    tr.set_shard(0, 1, rank, world)              # sample-index sharding: frames = rank (mod world)
+    # partition (no data-path collective): --shard sample: dispatch f -> rank f % N; tile: 8x8 tiles dealt
+    # round-robin; tile+sample: T tile groups x N/T sample groups.  Per-GPU work is the same in all three.
+    T = {"sample": 1, "tile": world, "tile+sample": (2 if world >= 4 else world)}[args.shard]
+    F = world // T
+    tr.set_shard(rank % T, T, rank // T, F)
     stream = torch.cuda.ExternalStream(tr.cuda_stream, device=dev)
     accum_t = torch.as_tensor(_DevArray(tr.accum_device_ptr, (H, W, 4)), device="cuda:%d" % dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda:%d" % dev)
 
     def step():
-        tr.render_frames(0, D * world)           # this rank renders D of the D*world frames
+        if T > 1:
+            tr.clear()                           # other ranks' tiles must be zero before the sum
+        tr.render_frames(0, D * world)           # this rank renders 1/T of the pixels of 1/F of the D*world frames
         if world > 1:
             cur = torch.cuda.current_stream()
             cur.wait_stream(stream)
-            sharding.combine_sample_shards(accum_t, D, D * world)   # NCCL all-reduce of the per-GPU running means over NVLink
+            sharding.combine_sample_shards(accum_t, 1, F)           # one NCCL all-reduce over NVLink: sum of disjoint tiles, count-weighted mean of sample groups
             stream.wait_stream(cur)
 
     def barrier():
@@ -223,6 +229,8 @@ def run_ours(args, rank, world, local_rank):
         raise SystemExit("rt_measure_fp32_peak failed")
     tr.set_option(_lib.RT_OPT_DETAIL_COUNTERS, 1)
     tr.reset_counters()
+    if T > 1:
+        tr.clear()
     tr.render_frames(0, D * world); tr.sync()
     det = tr.counters()
     tr.set_option(_lib.RT_OPT_DETAIL_COUNTERS, 0)
@@ -311,7 +319,7 @@ def run_ours(args, rank, world, local_rank):
             "config": {"workload": args.config, "width": W, "height": H, "spp_per_gpu": meta["spp"], "dispatches_per_gpu": D,
                        "bounces": p["number_of_bounces"], "rays_per_pixel": p["rays_per_pixel"], "skybox": p["skybox"],
                        "triangles": int(ms["triangles"].sum()), "spheres": int(sp.size), "traversal": "bvh2 (PLOC over 63-bit Morton order, GPU-built)", "textures": len(scene.textures),
-                       "parallelism": "sample-index sharding x%d + NCCL all-reduce per step" % world if world > 1 else "single GPU",
+                       "parallelism": ("%s sharding (%d tile groups x %d sample groups) + one NCCL all-reduce per step" % (args.shard, T, F)) if world > 1 else "single GPU",
                        "l2": "256 MiB write between timed steps (untimed); scene+BVH are L2-resident by design",
                        "spp_per_s": meta["spp"] * world / (ms_total / max(args.steps, 1) * 1e-3)},
             "clocks": clocks,
@@ -349,10 +357,14 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="c3_teapot")
+    ap.add_argument("--shard", default="sample", choices=["sample", "tile", "tile+sample"])
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    global METRIC
+    if args.config != "c3_teapot":
+        METRIC = "Mrays/s (all bounces) at %s" % args.config      # BASELINE.json's metric is quoted on C3; other configs are labelled as such
     if args.impl == "reference":
         run_reference(args, rank, world)
     else:
