@@ -161,6 +161,17 @@ int rt_upload_scene(rt_ctx* ctx,
                     const uint32_t* indices, uint32_t n_indices,
                     const rt_mesh* meshes, uint32_t n_meshes);
 
+/* Dynamic scenes (upstream rebuilds everything through RayTracer::new on a
+ * scene switch, context.rs:259-283).  Same counts and the same first/triangles/offset per mesh
+ * as the last rt_upload_scene; sphere positions / radii, mesh `pos` (the translation the shader
+ * adds per vertex, wgsl:172-174) and all material fields may change.  Records and bounds are
+ * re-derived with the same operations as at upload and the hierarchy's boxes are refitted
+ * bottom-up on the kept topology (no sort, no build): results are exactly those of a fresh
+ * rt_upload_scene of the updated records; traversal cost grows as primitives move away from
+ * where the topology was built. */
+int rt_update_records(rt_ctx* ctx, const rt_sphere* spheres, uint32_t n_spheres,
+                      const rt_mesh* meshes, uint32_t n_meshes);
+
 /* Texture extension: replaces the context's texture table (n = 0 clears it). Pixels are copied
  * into CUDA arrays bound to texture objects; handles in rt_mesh address this table (handles
  * above n are treated as "none"). Independent of rt_upload_scene order. */

@@ -65,6 +65,7 @@ SYMBOLS = {
     "rt_create": (C.c_int, [C.POINTER(_vp), C.c_int, _u32, _u32]),
     "rt_destroy": (None, [_vp]),
     "rt_upload_scene": (C.c_int, [_vp, _vp, _u32, _vp, _u32, _vp, _u32, _vp, _u32]),
+    "rt_update_records": (C.c_int, [_vp, _vp, _u32, _vp, _u32]),
     "rt_upload_textures": (C.c_int, [_vp, _vp, _u32]),
     "rt_set_camera": (C.c_int, [_vp, _vp]),
     "rt_set_params": (C.c_int, [_vp, _vp]),

@@ -38,6 +38,7 @@ struct rt_ctx {
     int64_t opt_staging_bytes = 2ll << 30;
     int64_t opt_sched = 8 | (1 << 8) | (22 << 16);     // node loop runs while >= 8 lanes can step; shade once >= 22 lanes wait (swept on C3/C5)
     rt::SceneBuffers scene;
+    std::vector<rt_mesh> mesh_ranges;             // the uploaded Mesh records (rt_update_records checks the index ranges against them)
     struct Tex { cudaArray_t arr; cudaTextureObject_t obj; uint32_t w, h; };
     std::vector<Tex> textures;                    // texture extension: CUDA arrays + texture objects
     rt::TexDev* d_tex = nullptr;                  // device table of (object, width, height)
@@ -274,6 +275,31 @@ int rt_upload_scene(rt_ctx* c, const rt_sphere* spheres, uint32_t ns, const rt_v
         return fail(c, RT_ERR_UNSUPPORTED, "rt_upload_scene: BVH deeper than the traversal stack");
     }
     c->has_scene = true;
+    c->mesh_ranges.assign(meshes, meshes + nm);
+    return RT_OK;
+}
+
+int rt_update_records(rt_ctx* c, const rt_sphere* spheres, uint32_t ns, const rt_mesh* meshes, uint32_t nm)
+{
+    if (!c) return RT_ERR_INVALID_ARGUMENT;
+    if (!c->has_scene) return fail(c, RT_ERR_NO_SCENE, "rt_update_records: no scene uploaded");
+    if ((ns && !spheres) || (nm && !meshes)) return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_update_records: NULL array with non-zero count");
+    if (ns != c->scene.n_spheres || nm != c->mesh_ranges.size())
+        return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_update_records: sphere / mesh counts differ from the uploaded scene (use rt_upload_scene)");
+    for (uint32_t m = 0; m < nm; m++) {
+        const rt_mesh &a = meshes[m], &b = c->mesh_ranges[m];
+        if (a.first != b.first || a.triangles != b.triangles || a.offset != b.offset) {
+            char t[160]; snprintf(t, sizeof t, "rt_update_records: mesh %u addresses a different index range than the uploaded one (use rt_upload_scene)", m);
+            return fail(c, RT_ERR_INVALID_ARGUMENT, t);
+        }
+        if (a.triangles && (a.diffuse_tex | a.normal_tex) && !c->scene.has_tex)
+            return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_update_records: texture handles on a scene uploaded without any (use rt_upload_scene)");
+    }
+    DeviceGuard g(c->device);
+    CU(c, cudaStreamSynchronize(c->stream));
+    cudaError_t e = rt::refit_scene(c->scene, spheres, meshes, c->stream);
+    if (e != cudaSuccess) { c->has_scene = false; return cuda_fail(c, e, "scene refit"); }
+    c->mesh_ranges.assign(meshes, meshes + nm);
     return RT_OK;
 }
 

@@ -345,6 +345,28 @@ __global__ void ploc_layout(int n, int root, const int2* __restrict__ children, 
     else ranges[self] = make_int2(off, off + __float_as_int(imin[self].w) - 1);
 }
 
+// Bottom-up boxes over a kept topology (either builder): parents are stored shifted left by
+// `shift` (PLOC keeps the is-right-child bit below the index); the second thread to arrive at
+// a node owns it; the climb ends at `root`, whose parent word is never read.
+__global__ void refit_boxes(int n, int root, int shift, const int2* children, const int* pin, const int* plf,
+                            const float4* lmin, const float4* lmax, float4* imin, float4* imax, int* flags)
+{
+    int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    int node = plf[k] >> shift;
+    for (;;) {
+        __threadfence();
+        if (atomicAdd(flags + node, 1) == 0) break;
+        int2 ch = children[node];
+        float4 alo = ch.x >= 0 ? ((volatile float4*)imin)[ch.x] : lmin[~ch.x], ahi = ch.x >= 0 ? ((volatile float4*)imax)[ch.x] : lmax[~ch.x];
+        float4 blo = ch.y >= 0 ? ((volatile float4*)imin)[ch.y] : lmin[~ch.y], bhi = ch.y >= 0 ? ((volatile float4*)imax)[ch.y] : lmax[~ch.y];
+        imin[node] = make_float4(fminf(alo.x, blo.x), fminf(alo.y, blo.y), fminf(alo.z, blo.z), 0.f);
+        imax[node] = make_float4(fmaxf(ahi.x, bhi.x), fmaxf(ahi.y, bhi.y), fmaxf(ahi.z, bhi.z), 0.f);
+        if (node == root) break;
+        node = pin[node] >> shift;
+    }
+}
+
 __global__ void identity_slots(uint32_t n, uint32_t* new_slot)
 {
     uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
@@ -410,6 +432,12 @@ void SceneBuffers::release()
 {
     float4** ps[] = {&prims, &c0, &c1, &c2, &c3, &c4, &c5, &m0, &m1, &m2, &nodes};
     for (auto p : ps) { if (*p) cudaFreeAsync(*p, stream); *p = nullptr; }
+    {
+        void* kp[] = {keep.sph, keep.vtx, keep.idx, keep.mesh, keep.tstart, keep.hot, keep.bmin, keep.bmax, keep.lmin, keep.lmax, keep.imin, keep.imax,
+                      keep.bounds, keep.ids2, keep.new_slot, keep.children, keep.ranges, keep.pin, keep.plf, keep.flags};
+        for (void* p : kp) if (p) cudaFreeAsync(p, stream);
+        keep = Keep();
+    }
     n_prims = n_spheres = n_tris = n_mats = n_nodes = max_depth = 0; root = -1; max_abs = 0.f; has_tex = false;
 }
 
@@ -536,6 +564,14 @@ cudaError_t build_scene(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns
             if (f == f && fabsf(f) <= 3.0e38f && fabsf(f) > m) m = fabsf(f);
         }
         out.max_abs = m;
+        // keep what refit_scene needs (ownership moves to `out`; the rest is freed below)
+        SceneBuffers::Keep& k = out.keep;
+        k.sph = d_sph; k.vtx = d_vtx; k.idx = d_idx; k.mesh = d_mesh; k.tstart = d_tstart; k.hot = hot; k.bmin = bmin; k.bmax = bmax;
+        k.lmin = lmin; k.lmax = lmax; k.imin = imin; k.imax = imax; k.bounds = d_bounds; k.ids2 = ids2; k.new_slot = new_slot;
+        k.children = children; k.ranges = ranges; k.pin = pin; k.plf = plf; k.flags = flags;
+        k.nm = nm; k.leaf_size = leaf_size; k.parent_shift = out.builder == 0 ? 1 : 0;
+        d_sph = nullptr; d_vtx = nullptr; d_idx = nullptr; d_mesh = nullptr; d_tstart = nullptr; hot = bmin = bmax = lmin = lmax = imin = imax = nullptr;
+        d_bounds = nullptr; ids2 = new_slot = nullptr; children = ranges = nullptr; pin = plf = flags = nullptr;
     }
 done:
     {
@@ -545,6 +581,46 @@ done:
         for (void* p : tmp) if (p) cudaFreeAsync(p, stream);
     }
     if (err != cudaSuccess) out.release();
+    return err;
+}
+
+cudaError_t refit_scene(SceneBuffers& sc, const rt_sphere* spheres, const rt_mesh* meshes, cudaStream_t stream)
+{
+    SceneBuffers::Keep& k = sc.keep;
+    const uint32_t n = sc.n_prims, ns = sc.n_spheres, nm = k.nm, nmat = sc.n_mats;
+    const int T = 256;
+    cudaError_t err = cudaSuccess;
+    if (n == 0) return cudaSuccess;                    // nothing is ever hit: no record is read
+    int hb[6]; int h_init[6] = {0x7fffffff, 0x7fffffff, 0x7fffffff, (int)0x80000000, (int)0x80000000, (int)0x80000000};
+    if (ns) RT_TRY(cudaMemcpyAsync(k.sph, spheres, ns * sizeof(rt_sphere), cudaMemcpyHostToDevice, stream));
+    if (nm) RT_TRY(cudaMemcpyAsync(k.mesh, meshes, nm * sizeof(rt_mesh), cudaMemcpyHostToDevice, stream));
+    {
+        RawScene rs{k.sph, k.vtx, k.idx, k.mesh, k.tstart, ns, nm, sc.n_tris};
+        if (nmat) setup_materials<<<(nmat + T - 1) / T, T, 0, stream>>>(rs, sc.m0, sc.m1, sc.m2);
+        if (n == 0) { RT_TRY(cudaStreamSynchronize(stream)); goto done; }
+        const int nb = (n + T - 1) / T;
+        RT_TRY(cudaMemcpyAsync(k.bounds, h_init, sizeof(h_init), cudaMemcpyHostToDevice, stream));
+        setup_prims<<<nb, T, 0, stream>>>(rs, k.hot, sc.c0, sc.c1, sc.c2, sc.c3, sc.c4, sc.c5, k.bmin, k.bmax, k.bounds);
+        gather_boxes<<<nb, T, 0, stream>>>(n, k.ids2, k.bmin, k.bmax, k.lmin, k.lmax);
+        if (n == 1) {
+            emit_single<<<1, 1, 0, stream>>>(k.lmin, k.lmax, sc.nodes);
+        } else {
+            RT_TRY(cudaMemsetAsync(k.flags, 0, n * sizeof(int), stream));
+            refit_boxes<<<nb, T, 0, stream>>>((int)n, sc.root, k.parent_shift, k.children, k.pin, k.plf, k.lmin, k.lmax, k.imin, k.imax, k.flags);
+            emit_nodes<<<nb, T, 0, stream>>>((int)n - 1, k.children, k.ranges, k.new_slot, k.lmin, k.lmax, k.imin, k.imax, (int)k.leaf_size, sc.nodes);
+        }
+        gather_slots<<<(4 * n + T - 1) / T, T, 0, stream>>>(n, k.ids2, k.new_slot, k.hot, sc.prims);
+        RT_TRY(cudaMemcpyAsync(hb, k.bounds, sizeof(hb), cudaMemcpyDeviceToHost, stream));
+        RT_TRY(cudaStreamSynchronize(stream));
+        RT_TRY(cudaGetLastError());
+        float m = 0.f;
+        for (int q = 0; q < 6; q++) {
+            int e = hb[q]; int b = e >= 0 ? e : e ^ 0x7fffffff; float f; memcpy(&f, &b, 4);
+            if (f == f && fabsf(f) <= 3.0e38f && fabsf(f) > m) m = fabsf(f);
+        }
+        sc.max_abs = m;
+    }
+done:
     return err;
 }
 

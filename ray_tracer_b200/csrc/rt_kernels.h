@@ -31,6 +31,15 @@ struct SceneBuffers {
     float4 *c3 = nullptr, *c4 = nullptr, *c5 = nullptr;   // texture extension (uvs + edges), only when has_tex
     bool has_tex = false;
     cudaStream_t stream = nullptr;  // the arrays are stream-ordered allocations on this stream
+    // Build state kept for refit_scene (rt_update_records): the device copies of the caller's records,
+    // the id-order hot records and bounds, the Morton-order permutation and the hierarchy's topology.
+    struct Keep {
+        rt_sphere* sph = nullptr; rt_vertex* vtx = nullptr; uint32_t* idx = nullptr; rt_mesh* mesh = nullptr; uint32_t* tstart = nullptr;
+        float4 *hot = nullptr, *bmin = nullptr, *bmax = nullptr, *lmin = nullptr, *lmax = nullptr, *imin = nullptr, *imax = nullptr;
+        int* bounds = nullptr; uint32_t *ids2 = nullptr, *new_slot = nullptr;
+        int2 *children = nullptr, *ranges = nullptr; int *pin = nullptr, *plf = nullptr, *flags = nullptr;
+        uint32_t nm = 0, leaf_size = 0; int parent_shift = 0;
+    } keep;
     float4 *m0 = nullptr, *m1 = nullptr, *m2 = nullptr;
     float4* nodes = nullptr;
     uint32_t n_prims = 0, n_spheres = 0, n_tris = 0, n_mats = 0, n_nodes = 0, max_depth = 0;
@@ -45,6 +54,11 @@ struct SceneBuffers {
 cudaError_t build_scene(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns, const rt_vertex* vertices,
                         uint32_t nv, const uint32_t* indices, uint32_t ni, const rt_mesh* meshes, uint32_t nm,
                         uint32_t leaf_size, int builder, int ploc_radius, cudaStream_t stream);
+
+// Same topology, new positions / radii / materials: re-derives the records and bounds from the
+// updated spheres and meshes (index ranges must be unchanged) and refits the hierarchy's boxes
+// bottom-up; no sort, no hierarchy build. Synchronous with respect to `stream` on return.
+cudaError_t refit_scene(SceneBuffers& sc, const rt_sphere* spheres, const rt_mesh* meshes, cudaStream_t stream);
 
 cudaError_t launch_tonemap(const float4* accum, uint8_t* rgba8, size_t n_pixels, cudaStream_t stream);
 

@@ -70,6 +70,12 @@ class RayTracer:
         self._ck(self._L.rt_upload_scene(self._h, _ptr(sp), sp.size, _ptr(vs), vs.size, _ptr(ix), ix.size,
                                          _ptr(ms), ms.size))
 
+    def update_records(self, spheres, meshes):
+        """Same topology, moved / re-coloured records: refit instead of rebuild (rt_update_records)."""
+        sp = np.ascontiguousarray(spheres, dtype=SPHERE_DT).reshape(-1)
+        ms = np.ascontiguousarray(meshes, dtype=MESH_DT).reshape(-1)
+        self._ck(self._L.rt_update_records(self._h, _ptr(sp), sp.size, _ptr(ms), ms.size))
+
     # -- texture extension (no reference counterpart) ------------------------------------
     def upload_textures(self, textures):
         """textures: list of (H, W, 4) uint8 arrays (row 0 first); handles in Mesh.diffuse_tex /

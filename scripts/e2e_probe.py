@@ -18,3 +18,12 @@ for b in (1, 0):
     for it in range(3):
         t0 = time.perf_counter(); tr.upload_scene(*scene.arrays()); t1 = time.perf_counter()
         print("builder", b, "upload %.2f ms" % ((t1-t0)*1e3))
+# refit vs rebuild on the 1.1 M-primitive scene
+scene, meta = configs.build("c5_stress", 64, 36)
+tr = rt.RayTracer(0, 64, 36)
+sp, vs, ix, ms = scene.arrays()
+tr.upload_scene(sp, vs, ix, ms)
+ms2 = ms.copy(); ms2["pos"][:, 2] += 5.0
+for it in range(3):
+    t0 = time.perf_counter(); tr.upload_scene(sp, vs, ix, ms); t1 = time.perf_counter(); tr.update_records(sp, ms2); t2 = time.perf_counter()
+    print("c5: rebuild %.2f ms  refit %.2f ms" % ((t1 - t0) * 1e3, (t2 - t1) * 1e3))

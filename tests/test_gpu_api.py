@@ -181,3 +181,43 @@ def test_counters_and_bvh_stats(rtlib):
     tr.reset_counters()
     assert tr.counters()["rays"] == 0
     tr.close()
+
+
+def test_update_records_equals_fresh_upload(rtlib):
+    """rt_update_records (refit on the kept topology) == rt_upload_scene of the moved records,
+    bit for bit, for both builders; topology changes are rejected."""
+    from ray_tracer_b200 import configs
+    scene, meta = configs.build("c5_stress", 96, 54)
+    cam, sp, vs, ix, ms = scene.as_tuple()
+    sp, ms = sp[:2000].copy(), ms.copy()
+    rng = np.random.default_rng(11)
+    sp2, ms2 = sp.copy(), ms.copy()
+    ms2["pos"] += rng.normal(0, 40.0, ms2["pos"].shape).astype(np.float32)       # the teapot instances drift
+    sp2["position"] += rng.normal(0, 25.0, sp2["position"].shape).astype(np.float32)
+    sp2["radius"] *= np.float32(1.5)
+    ms2["color"][:, 0] = 0.9
+    for builder in (0, 1):
+        def render(tr):
+            tr.set_camera(cam); tr.set_params(number_of_bounces=3, rays_per_pixel=1, skybox=1, frames=0)
+            tr.set_option(rtlib._lib.RT_OPT_PRIMARY_IDS, 1)
+            tr.clear(); tr.reset_counters(); tr.render_frames(0, 1)
+            return tr.read_accum(), tr.read_primary_ids(), tr.counters()["rays"]
+        a = rtlib.RayTracer(0, 96, 54); a.set_option(rtlib._lib.RT_OPT_BUILDER, builder)
+        a.upload_scene(sp, vs, ix, ms)
+        img0, _, _ = render(a)
+        a.update_records(sp2, ms2)
+        img_a, ids_a, rays_a = render(a)
+        b = rtlib.RayTracer(0, 96, 54); b.set_option(rtlib._lib.RT_OPT_BUILDER, builder)
+        b.upload_scene(sp2, vs, ix, ms2)
+        img_b, ids_b, rays_b = render(b)
+        assert not np.array_equal(img0, img_a)
+        assert np.array_equal(ids_a, ids_b) and rays_a == rays_b
+        assert np.array_equal(img_a.view(np.uint32), img_b.view(np.uint32))
+        a.update_records(sp, ms)                                                   # and back
+        assert np.array_equal(render(a)[0].view(np.uint32), img0.view(np.uint32))
+        bad = ms2.copy(); bad["triangles"][0] -= 1
+        with pytest.raises(rtlib.RtError):
+            a.update_records(sp2, bad)
+        with pytest.raises(rtlib.RtError):
+            a.update_records(sp2[:-1], ms2)
+        a.close(); b.close()
