@@ -62,3 +62,14 @@ def test_host_library_loads(rtlib):
     for n in ("rth_camera_to_uniform", "rth_scene_builtin", "rth_scene_from_model", "rth_context_new", "rth_context_update",
               "rth_context_render", "rth_context_run_frames", "rth_context_resize", "rth_context_clear_accululation"):
         assert hasattr(L, n)
+
+
+def test_rust_binding_declares_exactly_the_header():
+    """rust/src/lib.rs (source only: no rustc in this image) binds every rt_* entry point of the
+    header, nothing else, and carries the same option numbers."""
+    rs = open(os.path.join(ROOT, "rust", "src", "lib.rs")).read()
+    assert sorted(set(re.findall(r"pub fn (rt_[a-z0-9_]+)", rs))) == _declared()
+    hdr = open(os.path.join(ROOT, "include", "rt_b200.h")).read()
+    opts = dict(re.findall(r"RT_OPT_([A-Z_]+) = (\d+)", hdr))
+    for name, val in re.findall(r"pub const ([A-Z_]+): i32 = (\d+);", rs):
+        assert opts[name] == val, name
