@@ -178,6 +178,7 @@ static double sah_cost(const Tree& t, int leaf_size)
 // ---- traversal statistics: same policy as the CUDA kernel (near child first, prune on tn <= best) ----
 struct Stats { uint64_t rays = 0, nodes = 0, tris = 0, hits = 0; };
 static int g_leaf = 4;
+static bool g_popcull = false;   // stack entries carry their entry distance; popped nodes beyond the closest hit are skipped unfetched
 
 static bool slab(const Box& b, V3 o, V3 inv, float best, float& tn)
 {
@@ -198,7 +199,7 @@ static void leaf_prims(const Tree& t, int n, std::vector<int>& out)
 static int trace(const Tree& t, V3 o, V3 d, float& best, Stats& st)
 {
     V3 inv = {1.f / d.x, 1.f / d.y, 1.f / d.z};
-    int stack[128], sp = 0, hit = -1;
+    int stack[128], sp = 0, hit = -1; float stn[128];
     int node = t.root;
     auto is_leaf = [&](int n) { return n < 0 || t.nodes[n].count <= g_leaf; };
     auto test_leaf = [&](int n) {
@@ -221,10 +222,10 @@ static int trace(const Tree& t, V3 o, V3 d, float& best, Stats& st)
         auto cbox = [&](int c) { return c < 0 ? pbox[~c] : t.nodes[c].box; };
         float tl, tr_; bool hl = slab(cbox(nd.l), o, inv, best, tl), hr = slab(cbox(nd.r), o, inv, best, tr_);
         int next = INT32_MAX;
-        if (hl && hr) { bool lf = tl <= tr_; stack[sp++] = lf ? nd.r : nd.l; next = lf ? nd.l : nd.r; }
+        if (hl && hr) { bool lf = tl <= tr_; stn[sp] = lf ? tr_ : tl; stack[sp++] = lf ? nd.r : nd.l; next = lf ? nd.l : nd.r; }
         else if (hl) next = nd.l; else if (hr) next = nd.r;
         for (;;) {
-            if (next == INT32_MAX) { if (sp == 0) return hit; next = stack[--sp]; }
+            if (next == INT32_MAX) { if (sp == 0) return hit; next = stack[--sp]; if (g_popcull && stn[sp] > best) { next = INT32_MAX; continue; } }
             if (is_leaf(next)) { test_leaf(next); next = INT32_MAX; continue; }
             break;
         }
@@ -281,6 +282,7 @@ int main(int argc, char** argv)
         }
     };
     { Tree t; t.root = lbvh_rec(t, 0, n - 1); report("lbvh", t); }
+    { Tree t = build_ploc(3); report("ploc r=3", t); g_popcull = true; report("ploc3+popcull", t); g_popcull = false; }
     for (int r : {4, 10, 25, 50}) { Tree t = build_ploc(r); char nm[32]; snprintf(nm, sizeof nm, "ploc r=%d", r); report(nm, t); }
     if (n <= 200000) { Tree t; std::vector<int> ids(n); for (int i = 0; i < n; i++) ids[i] = i; t.root = sah_rec(t, ids, 0, n - 1); report("sah sweep", t); }
     return 0;
