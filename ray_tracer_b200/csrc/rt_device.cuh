@@ -69,6 +69,14 @@ struct LaunchParams {
     int32_t sched_n_stay, sched_l_stay, sched_s_min;   // warp scheduler thresholds (lanes)
 };
 
+// 256-bit read-only load (sm_100: LDG.E.256): two float4 from a 32-byte-aligned address in one
+// request, i.e. half the L1 requests / data-pipe wavefronts of two 128-bit loads for the same sector.
+__device__ __forceinline__ void ldg256(const float4* p, float4& a, float4& b)
+{
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w) : "l"(p));
+}
+
 // ---- vector helpers (the fused forms are the arithmetic contract's) -----
 __device__ __forceinline__ float3 f3(float x, float y, float z) { return make_float3(x, y, z); }
 __device__ __forceinline__ float3 operator+(float3 a, float3 b) { return f3(a.x + b.x, a.y + b.y, a.z + b.z); }

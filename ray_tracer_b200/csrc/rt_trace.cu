@@ -208,7 +208,8 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
             while (__popc(__ballot_sync(0xffffffffu, !shading && node >= 0 && node != RT_EMPTY)) >= thr) {
                 if (!shading && node >= 0 && node != RT_EMPTY) {
                     const float4* np = sc.nodes + 4 * (size_t)node;
-                    const float4 n0 = __ldg(np + 0), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3);
+                    float4 n0, n1, n2, n3;
+                    ldg256(np, n0, n1); ldg256(np + 2, n2, n3);
                     if (DETAIL) n_nodes++;
                     // left: centre (n0.x,n0.y,n0.z) half (n0.w,n1.x,n1.y); right: centre (n1.z,n1.w,n2.x) half (n2.y,n2.z,n2.w).
                     // 12 FFMA + 12 FADD on the fma pipe, 4 three-input min/max on the alu pipe (no sign selects).
@@ -242,16 +243,18 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
             while (__ballot_sync(0xffffffffu, !shading && leaf_count != 0u)) {
                 if (!shading && leaf_count != 0u) {
                     const float4* pr = sc.prims + 4 * (size_t)leaf_first;
-                    const float4 q0 = __ldg(pr);
+                    float4 q0, q1;
+                    ldg256(pr, q0, q1);
                     const uint32_t id = __float_as_uint(q0.w);
                     if (id < sc.n_spheres) {
                         if (DETAIL) n_sph++;
-                        test_sphere(ro, rd, q0, __ldg(pr + 1), id, best);
+                        test_sphere(ro, rd, q0, q1, id, best);
                     } else {
                         if (DETAIL) n_tri++;
                         float det;
                         if (triangle_faces_ray(rd, xyz(q0), det)) {
-                            const float4 q1 = __ldg(pr + 1), q2 = __ldg(pr + 2), q3 = __ldg(pr + 3);
+                            float4 q2, q3;
+                            ldg256(pr + 2, q2, q3);
                             test_triangle(ro, rd, xyz(q0), det, xyz(q1), f3(q1.w, q2.x, q2.y), f3(q2.z, q2.w, q3.x), id, best);
                         }
                     }
