@@ -46,7 +46,8 @@ struct rt_ctx {
     rt_params params{};
     rt_camera_uniform camera{};
     uint32_t tile_rank = 0, tile_world = 1, frame_rank = 0, frame_world = 1;
-    int64_t opt_traversal = 0, opt_seed_mode = 0, opt_primary_ids = 0, opt_detail = 0, opt_frames_per_launch = 64, opt_leaf_size = 2, opt_builder = 0, opt_ploc_radius = 3;
+    int64_t opt_traversal = 0, opt_seed_mode = 0, opt_primary_ids = 0, opt_detail = 0, opt_frames_per_launch = 64, opt_leaf_size = 2, opt_builder = 0, opt_ploc_radius = 3, opt_kernel = 0, opt_wave_slots = 1 << 21;
+    rt::WavePool wave;                            // path-slot pool of the wavefront kernels (RT_OPT_KERNEL = 1)
     uint64_t dispatches = 0, launches = 0;
     double kernel_ms = 0.0;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> pending, pool;
@@ -153,8 +154,16 @@ int launch(rt_ctx* c, int32_t first_frame, uint32_t n_frames, bool want_ids)
     if (!c->pool.empty()) { ev = c->pool.back(); c->pool.pop_back(); }
     else { CU(c, cudaEventCreate(&ev.first)); CU(c, cudaEventCreate(&ev.second)); }
     CU(c, cudaEventRecord(ev.first, c->stream));
-    cudaError_t e = rt::launch_trace(sd, to_dev(c->camera), lp, c->staging, c->accum, want_ids ? c->primary_ids : nullptr,
-                                     c->d_counters, c->d_queue, c->opt_traversal == 1, c->opt_detail != 0, c->n_sms, c->stream);
+    cudaError_t e;
+    if (c->opt_kernel == 1) {
+        if ((e = c->wave.ensure((uint32_t)c->opt_wave_slots)) != cudaSuccess) return cuda_fail(c, e, "wavefront pool");
+        e = rt::launch_wave(sd, to_dev(c->camera), lp, c->wave, c->staging, want_ids ? c->primary_ids : nullptr, c->d_counters,
+                            c->opt_traversal == 1, c->opt_detail != 0, c->n_sms, c->stream);
+        if (e == cudaSuccess) e = rt::launch_blend(lp, c->staging, c->accum, c->stream);
+    } else {
+        e = rt::launch_trace(sd, to_dev(c->camera), lp, c->staging, c->accum, want_ids ? c->primary_ids : nullptr,
+                             c->d_counters, c->d_queue, c->opt_traversal == 1, c->opt_detail != 0, c->n_sms, c->stream);
+    }
     if (e != cudaSuccess) return cuda_fail(c, e, "trace kernel launch");
     CU(c, cudaEventRecord(ev.second, c->stream));
     c->pending.push_back(ev);
@@ -234,6 +243,7 @@ void rt_destroy(rt_ctx* c)
     if (c->primary_ids) cudaFree(c->primary_ids);
     if (c->d_counters) cudaFree(c->d_counters);
     if (c->d_queue) cudaFree(c->d_queue);
+    c->wave.release();
     if (c->staging) cudaFree(c->staging);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
@@ -449,6 +459,8 @@ int rt_set_option(rt_ctx* c, int option, int64_t value)
     case RT_OPT_SCHED: c->opt_sched = value & 0xffffff; return RT_OK;
     case RT_OPT_BUILDER: if (value != 0 && value != 1) break; c->opt_builder = value; return RT_OK;
     case RT_OPT_PLOC_RADIUS: if (value < 1 || value > 16) break; c->opt_ploc_radius = value; return RT_OK;
+    case RT_OPT_KERNEL: if (value != 0 && value != 1) break; c->opt_kernel = value; return RT_OK;
+    case RT_OPT_WAVE_SLOTS: if (value < 1024 || value > (1 << 26)) break; c->opt_wave_slots = value; return RT_OK;
     default: return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_set_option: unknown option");
     }
     return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_set_option: value out of range");
@@ -467,6 +479,8 @@ int rt_get_option(const rt_ctx* c, int option, int64_t* value)
     case RT_OPT_SCHED: *value = c->opt_sched; return RT_OK;
     case RT_OPT_BUILDER: *value = c->opt_builder; return RT_OK;
     case RT_OPT_PLOC_RADIUS: *value = c->opt_ploc_radius; return RT_OK;
+    case RT_OPT_KERNEL: *value = c->opt_kernel; return RT_OK;
+    case RT_OPT_WAVE_SLOTS: *value = c->opt_wave_slots; return RT_OK;
     default: return RT_ERR_INVALID_ARGUMENT;
     }
 }

@@ -60,6 +60,32 @@ cudaError_t build_scene(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns
 // bottom-up; no sort, no hierarchy build. Synchronous with respect to `stream` on return.
 cudaError_t refit_scene(SceneBuffers& sc, const rt_sphere* spheres, const rt_mesh* meshes, cudaStream_t stream);
 
+// ---- wavefront execution (rt_wave.cu), RT_OPT_KERNEL = 1 ---------------------------------------
+#ifndef RT_WAVE_MIN_BLOCKS
+#define RT_WAVE_MIN_BLOCKS 10      // resident blocks per SM of the wavefront trace kernel (48 registers per thread)
+#endif
+struct WaveDev {                   // path-slot pool in HBM, 32-byte groups
+    float4* ray;                   // [2s] = (origin, segment index), [2s+1] = (direction, 0)
+    float4* hit;                   // [s]  = (distance, u, v, id)
+    float4* rad;                   // [2s] = incoming light, [2s+1] = ray colour
+    float4* acc;                   // [2s] = item total, [2s+1] = (rng, pixel, dispatch, path index)
+    uint32_t *q_cur, *q_next, *q_hit, *q_miss;
+    unsigned long long* counts;    // queue lengths, fetch cursor, item cursor
+    unsigned long long* stats;     // rays, samples, node visits, tri tests, sphere tests, hits
+};
+struct WavePool {
+    float4 *ray = nullptr, *hit = nullptr, *rad = nullptr, *acc = nullptr;
+    uint32_t *q[2] = {nullptr, nullptr}, *q_hit = nullptr, *q_miss = nullptr;
+    unsigned long long *counts = nullptr, *stats = nullptr, *h_live = nullptr;
+    uint32_t n_slots = 0;
+    cudaError_t ensure(uint32_t slots);
+    void release();
+};
+// Same result as launch_trace (staging planes, counters, primary ids); the caller runs launch_blend next.
+cudaError_t launch_wave(const SceneDev& sc, const CameraDev& cam, const LaunchParams& lp, WavePool& pool, float4* staging,
+                        uint32_t* primary_ids, unsigned long long* counters, bool brute, bool detail, int n_sms, cudaStream_t stream);
+cudaError_t launch_blend(const LaunchParams& lp, const float4* staging, float4* accum, cudaStream_t stream);
+
 cudaError_t launch_tonemap(const float4* accum, uint8_t* rgba8, size_t n_pixels, cudaStream_t stream);
 
 } // namespace rt

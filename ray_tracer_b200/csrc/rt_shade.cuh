@@ -134,7 +134,7 @@ __device__ __forceinline__ float4 sample_texture(const TexDev& t, float u, float
     return mix4(top, bot, fy);
 }
 // diffuse: mcolor *= texel; normal map: normal = normalize(T*n.x + B*n.y + N*n.z), n = 2*rgb - 1
-__device__ __noinline__ void apply_textures(const SceneDev& sc, uint32_t id, float bu, float bv, uint32_t dtex, uint32_t ntex,
+static __device__ __noinline__ void apply_textures(const SceneDev& sc, uint32_t id, float bu, float bv, uint32_t dtex, uint32_t ntex,
                                             float3& normal, float4& mcolor)
 {
     const float4 k3 = __ldg(sc.c3 + id), k4 = __ldg(sc.c4 + id);

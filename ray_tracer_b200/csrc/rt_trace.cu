@@ -358,7 +358,13 @@ cudaError_t launch_trace(const SceneDev& sc, const CameraDev& cam, const LaunchP
     dim3 grid((unsigned)blocks), block(RT_BLOCK_THREADS);
     trace_variant(brute, detail, tex)<<<grid, block, 0, stream>>>(sc, cam, lp, staging, primary_ids, counters, queue);
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    return launch_blend(lp, staging, accum, stream);
+}
+
+cudaError_t launch_blend(const LaunchParams& lp, const float4* staging, float4* accum, cudaStream_t stream)
+{
     const size_t n_local = (size_t)lp.n_warp_tiles * 32u;
+    if (n_local == 0 || lp.n_frames == 0) return cudaSuccess;
     blend_kernel<<<(unsigned)((n_local + 255) / 256), 256, 0, stream>>>(lp, staging, accum);
     return cudaGetLastError();
 }

@@ -9,7 +9,7 @@ from util import assert_bits_equal
 pytestmark = pytest.mark.gpu
 
 
-def _gpu(rt, scene, w, h, frames, bounces, sky, brute=False, leaf=None, builder=None, radius=None):
+def _gpu(rt, scene, w, h, frames, bounces, sky, brute=False, leaf=None, builder=None, radius=None, kernel=None, slots=None, rpp=1, detail=False):
     cam, sp, vs, ix, ms = scene.as_tuple()
     tr = rt.RayTracer(0, w, h)
     if leaf is not None:
@@ -18,11 +18,17 @@ def _gpu(rt, scene, w, h, frames, bounces, sky, brute=False, leaf=None, builder=
         tr.set_option(rt._lib.RT_OPT_BUILDER, builder)
     if radius is not None:
         tr.set_option(rt._lib.RT_OPT_PLOC_RADIUS, radius)
+    if kernel is not None:
+        tr.set_option(rt._lib.RT_OPT_KERNEL, kernel)
+    if slots is not None:
+        tr.set_option(rt._lib.RT_OPT_WAVE_SLOTS, slots)
+    if detail:
+        tr.set_option(rt._lib.RT_OPT_DETAIL_COUNTERS, 1)
     tr.upload_scene(sp, vs, ix, ms)
     if scene.textures:
         tr.upload_textures(scene.textures)
     tr.set_camera(cam)
-    tr.set_params(number_of_bounces=bounces, rays_per_pixel=1, skybox=sky, frames=0)
+    tr.set_params(number_of_bounces=bounces, rays_per_pixel=rpp, skybox=sky, frames=0)
     tr.set_option(rt._lib.RT_OPT_PRIMARY_IDS, 1)
     tr.set_option(rt._lib.RT_OPT_TRAVERSAL, 1 if brute else 0)
     tr.render_frames(0, frames)
@@ -114,3 +120,30 @@ def test_stress_scene_builds_and_matches_brute_force_on_a_crop(rtlib):
     b, bid, bc, _ = _gpu(rtlib, scene, 64, 36, 1, 3, 1, brute=True)
     assert np.array_equal(aid, bid) and ac["rays"] == bc["rays"]
     assert_bits_equal(a, b, "c5")
+
+
+@pytest.mark.parametrize("name,w,h,frames,slots", [("c1_balls", 320, 180, 3, None), ("c2_cube", 320, 180, 3, 4096), ("c3_teapot", 480, 270, 2, 1 << 16),
+                                                   ("c4_tree", 480, 270, 2, None), ("c5_stress", 240, 136, 2, 1 << 14)])
+def test_wavefront_kernels_equal_megakernel(rtlib, name, w, h, frames, slots):
+    """RT_OPT_KERNEL = 1 (trace / hit / miss kernels over a path-slot pool) gives the image, primary ids and the ray,
+    sample and hit counts of the persistent megakernel, whatever the pool size."""
+    from ray_tracer_b200 import configs
+    scene, meta = configs.build(name, w, h)
+    p = meta["params"]
+    a, aid, ac, _ = _gpu(rtlib, scene, w, h, frames, p["number_of_bounces"], p["skybox"], detail=True)
+    b, bid, bc, _ = _gpu(rtlib, scene, w, h, frames, p["number_of_bounces"], p["skybox"], kernel=1, slots=slots, detail=True)
+    assert np.array_equal(aid, bid)
+    for k in ("rays", "samples", "hit_segments"):          # node visits / primitive tests depend on the warp schedule (parked leaves)
+        assert ac[k] == bc[k], k
+    assert_bits_equal(a, b, name)
+
+
+@pytest.mark.parametrize("bounces,rpp,sky,brute", [(0, 1, 1, False), (-1, 1, 1, False), (3, 0, 1, False), (3, -1, 0, False), (2, 3, 0, True), (50, 2, 1, False)])
+def test_wavefront_kernels_edge_parameters(rtlib, oracle, bounces, rpp, sky, brute):
+    """Loop-bound quirks (bounces < 0, rpp <= 0), exhaustive traversal and long paths through the wavefront kernels."""
+    from ray_tracer_b200 import configs
+    scene, _ = configs.build("c1_balls", 64, 36)
+    a, aid, ac, _ = _gpu(rtlib, scene, 64, 36, 2, bounces, sky, rpp=rpp, brute=brute)
+    b, bid, bc, _ = _gpu(rtlib, scene, 64, 36, 2, bounces, sky, rpp=rpp, brute=brute, kernel=1, slots=1024)
+    assert np.array_equal(aid, bid) and ac["rays"] == bc["rays"] and ac["samples"] == bc["samples"]
+    assert_bits_equal(a, b, "bounces %d rpp %d" % (bounces, rpp), any_nan=(rpp == 0))
