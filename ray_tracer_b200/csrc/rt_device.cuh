@@ -57,6 +57,26 @@ struct CameraDev {         // the fields of CameraUniform the shader reads (wgsl
     float lens_radius;
 };
 
+// Exact unsigned 32-bit division by a launch constant (Granlund-Montgomery round-up multiplier):
+// q = (t + ((n - t) >> s1)) >> s2 with t = umulhi(m, n); 5 instructions instead of the ~25 of a
+// hardware-less integer division, and the item decode runs with few lanes active.
+struct FastDiv {
+    uint32_t d, m, s1, s2;
+    __host__ __device__ __forceinline__ uint32_t div(uint32_t n) const
+    {
+        const uint32_t t = (uint32_t)(((unsigned long long)m * n) >> 32);    // IMAD.HI
+        return (t + ((n - t) >> s1)) >> s2;
+    }
+};
+inline FastDiv make_fastdiv(uint32_t d)
+{
+    FastDiv f; f.d = d ? d : 1u;
+    uint32_t l = 0; while ((1ull << l) < f.d) l++;
+    f.m = (uint32_t)((((1ull << l) - f.d) << 32) / f.d + 1ull);
+    f.s1 = l < 1u ? l : 1u; f.s2 = l ? l - 1u : 0u;
+    return f;
+}
+
 struct LaunchParams {
     uint32_t width, height;
     int32_t bounces, rpp, toggle;
@@ -67,6 +87,8 @@ struct LaunchParams {
     uint32_t tiles_x, n_warp_tiles;  // 8x8 shard tiles per row; 8x4 warp tiles owned by this rank (2 per shard tile)
     int32_t seed_mode;
     int32_t sched_n_stay, sched_l_stay, sched_s_min;   // warp scheduler thresholds (lanes)
+    FastDiv div_frames, div_tiles_x, div_width;         // item decode without integer divisions
+    float rpp_scale;                                    // 1/rpp when rpp is a power of two (x/2^k == x*2^-k exactly), else 0
 };
 
 // 256-bit read-only load (sm_100: LDG.E.256): two float4 from a 32-byte-aligned address in one

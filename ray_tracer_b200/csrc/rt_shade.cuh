@@ -103,6 +103,30 @@ __device__ __forceinline__ uint32_t pixel_seed(uint32_t x, uint32_t y, uint32_t 
     return __float2uint_rz(lin) + af * 71939u;
 }
 
+// Work item g -> (pixel, dispatch): items are numbered tile-major, dispatch-minor, 32 pixels (an 8x4
+// warp tile) at a time; shard tile t belongs to rank t % tile_world.  False when the pixel lies
+// outside the image (the tile grid is rounded up).
+__device__ __forceinline__ bool decode_item(const LaunchParams& lp, uint64_t g, uint32_t& px, uint32_t& py, uint32_t& fi)
+{
+    const uint32_t pos = (uint32_t)(g & 31ull);
+    const uint64_t tf = g >> 5;
+    uint32_t wt;
+    if ((tf >> 32) == 0ull) { wt = lp.div_frames.div((uint32_t)tf); fi = (uint32_t)tf - wt * lp.n_frames; }
+    else { fi = (uint32_t)(tf % lp.n_frames); wt = (uint32_t)(tf / lp.n_frames); }
+    const uint32_t t = (wt >> 1) * lp.tile_world + lp.tile_rank;
+    const uint32_t ty = lp.div_tiles_x.div(t), tx = t - ty * lp.tiles_x;
+    px = tx * 8u + (pos & 7u);
+    py = ty * 8u + (wt & 1u) * 4u + (pos >> 3);
+    return px < lp.width && py < lp.height;
+}
+// wgsl:326 `pixel_color / f32(rpp)`: an exact power-of-two scale when it can be, else the IEEE division
+__device__ __forceinline__ float4 frag_of_total(const LaunchParams& lp, float4 total)
+{
+    if (lp.rpp_scale != 0.0f) return make_float4(total.x * lp.rpp_scale, total.y * lp.rpp_scale, total.z * lp.rpp_scale, total.w * lp.rpp_scale);
+    const float rppf = (float)lp.rpp;
+    return make_float4(total.x / rppf, total.y / rppf, total.z / rppf, total.w / rppf);
+}
+
 // ---- texture extension (no reference counterpart; arithmetic specified by the oracle's
 // sample_texture / apply_textures) ----------------------------------------------------------
 // The four texels come through the texture path (CUDA array + texture object, point

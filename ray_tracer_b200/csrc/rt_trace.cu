@@ -107,8 +107,7 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
                     need_path = true;                                                              // fresh item
                 }
                 if (need_path && j > lp.rpp) {
-                    staging[(size_t)fi * plane + pix] =
-                        make_float4(total.x / rppf, total.y / rppf, total.z / rppf, total.w / rppf);   // wgsl:326
+                    staging[(size_t)fi * plane + pix] = frag_of_total(lp, total);                       // wgsl:326
                     has_item = false; need_path = false;
                 }
             }
@@ -126,15 +125,8 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
                 const uint32_t rank = __popc(want & ((1u << lane) - 1u));
                 const uint64_t avail = pool_end - pool_next;
                 if (mine && rank < avail) {
-                    const uint64_t g = pool_next + rank;
-                    const uint32_t pos = (uint32_t)(g & 31ull);
-                    const uint64_t tf = g >> 5;
-                    fi = (uint32_t)(tf % lp.n_frames);
-                    const uint32_t wt = (uint32_t)(tf / lp.n_frames);            // local 8x4 warp tile
-                    const uint32_t t = (wt >> 1) * lp.tile_world + lp.tile_rank; // 8x8 shard tile (tile t -> rank t % world)
-                    const uint32_t px = (t % lp.tiles_x) * 8u + (pos & 7u);
-                    const uint32_t py = (t / lp.tiles_x) * 8u + (wt & 1u) * 4u + (pos >> 3);
-                    if (px < lp.width && py < lp.height) {                       // else: outside the image, ask again
+                    uint32_t px, py;
+                    if (decode_item(lp, pool_next + rank, px, py, fi)) {         // else: outside the image, ask again
                         pix = py * lp.width + px;
                         rng = pixel_seed(px, py, lp.width, lp.height, lp.first_frame + (int32_t)(fi * lp.frame_world));
                         j = 0; has_item = true; need_path = true;
@@ -154,7 +146,7 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
             if (shading && !idle) {
                 if (need_path) {
                     // camera ray, wgsl:313-321
-                    const uint32_t px = pix % lp.width, py = pix / lp.width;
+                    const uint32_t py = lp.div_width.div(pix), px = pix - py * lp.width;
                     float aax = rand01(rng), aay = rand01(rng);
                     float posx = ((float)px + aax) / sw, posy = ((float)py + aay) / sh;
                     float rdx, rdy;

@@ -325,7 +325,7 @@ wave_miss(CameraDev cam, WaveDev wv, LaunchParams lp, float4* __restrict__ stagi
         float3 ro = f3(0.f, 0.f, 0.f), rd = ro;
         for (;;) {                                                                         // block-uniform trip count
             if (need_ray && has_item && j > lp.rpp) {
-                staging[(size_t)fi * plane + pix] = make_float4(tot.x / rppf, tot.y / rppf, tot.z / rppf, tot.w / rppf);   // wgsl:326
+                staging[(size_t)fi * plane + pix] = frag_of_total(lp, tot);                // wgsl:326
                 has_item = false;
             }
             // next work items: same numbering as the megakernel (tile-major, dispatch-minor, 32 pixels at a time)
@@ -334,14 +334,8 @@ wave_miss(CameraDev cam, WaveDev wv, LaunchParams lp, float4* __restrict__ stagi
             if (want) {
                 if (g >= n_items) need_ray = false;                                        // no work left: the slot dies
                 else {
-                    const uint32_t pos = (uint32_t)(g & 31ull);
-                    const uint64_t tf = g >> 5;
-                    fi = (uint32_t)(tf % lp.n_frames);
-                    const uint32_t wt = (uint32_t)(tf / lp.n_frames);
-                    const uint32_t t = (wt >> 1) * lp.tile_world + lp.tile_rank;
-                    const uint32_t px = (t % lp.tiles_x) * 8u + (pos & 7u);
-                    const uint32_t py = (t / lp.tiles_x) * 8u + (wt & 1u) * 4u + (pos >> 3);
-                    if (px < lp.width && py < lp.height) {                                 // else: outside the image, ask again
+                    uint32_t px, py;
+                    if (decode_item(lp, g, px, py, fi)) {                                  // else: outside the image, ask again
                         pix = py * lp.width + px;
                         rng = pixel_seed(px, py, lp.width, lp.height, lp.first_frame + (int32_t)(fi * lp.frame_world));
                         j = 0; has_item = true;
@@ -355,7 +349,7 @@ wave_miss(CameraDev cam, WaveDev wv, LaunchParams lp, float4* __restrict__ stagi
             }
             if (need_ray && has_item) {
                 // camera ray, wgsl:313-321
-                const uint32_t px = pix % lp.width, py = pix / lp.width;
+                const uint32_t py = lp.div_width.div(pix), px = pix - py * lp.width;
                 float aax = rand01(rng), aay = rand01(rng);
                 float posx = ((float)px + aax) / sw, posy = ((float)py + aay) / sh;
                 float rdx, rdy;

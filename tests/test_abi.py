@@ -73,3 +73,15 @@ def test_rust_binding_declares_exactly_the_header():
     opts = dict(re.findall(r"RT_OPT_([A-Z_]+) = (\d+)", hdr))
     for name, val in re.findall(r"pub const ([A-Z_]+): i32 = (\d+);", rs):
         assert opts[name] == val, name
+
+
+def test_fastdiv_is_exact(tmp_path):
+    """rt::FastDiv (the item decode's division by launch constants) against `/` on the host: edge values,
+    multiples of the divisor and their neighbours, a pseudo-random sweep, every dividend below 2^26."""
+    import shutil, subprocess
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    exe = str(tmp_path / "fastdiv_check")
+    subprocess.run([nvcc, "-O2", "-std=c++17", "-Wno-deprecated-gpu-targets", "-I", os.path.join(ROOT, "ray_tracer_b200", "csrc"),
+                    "-o", exe, os.path.join(ROOT, "tests", "native", "fastdiv_check.cu")], check=True, capture_output=True)
+    out = subprocess.run([exe], check=True, capture_output=True, text=True).stdout
+    assert out.startswith("OK"), out
