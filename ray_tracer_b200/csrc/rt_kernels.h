@@ -14,6 +14,21 @@
 #endif
 #define RT_STACK 64                 // traversal stack entries per lane (BVH depth limit checked at upload)
 
+
+// Subtrees are skipped when the ray enters their (padded) box beyond best.dst * RT_CULL_SLACK, not beyond
+// best.dst itself.  The reference's computed distances carry rounding error that grows as a ray grazes a
+// primitive: a sphere's dst = (-b - sqrt(disc)) / 2a is off by up to 2^-12 relative when disc ~ 0 (the square
+// root of the rounding error of b*b - 4ac), a triangle's dst = dot(ao, n) / det by 2^-23 / sin(grazing angle).
+// So a primitive's computed distance can be smaller than the distance at which the ray enters its box; in the
+// reference's exhaustive scan it still wins, here it would be skipped whenever a slightly farther hit was
+// found first -- and whether it was depends on when a parked leaf gets tested, i.e. on the warp schedule.
+// Seen on C5 at 4K with the radix-tree builder: 2 pixels of 8.3 M changed from render to render
+// (scripts/order_probe.py); with the slack 30 renders and 12 rebuilds agree and the 4K image equals exhaustive
+// mode at every pixel (scripts/brute_check.py).  2^-9 covers the sphere bound 8 times over.
+#ifndef RT_CULL_SLACK
+#define RT_CULL_SLACK 1.001953125f  // 1 + 2^-9 (2^-7 costs 2.7 % of the rays per second on C3, 2^-9 and 2^-11 0.6 %)
+#endif
+
 namespace rt {
 
 #define RT_QUEUE_CHUNK 128ull     // work items a warp takes from the global queue per atomic

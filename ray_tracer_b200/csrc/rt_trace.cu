@@ -44,6 +44,15 @@ namespace rt {
 //              primitives are tested with most lanes busy.
 // The warp goes back to SHADE when enough lanes have finished their ray (sched_s_min), the
 // others keep their traversal state (node, stack, closest hit) across the switch.
+#ifndef RT_NODE_U2
+#define RT_NODE_U2 1                 // lanes able to step for a second / third node step on the same warp vote
+#endif
+#ifndef RT_NODE_U3
+#define RT_NODE_U3 12
+#endif
+#ifndef RT_NODE_U4
+#define RT_NODE_U4 20
+#endif
 #define RT_EMPTY 0x7fffffff                        // "no current node": traversal stack exhausted
 
 template <bool BRUTE, bool DETAIL, bool TEX>
@@ -54,6 +63,7 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
 {
     const uint32_t lane = threadIdx.x & 31u;
     int stack[RT_STACK];                           // local memory: lane-interleaved by the hardware, only touched levels occupy L1
+    stack[0] = RT_EMPTY;                           // sentinel under every traversal (sp starts at 1): a pop needs no emptiness test
 
     const uint64_t n_items = (uint64_t)lp.n_warp_tiles * lp.n_frames * 32ull;
     const size_t plane = (size_t)lp.width * lp.height;
@@ -80,6 +90,7 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
     uint32_t& fi = s_item[threadIdx.x].y;
     total = make_float4(0.f, 0.f, 0.f, 0.f); pix = 0; fi = 0;
     HitRec best; best.dst = RT_FLT_MAX; best.u = best.v = 0.f; best.id = RT_MISS;
+    float cull = RT_FLT_MAX;                       // best.dst with slack: the distance beyond which a subtree is skipped (see RT_CULL_SLACK)
     int node = RT_EMPTY, sp = 0;                   // current node (inner >= 0, leaf < 0, or RT_EMPTY) / stack height
     uint32_t leaf_first = 0, leaf_count = 0;       // parked leaf primitives
 
@@ -165,8 +176,8 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
                     n_samples++;
                 }
                 // ---- start the traversal of (ro, rd): wgsl:234 ----
-                best.dst = RT_FLT_MAX; best.u = 0.0f; best.v = 0.0f; best.id = RT_MISS;
-                sp = 0; node = RT_EMPTY; leaf_count = 0;
+                best.dst = RT_FLT_MAX; best.u = 0.0f; best.v = 0.0f; best.id = RT_MISS; cull = RT_FLT_MAX;
+                sp = 1; node = RT_EMPTY; leaf_count = 0;
                 if (lp.bounces < 0) {
                     total = total + incoming; j++;                // wgsl:233 loop never runs: the path ends untraced
                     traced = false;                               // stays "shading" as a fresh lane needing a path
@@ -197,7 +208,7 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
             // (left when fewer than `thr` lanes can still take a node step; thr adapts so a thin warp still advances)
             const int cnt0 = __popc(__ballot_sync(0xffffffffu, !shading && node >= 0 && node != RT_EMPTY));
             const int thr = max(1, min(lp.sched_n_stay, (cnt0 + 1) >> 1));
-            while (__popc(__ballot_sync(0xffffffffu, !shading && node >= 0 && node != RT_EMPTY)) >= thr) {
+            auto node_step = [&]() {
                 if (!shading && node >= 0 && node != RT_EMPTY) {
                     const float4* np = sc.nodes + 4 * (size_t)node;
                     float4 n0, n1, n2, n3;
@@ -212,9 +223,9 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
                     const float ray_ = __fmaf_rn(n1.w, inv.y, noi.y), rby = __fmaf_rn(n2.z, ainv.y, pi.y);
                     const float raz = __fmaf_rn(n2.x, inv.z, noi.z), rbz = __fmaf_rn(n2.w, ainv.z, pi.z);
                     const float ltn = fmaxf(fmaxf(lax - lbx, lay - lby), fmaxf(laz - lbz, 0.0f));
-                    const float ltf = fminf(fminf(lax + lbx, lay + lby), fminf(laz + lbz, best.dst));
+                    const float ltf = fminf(fminf(lax + lbx, lay + lby), fminf(laz + lbz, cull));
                     const float rtn = fmaxf(fmaxf(rax - rbx, ray_ - rby), fmaxf(raz - rbz, 0.0f));
-                    const float rtf = fminf(fminf(rax + rbx, ray_ + rby), fminf(raz + rbz, best.dst));
+                    const float rtf = fminf(fminf(rax + rbx, ray_ + rby), fminf(raz + rbz, cull));
                     const bool hl = ltn <= ltf, hr = rtn <= rtf;
                     const int cl = __float_as_int(n3.x), cr = __float_as_int(n3.y);
                     if (hl && hr) {
@@ -223,13 +234,22 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
                         node = left_first ? cl : cr;
                     } else if (hl) node = cl;
                     else if (hr) node = cr;
-                    else node = (sp > 0) ? stack[--sp] : RT_EMPTY;
+                    else node = stack[--sp];
                     if (node < 0 && leaf_count == 0u) {          // park the leaf, keep descending
                         const uint32_t leaf = (uint32_t)(~node);
                         leaf_first = leaf >> 3; leaf_count = (leaf & 7u) + 1u;
-                        node = (sp > 0) ? stack[--sp] : RT_EMPTY;
+                        node = stack[--sp];
                     }
                 }
+            };
+            for (;;) {
+                // one vote pays for up to four node steps when most lanes can take them (a lane that runs out idles for the rest)
+                const int cnt = __popc(__ballot_sync(0xffffffffu, !shading && node >= 0 && node != RT_EMPTY));
+                if (cnt < thr) break;
+                node_step();
+                if (cnt >= RT_NODE_U2) node_step();
+                if (cnt >= RT_NODE_U3) node_step();
+                if (cnt >= RT_NODE_U4) node_step();
             }
             // ---- leaf loop: test parked primitives, one per lane per step ----
             while (__ballot_sync(0xffffffffu, !shading && leaf_count != 0u)) {
@@ -250,11 +270,12 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
                             test_triangle(ro, rd, xyz(q0), det, xyz(q1), f3(q1.w, q2.x, q2.y), f3(q2.z, q2.w, q3.x), id, best);
                         }
                     }
+                    cull = best.dst * RT_CULL_SLACK;
                     leaf_first++;
                     if (--leaf_count == 0u && node < 0) {        // a second leaf was waiting in `node`
                         const uint32_t leaf = (uint32_t)(~node);
                         leaf_first = leaf >> 3; leaf_count = (leaf & 7u) + 1u;
-                        node = (sp > 0) ? stack[--sp] : RT_EMPTY;
+                        node = stack[--sp];
                     }
                 }
             }

@@ -106,6 +106,7 @@ wave_trace(SceneDev sc, WaveDev wv, int n_stay, int refill_min)
 {
     const uint32_t lane = threadIdx.x & 31u;
     int stack[RT_STACK];
+    stack[0] = WV_EMPTY;                             // sentinel under every traversal (sp starts at 1)
     const unsigned long long n_queued = wv.counts[WC_CUR];
     const uint32_t* __restrict__ qcur = wv.q_cur;
     uint32_t n_rays = 0, n_nodes = 0, n_tri = 0, n_sph = 0;
@@ -116,7 +117,8 @@ wave_trace(SceneDev sc, WaveDev wv, int n_stay, int refill_min)
     uint32_t slot = 0;
     float3 ro = f3(0.f, 0.f, 0.f), rd = ro, inv = ro, noi = ro, ainv = ro, pi = ro;
     HitRec best; best.dst = RT_FLT_MAX; best.u = best.v = 0.f; best.id = RT_MISS;
-    int node = WV_EMPTY, sp = 0;
+    float cull = RT_FLT_MAX;                         // best.dst with slack (RT_CULL_SLACK, rt_kernels.h)
+    int node = WV_EMPTY, sp = 1;
     uint32_t leaf_first = 0, leaf_count = 0;
 
     for (;;) {
@@ -137,8 +139,8 @@ wave_trace(SceneDev sc, WaveDev wv, int n_stay, int refill_min)
                 float4 a, b;
                 ld256(wv.ray + 2 * (size_t)slot, a, b);
                 ro = xyz(a); rd = xyz(b);
-                best.dst = RT_FLT_MAX; best.u = 0.0f; best.v = 0.0f; best.id = RT_MISS;
-                sp = 0; node = WV_EMPTY; leaf_count = 0; leaf_first = 0;
+                best.dst = RT_FLT_MAX; best.u = 0.0f; best.v = 0.0f; best.id = RT_MISS; cull = RT_FLT_MAX;
+                sp = 1; node = WV_EMPTY; leaf_count = 0; leaf_first = 0;
                 if (BRUTE) leaf_count = sc.n_prims;
                 else if (sc.root >= 0) {
                     node = sc.root;
@@ -174,9 +176,9 @@ wave_trace(SceneDev sc, WaveDev wv, int n_stay, int refill_min)
                     const float ray_ = __fmaf_rn(n1.w, inv.y, noi.y), rby = __fmaf_rn(n2.z, ainv.y, pi.y);
                     const float raz = __fmaf_rn(n2.x, inv.z, noi.z), rbz = __fmaf_rn(n2.w, ainv.z, pi.z);
                     const float ltn = fmaxf(fmaxf(lax - lbx, lay - lby), fmaxf(laz - lbz, 0.0f));
-                    const float ltf = fminf(fminf(lax + lbx, lay + lby), fminf(laz + lbz, best.dst));
+                    const float ltf = fminf(fminf(lax + lbx, lay + lby), fminf(laz + lbz, cull));
                     const float rtn = fmaxf(fmaxf(rax - rbx, ray_ - rby), fmaxf(raz - rbz, 0.0f));
-                    const float rtf = fminf(fminf(rax + rbx, ray_ + rby), fminf(raz + rbz, best.dst));
+                    const float rtf = fminf(fminf(rax + rbx, ray_ + rby), fminf(raz + rbz, cull));
                     const bool hl = ltn <= ltf, hr = rtn <= rtf;
                     const int cl = __float_as_int(n3.x), cr = __float_as_int(n3.y);
                     if (hl && hr) {
@@ -185,11 +187,11 @@ wave_trace(SceneDev sc, WaveDev wv, int n_stay, int refill_min)
                         node = left_first ? cl : cr;
                     } else if (hl) node = cl;
                     else if (hr) node = cr;
-                    else node = (sp > 0) ? stack[--sp] : WV_EMPTY;
+                    else node = stack[--sp];
                     if (node < 0 && leaf_count == 0u) {
                         const uint32_t leaf = (uint32_t)(~node);
                         leaf_first = leaf >> 3; leaf_count = (leaf & 7u) + 1u;
-                        node = (sp > 0) ? stack[--sp] : WV_EMPTY;
+                        node = stack[--sp];
                     }
                 }
             }
@@ -211,11 +213,12 @@ wave_trace(SceneDev sc, WaveDev wv, int n_stay, int refill_min)
                             test_triangle(ro, rd, xyz(q0), det, xyz(q1), f3(q1.w, q2.x, q2.y), f3(q2.z, q2.w, q3.x), id, best);
                         }
                     }
+                    cull = best.dst * RT_CULL_SLACK;
                     leaf_first++;
                     if (--leaf_count == 0u && node < 0) {
                         const uint32_t leaf = (uint32_t)(~node);
                         leaf_first = leaf >> 3; leaf_count = (leaf & 7u) + 1u;
-                        node = (sp > 0) ? stack[--sp] : WV_EMPTY;
+                        node = stack[--sp];
                     }
                 }
             }
