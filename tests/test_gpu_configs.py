@@ -169,3 +169,27 @@ def test_image_does_not_depend_on_schedule_or_builder_at_4k(rtlib):
     for rays, img in imgs[1:]:
         assert rays == imgs[0][0]
         assert_bits_equal(img, imgs[0][1], "c5_stress 4K")
+
+
+@pytest.mark.parametrize("name,frames", [("c3_teapot", 2), ("c4_tree", 1), ("c2_cube", 2)])
+def test_full_size_image_equals_exhaustive_mode(rtlib, name, frames):
+    """BASELINE.json's full resolutions (1080p / 4K): every pixel and every primary id through the hierarchy equals
+    the GPU's exhaustive scan of all primitives (the reference's own loop, wgsl:149-185)."""
+    from ray_tracer_b200 import configs
+    scene, meta = configs.build(name)
+    p = meta["params"]
+    a, aid, ac, _ = _gpu(rtlib, scene, p["width"], p["height"], frames, p["number_of_bounces"], p["skybox"])
+    b, bid, bc, _ = _gpu(rtlib, scene, p["width"], p["height"], frames, p["number_of_bounces"], p["skybox"], brute=True)
+    assert np.array_equal(aid, bid) and ac["rays"] == bc["rays"]
+    assert_bits_equal(a, b, name)
+
+
+def test_teapot_vs_oracle_at_eighth_resolution(rtlib, oracle):
+    """C3 at 240x136, one dispatch (88 k rays x 15,704 triangles on the CPU): image, ids and ray count bit for bit."""
+    from ray_tracer_b200 import configs
+    scene, meta = configs.build("c3_teapot", 240, 136)
+    p = meta["params"]
+    gi, gid, gc, _ = _gpu(rtlib, scene, 240, 136, 1, p["number_of_bounces"], p["skybox"])
+    ci, cid, cc = _cpu(oracle, scene, 240, 136, 1, p["number_of_bounces"], p["skybox"])
+    assert np.array_equal(gid, cid) and gc["rays"] == int(cc[0])
+    assert_bits_equal(gi, ci, "c3_teapot 240x136")
