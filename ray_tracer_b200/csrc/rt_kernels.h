@@ -9,9 +9,6 @@
 #ifndef RT_MIN_BLOCKS
 #define RT_MIN_BLOCKS 8            // resident blocks per SM the trace kernel is compiled for (64 registers per thread)
 #endif
-#ifndef RT_SMEM_STACK
-#define RT_SMEM_STACK 0
-#endif
 #define RT_STACK 64                 // traversal stack entries per lane (BVH depth limit checked at upload)
 
 
