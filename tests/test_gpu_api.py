@@ -221,3 +221,24 @@ def test_update_records_equals_fresh_upload(rtlib):
         with pytest.raises(rtlib.RtError):
             a.update_records(sp2[:-1], ms2)
         a.close(); b.close()
+
+
+def test_wavefront_kernels_respect_the_shard(rtlib):
+    """RT_OPT_KERNEL = 1 under tile + sample sharding, an odd image size and a resumed accumulation: same image as
+    the megakernel with the same shard."""
+    scene = _scene()
+    out = []
+    for kernel in (0, 1):
+        cam, sp, vs, ix, ms = scene
+        tr = rtlib.RayTracer(0, 75, 43)
+        tr.set_option(rtlib._lib.RT_OPT_KERNEL, kernel)
+        tr.set_option(rtlib._lib.RT_OPT_WAVE_SLOTS, 2048)
+        tr.upload_scene(sp, vs, ix, ms); tr.set_camera(cam)
+        tr.set_params(number_of_bounces=BOUNCES, rays_per_pixel=2, skybox=1, frames=0)
+        tr.set_shard(tile_rank=1, tile_world=3, frame_rank=1, frame_world=2)
+        tr.render_frames(1, 3)
+        tr.render_frames(7, 2)
+        out.append((tr.read_accum(), tr.counters()))
+        tr.close()
+    assert out[0][1]["rays"] == out[1][1]["rays"] and out[0][1]["samples"] == out[1][1]["samples"]
+    assert_bits_equal(out[0][0], out[1][0], "wavefront under sharding")
