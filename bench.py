@@ -41,6 +41,9 @@ F_SHADE = 110
 F_MISS = 30
 
 
+_JSON_OUT = sys.stdout
+
+
 def peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -162,7 +165,7 @@ def run_reference(args, rank, world):
         "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_JSON_OUT, flush=True)
 
 
 class _DevArray:
@@ -327,7 +330,8 @@ def run_ours(args, rank, world, local_rank):
                     "steps": e2e_steps, "what": "rt_upload_scene (host records -> SoA + LBVH build) + rt_render_frames + rt_read_accum, wall clock"},
             "gpu_launches": int(ctr["launches"]),
             "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak_tf.value, "unit": "TFLOP/s",
-                         "frac": achieved / peak_tf.value if peak_tf.value else None, "traffic": ncu_traffic(args.config),
+                         "frac": achieved / peak_tf.value if peak_tf.value else None,
+                         "traffic": (ncu_traffic(args.config) or {}).get("dram_bytes_per_launch"), "traffic_detail": ncu_traffic(args.config),
                          "peak_source": "FFMA microbenchmark run in this process (rt_measure_fp32_peak); theoretical 148x128x2x%.0f MHz = %.1f" % (
                              pk.get("sm_max_mhz", 1965.0), 148 * 128 * 2 * pk.get("sm_max_mhz", 1965.0) * 1e6 / 1e12),
                          "kernel": "rt::trace_kernel<BRUTE=false,DETAIL=false,TEX=%s>" % ("true" if scene.textures else "false"), "launch_ms": launch_s * 1e3,
@@ -344,7 +348,7 @@ def run_ours(args, rank, world, local_rank):
             v, r, dt, threads = cpu_sample(scene, p, 0, 2, CPU_STRIDE)
             line["cpu_baseline"] = {"value": v, "unit": "Mrays/s", "cores": threads, "kind": "port",
                                     "sample": "2 dispatches (4 spp) over every %dth pixel in x and y (%d rays, %.1f s), brute force" % (CPU_STRIDE, r, dt)}
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=_JSON_OUT, flush=True)
     tr.close()
     if world > 1:
         dist.destroy_process_group()
@@ -365,6 +369,12 @@ def main():
     global METRIC
     if args.config != "c3_teapot":
         METRIC = "Mrays/s (all bounces) at %s" % args.config      # BASELINE.json's metric is quoted on C3; other configs are labelled as such
+    # stdout carries the JSON line and nothing else: libraries that write to file descriptor 1 on their own
+    # (NCCL prints its version there under torchrun) are pointed at stderr while the benchmark runs
+    global _JSON_OUT
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args, rank, world)
     else:
