@@ -248,11 +248,18 @@ __device__ __forceinline__ float union_area(float4 alo, float4 ahi, float4 blo, 
 
 #define PLOC_THREADS 256
 #define PLOC_MAX_RADIUS 16
+#define PLOC_ROUNDS_PER_CHECK 8
 // nearest neighbour inside the window; ties: the parity partner i^1 first (so that runs of
 // identical boxes pair up), then the closer index, then the smaller one.  NaN areas never win.
-__global__ void ploc_nn(int m, int radius, int force_pairs, const float4* __restrict__ clo, const float4* __restrict__ chi, int* __restrict__ nn)
+// The round loop runs from device-side state st = {clusters left, nodes created, force flag}: the host
+// launches rounds in batches for an upper bound of the cluster count and reads the state back once
+// per batch, so an upload costs a handful of host round trips instead of one per round; rounds
+// launched after the last merge return at once.
+__global__ void ploc_nn(const int* __restrict__ st, int radius, const float4* __restrict__ clo, const float4* __restrict__ chi, int* __restrict__ nn)
 {
     __shared__ float4 slo[PLOC_THREADS + 2 * PLOC_MAX_RADIUS], shi[PLOC_THREADS + 2 * PLOC_MAX_RADIUS];
+    const int m = st[0], force_pairs = st[2];
+    if (m <= 1 || (int)(blockIdx.x * PLOC_THREADS) >= m) return;      // block-uniform
     const int base = blockIdx.x * PLOC_THREADS - radius;
     for (int t = threadIdx.x; t < PLOC_THREADS + 2 * radius; t += PLOC_THREADS) {
         int g = base + t;
@@ -278,10 +285,11 @@ __global__ void ploc_nn(int m, int radius, int force_pairs, const float4* __rest
 }
 
 // keep flag (high word) and merge flag (low word) of every cluster, for one 64-bit prefix sum
-__global__ void ploc_flags(int m, const int* __restrict__ nn, unsigned long long* __restrict__ flags)
+__global__ void ploc_flags(const int* __restrict__ st, const int* __restrict__ nn, unsigned long long* __restrict__ flags)
 {
+    const int m = st[0];
     int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= m) return;
+    if (m <= 1 || i >= m) return;
     int j = nn[i];
     bool mutual = j >= 0 && nn[j] == i;
     unsigned long long keep = (!mutual || i < j) ? 1ull : 0ull, merge = (mutual && i < j) ? 1ull : 0ull;
@@ -289,14 +297,15 @@ __global__ void ploc_flags(int m, const int* __restrict__ nn, unsigned long long
 }
 
 // parents are stored as (node << 1) | is_right_child, -1 for the root
-__global__ void ploc_scatter(int m, int node_base, const int* __restrict__ nn, const unsigned long long* __restrict__ pos,
+__global__ void ploc_scatter(const int* __restrict__ st, const int* __restrict__ nn, const unsigned long long* __restrict__ pos,
                              const int* __restrict__ cid, const float4* __restrict__ clo, const float4* __restrict__ chi,
                              int* __restrict__ cid2, float4* __restrict__ clo2, float4* __restrict__ chi2,
                              int2* __restrict__ children, float4* __restrict__ imin, float4* __restrict__ imax,
                              int* __restrict__ par_inner, int* __restrict__ par_leaf, unsigned int* __restrict__ totals)
 {
+    const int m = st[0], node_base = st[1];
     int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= m) return;
+    if (m <= 1 || i >= m) return;
     const int j = nn[i];
     const bool mutual = j >= 0 && nn[j] == i;
     const unsigned long long p = pos[i];
@@ -321,6 +330,17 @@ __global__ void ploc_scatter(int m, int node_base, const int* __restrict__ nn, c
         totals[0] = out + (keep ? 1u : 0u);
         totals[1] = mrg + (merge ? 1u : 0u);
     }
+}
+
+// end of a round: survivors become the cluster list, new nodes are counted, a round without a mutual
+// pair (only possible with tied areas) forces neighbour pairs next time
+__global__ void ploc_advance(int* st, const unsigned int* __restrict__ totals)
+{
+    if (st[0] <= 1) return;
+    st[1] += (int)totals[1];
+    st[2] = totals[1] == 0u;
+    st[0] = (int)totals[0];
+    st[3] += 1;
 }
 
 // Final primitive layout of a PLOC tree: a node's first slot = number of primitives to its
@@ -464,7 +484,7 @@ cudaError_t build_scene(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns
     int* d_bounds = nullptr; uint64_t *keys = nullptr, *keys2 = nullptr; uint32_t *ids = nullptr, *ids2 = nullptr, *new_slot = nullptr;
     int2 *children = nullptr, *ranges = nullptr; int *pin = nullptr, *plf = nullptr, *flags = nullptr, *d_depth = nullptr;
     int *cidA = nullptr, *cidB = nullptr, *nn = nullptr; float4 *cloA = nullptr, *chiA = nullptr, *cloB = nullptr, *chiB = nullptr;
-    unsigned long long *pflags = nullptr, *ppos = nullptr; unsigned int* d_tot = nullptr;
+    unsigned long long *pflags = nullptr, *ppos = nullptr; unsigned int* d_tot = nullptr; int* d_state = nullptr;
     void* cub_tmp = nullptr; size_t cub_bytes = 0;
     void* scan_tmp = nullptr; size_t scan_bytes = 0;
     int hb[6]; int h_init[6] = {0x7fffffff, 0x7fffffff, 0x7fffffff, (int)0x80000000, (int)0x80000000, (int)0x80000000};
@@ -519,20 +539,24 @@ cudaError_t build_scene(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns
                 RT_TRY(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, pflags, ppos, (int)n, stream));
                 RT_TRY(cudaMallocAsync(&scan_tmp, scan_bytes ? scan_bytes : 1, stream));
                 ploc_init<<<nb, T, 0, stream>>>((int)n, lmin, lmax, cidA, cloA, chiA);
-                int m = (int)n, node_base = 0, force = 0;
-                while (m > 1) {
-                    const int mb = (m + PLOC_THREADS - 1) / PLOC_THREADS;
-                    ploc_nn<<<mb, PLOC_THREADS, 0, stream>>>(m, ploc_radius, force, cloA, chiA, nn);
-                    ploc_flags<<<mb, PLOC_THREADS, 0, stream>>>(m, nn, pflags);
-                    RT_TRY(cub::DeviceScan::ExclusiveSum(scan_tmp, scan_bytes, pflags, ppos, m, stream));
-                    ploc_scatter<<<mb, PLOC_THREADS, 0, stream>>>(m, node_base, nn, ppos, cidA, cloA, chiA, cidB, cloB, chiB,
-                                                                  children, imin, imax, pin, plf, d_tot);
-                    unsigned int tot[2];
-                    RT_TRY(cudaMemcpyAsync(tot, d_tot, sizeof tot, cudaMemcpyDeviceToHost, stream));
+                RT_TRY(dalloc(&d_state, 4));
+                int h_state[4] = {(int)n, 0, 0, 0};              // clusters left, nodes created, force flag, rounds done
+                RT_TRY(cudaMemcpyAsync(d_state, h_state, sizeof h_state, cudaMemcpyHostToDevice, stream));
+                for (int checks = 0; h_state[0] > 1; checks++) {
+                    if (checks > 4096) { RT_TRY(cudaErrorUnknown); }   // cannot happen: every round merges at least one pair
+                    const int m_ub = h_state[0];                 // the cluster count only shrinks: grids and the scan are sized for the last known one
+                    const int mb = (m_ub + PLOC_THREADS - 1) / PLOC_THREADS;
+                    for (int r = 0; r < PLOC_ROUNDS_PER_CHECK; r++) {
+                        ploc_nn<<<mb, PLOC_THREADS, 0, stream>>>(d_state, ploc_radius, cloA, chiA, nn);
+                        ploc_flags<<<mb, PLOC_THREADS, 0, stream>>>(d_state, nn, pflags);
+                        RT_TRY(cub::DeviceScan::ExclusiveSum(scan_tmp, scan_bytes, pflags, ppos, m_ub, stream));
+                        ploc_scatter<<<mb, PLOC_THREADS, 0, stream>>>(d_state, nn, ppos, cidA, cloA, chiA, cidB, cloB, chiB,
+                                                                      children, imin, imax, pin, plf, d_tot);
+                        ploc_advance<<<1, 1, 0, stream>>>(d_state, d_tot);
+                        std::swap(cidA, cidB); std::swap(cloA, cloB); std::swap(chiA, chiB);
+                    }
+                    RT_TRY(cudaMemcpyAsync(h_state, d_state, sizeof h_state, cudaMemcpyDeviceToHost, stream));
                     RT_TRY(cudaStreamSynchronize(stream));
-                    force = (tot[1] == 0);                       // no mutual pair (only possible with tied areas): pair up neighbours next round
-                    node_base += (int)tot[1]; m = (int)tot[0];
-                    std::swap(cidA, cidB); std::swap(cloA, cloB); std::swap(chiA, chiB);
                 }
                 root = (int)n - 2;                               // the last node created
                 RT_TRY(cudaMemsetAsync(d_depth, 0, sizeof(int), stream));
@@ -577,7 +601,7 @@ done:
     {
         void* tmp[] = {d_sph, d_vtx, d_idx, d_mesh, d_tstart, hot, bmin, bmax, lmin, lmax, imin, imax, d_bounds,
                        keys, keys2, ids, ids2, children, ranges, pin, plf, flags, d_depth, cub_tmp, new_slot,
-                       cidA, cidB, nn, cloA, chiA, cloB, chiB, pflags, ppos, d_tot, scan_tmp};
+                       cidA, cidB, nn, cloA, chiA, cloB, chiB, pflags, ppos, d_tot, d_state, scan_tmp};
         for (void* p : tmp) if (p) cudaFreeAsync(p, stream);
     }
     if (err != cudaSuccess) out.release();
