@@ -193,3 +193,38 @@ def test_teapot_vs_oracle_at_eighth_resolution(rtlib, oracle):
     ci, cid, cc = _cpu(oracle, scene, 240, 136, 1, p["number_of_bounces"], p["skybox"])
     assert np.array_equal(gid, cid) and gc["rays"] == int(cc[0])
     assert_bits_equal(gi, ci, "c3_teapot 240x136")
+
+
+@pytest.mark.parametrize("name,frames", [("c3_teapot", 8), ("c4_tree", 4), ("c5_stress", 2)])
+def test_full_size_launch_structure_is_result_invisible(rtlib, name, frames):
+    """BASELINE.json's full sizes, properties that need no reference image: all dispatches fused in one launch ==
+    one launch per dispatch == two resumed halves == the wavefront kernels == the union of three tile shards."""
+    from ray_tracer_b200 import configs
+    L = rtlib._lib
+    scene, meta = configs.build(name)
+    p = meta["params"]
+    tr = rtlib.RayTracer(0, p["width"], p["height"])
+    tr.upload_scene(*scene.arrays()); tr.upload_textures(scene.textures); tr.set_camera(scene.camera_uniform()); tr.set_params(**p)
+
+    def render(first_then=None, per_launch=None, kernel=0, shard=None):
+        tr.set_option(L.RT_OPT_FRAMES_PER_LAUNCH, per_launch or 64); tr.set_option(L.RT_OPT_KERNEL, kernel)
+        tr.set_shard(*(shard or (0, 1, 0, 1)))
+        tr.clear(); tr.reset_counters()
+        for first, n in (first_then or [(0, frames)]):
+            tr.render_frames(first, n)
+        tr.sync()
+        return tr.read_accum(), tr.counters()["rays"]
+
+    ref, rays = render()
+    for what, (img, r) in (("one launch per dispatch", render(per_launch=1)),
+                           ("two resumed halves", render(first_then=[(0, frames // 2), (frames // 2, frames - frames // 2)])),
+                           ("wavefront kernels", render(kernel=1))):
+        assert r == rays, what
+        assert_bits_equal(img, ref, "%s: %s" % (name, what))
+    union, total = np.zeros_like(ref), 0
+    for rank in range(3):
+        img, r = render(shard=(rank, 3, 0, 1))
+        union += img; total += r                      # shards are disjoint and the rest of each image is zero
+    assert total == rays
+    assert_bits_equal(union, ref, "%s: union of three tile shards" % name)
+    tr.close()
