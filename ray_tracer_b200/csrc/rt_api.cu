@@ -35,7 +35,7 @@ struct rt_ctx {
     float4* staging = nullptr;                    // per-dispatch frag planes awaiting the blend
     uint32_t staging_frames = 0;
     int n_sms = 148;
-    int64_t opt_staging_bytes = 2ll << 30;
+    int64_t opt_staging_bytes = 8ll << 30;        // staging planes: 128 dispatches at 1080p, 61 at 4K (RT_OPT_STAGING_MIB)
     int64_t opt_sched = 8 | (1 << 8) | (22 << 16);     // node loop runs while >= 8 lanes can step; shade once >= 22 lanes wait (swept on C3/C5)
     rt::SceneBuffers scene;
     std::vector<rt_mesh> mesh_ranges;             // the uploaded Mesh records (rt_update_records checks the index ranges against them)
@@ -46,7 +46,7 @@ struct rt_ctx {
     rt_params params{};
     rt_camera_uniform camera{};
     uint32_t tile_rank = 0, tile_world = 1, frame_rank = 0, frame_world = 1;
-    int64_t opt_traversal = 0, opt_seed_mode = 0, opt_primary_ids = 0, opt_detail = 0, opt_frames_per_launch = 64, opt_leaf_size = 2, opt_builder = 0, opt_ploc_radius = 3, opt_kernel = 0, opt_wave_slots = 1 << 21;
+    int64_t opt_traversal = 0, opt_seed_mode = 0, opt_primary_ids = 0, opt_detail = 0, opt_frames_per_launch = 128, opt_leaf_size = 2, opt_builder = 0, opt_ploc_radius = 3, opt_kernel = 0, opt_wave_slots = 1 << 21;
     rt::WavePool wave;                            // path-slot pool of the wavefront kernels (RT_OPT_KERNEL = 1)
     uint64_t dispatches = 0, launches = 0;
     double kernel_ms = 0.0;
@@ -463,6 +463,7 @@ int rt_set_option(rt_ctx* c, int option, int64_t value)
     case RT_OPT_PLOC_RADIUS: if (value < 1 || value > 16) break; c->opt_ploc_radius = value; return RT_OK;
     case RT_OPT_KERNEL: if (value != 0 && value != 1) break; c->opt_kernel = value; return RT_OK;
     case RT_OPT_WAVE_SLOTS: if (value < 1024 || value > (1 << 26)) break; c->opt_wave_slots = value; return RT_OK;
+    case RT_OPT_STAGING_MIB: if (value < 16 || value > (1 << 17)) break; c->opt_staging_bytes = value << 20; return RT_OK;
     default: return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_set_option: unknown option");
     }
     return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_set_option: value out of range");
@@ -483,6 +484,7 @@ int rt_get_option(const rt_ctx* c, int option, int64_t* value)
     case RT_OPT_PLOC_RADIUS: *value = c->opt_ploc_radius; return RT_OK;
     case RT_OPT_KERNEL: *value = c->opt_kernel; return RT_OK;
     case RT_OPT_WAVE_SLOTS: *value = c->opt_wave_slots; return RT_OK;
+    case RT_OPT_STAGING_MIB: *value = c->opt_staging_bytes >> 20; return RT_OK;
     default: return RT_ERR_INVALID_ARGUMENT;
     }
 }

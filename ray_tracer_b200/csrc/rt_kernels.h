@@ -28,7 +28,12 @@
 
 namespace rt {
 
-#define RT_QUEUE_CHUNK 128ull     // work items a warp takes from the global queue per atomic
+#ifndef RT_QUEUE_CHUNK
+#define RT_QUEUE_CHUNK 128ull     // work items a warp takes from the global queue per atomic (while plenty remain)
+#endif
+#ifndef RT_QUEUE_GUIDE
+#define RT_QUEUE_GUIDE 20ull      // grab size = remaining items / (warps x this), clamped to [32, RT_QUEUE_CHUNK]
+#endif
 
 // trace (persistent warps over the (pixel, dispatch) item queue) + blend (running mean of the
 // staged dispatches into `accum`). `staging` holds lp.n_frames planes of W*H float4.

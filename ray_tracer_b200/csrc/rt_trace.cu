@@ -66,6 +66,7 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
     stack[0] = RT_EMPTY;                           // sentinel under every traversal (sp starts at 1): a pop needs no emptiness test
 
     const uint64_t n_items = (uint64_t)lp.n_warp_tiles * lp.n_frames * 32ull;
+    const unsigned long long guide = (unsigned long long)gridDim.x * (RT_BLOCK_THREADS / 32) * RT_QUEUE_GUIDE;   // warps x K
     const size_t plane = (size_t)lp.width * lp.height;
     const float sw = (float)lp.width, sh = (float)lp.height, rppf = (float)lp.rpp;
     uint32_t n_rays = 0, n_samples = 0, n_nodes = 0, n_tri = 0, n_sph = 0, n_hits = 0;
@@ -126,11 +127,21 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
             unsigned want = __ballot_sync(0xffffffffu, shading && !idle && !has_item && !exhausted);
             while (want) {
                 if (pool_next == pool_end) {
-                    unsigned long long g = 0;
-                    if (lane == 0) g = atomicAdd(queue, (unsigned long long)RT_QUEUE_CHUNK);
-                    g = __shfl_sync(0xffffffffu, g, 0);
+                    // guided self-scheduling: RT_QUEUE_CHUNK items per grab while plenty remain, down to one
+                    // 8x4 tile of one dispatch (32 items) near the end, so that no warp is left holding a
+                    // large pool of heavy pixels when the queue runs dry (a heavy 128-item pool takes one
+                    // warp milliseconds: the launch's fixed cost went from 3.3 ms to under 1 ms on C3)
+                    unsigned long long g = 0, chunk = 0;
+                    if (lane == 0) {
+                        const unsigned long long cur = *(volatile unsigned long long*)queue;
+                        const unsigned long long rem = cur < n_items ? n_items - cur : 0ull;
+                        chunk = (rem / guide) & ~31ull;
+                        chunk = chunk < 32ull ? 32ull : (chunk > RT_QUEUE_CHUNK ? RT_QUEUE_CHUNK : chunk);
+                        g = atomicAdd(queue, chunk);
+                    }
+                    g = __shfl_sync(0xffffffffu, g, 0); chunk = __shfl_sync(0xffffffffu, chunk, 0);
                     if (g >= n_items) { exhausted = true; break; }
-                    pool_next = g; pool_end = (g + RT_QUEUE_CHUNK < n_items) ? g + RT_QUEUE_CHUNK : n_items;
+                    pool_next = g; pool_end = (g + chunk < n_items) ? g + chunk : n_items;
                 }
                 const bool mine = (want >> lane) & 1u;
                 const uint32_t rank = __popc(want & ((1u << lane) - 1u));
