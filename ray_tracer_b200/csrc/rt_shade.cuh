@@ -82,12 +82,23 @@ __device__ __forceinline__ float rand_normal_dist(uint32_t& rng)
     float rho = sqrtf(-2.0f * spec_logf(rand01(rng)));
     return rho * spec_cosf(theta);
 }
-// wgsl:297-304
+// wgsl:297-304.  The two pow() calls are the most expensive part of a sky miss; most rays need at most
+// one of them: pow(t, 0.35) is t itself for t = 0 and t = 1 (below the horizon / above d.y = 0.4), and
+// pow(x, 500) is +0 for every x <= 0.8 (away from the sun) -- identities of the contract's pow checked
+// exhaustively by tests/native/sky_shortcuts_check.cpp.  Lanes that need exactly one share a single
+// evaluation with their own arguments; a second one runs only where a lane needs both.
 __device__ __forceinline__ float4 environment_light(float3 d)
 {
-    float sky_t = spec_powf(smoothstep1(0.0f, 0.4f, d.y), 0.35f);
-    float g2s = smoothstep1(-0.01f, 0.0f, d.y);
-    float sun = spec_powf(fmaxf(0.0f, dot3(d, f3(0.1f, 1.0f, 0.1f))), 500.0f) * 0.1f;
+    const float t = smoothstep1(0.0f, 0.4f, d.y);
+    const float g2s = smoothstep1(-0.01f, 0.0f, d.y);
+    const float x = fmaxf(0.0f, dot3(d, f3(0.1f, 1.0f, 0.1f)));
+    const bool need1 = !(t == 0.0f || t == 1.0f), need2 = !(x <= 0.8f);
+    float p = 0.0f;
+    if (need1 || need2) p = spec_powf(need1 ? t : x, need1 ? 0.35f : 500.0f);
+    const float sky_t = need1 ? p : t;
+    float sun_p = need2 ? p : 0.0f;
+    if (need1 && need2) sun_p = spec_powf(x, 500.0f);
+    const float sun = sun_p * 0.1f;
     float s = sun * ((g2s >= 1.0f) ? 1.0f : 0.0f);
     float4 sky = make_float4(mix1(1.0f, 0.0788092f, sky_t), mix1(1.0f, 0.36480793f, sky_t), mix1(1.0f, 0.7264151f, sky_t), mix1(0.0f, 0.0f, sky_t));
     return make_float4(mix1(0.35f, sky.x, g2s) + s, mix1(0.3f, sky.y, g2s) + s, mix1(0.35f, sky.z, g2s) + s, mix1(0.0f, sky.w, g2s) + s);

@@ -85,3 +85,14 @@ def test_fastdiv_is_exact(tmp_path):
                     "-o", exe, os.path.join(ROOT, "tests", "native", "fastdiv_check.cu")], check=True, capture_output=True)
     out = subprocess.run([exe], check=True, capture_output=True, text=True).stdout
     assert out.startswith("OK"), out
+
+
+def test_sky_pow_shortcuts_hold(tmp_path):
+    """environment_light (rt_shade.cuh) skips pow(t, 0.35) for t in {0, 1} and pow(x, 500) for x <= 0.8: the
+    identities behind that, against the oracle's pow (every 97th float of [0, 0.8]; `full` walks them all)."""
+    import subprocess
+    exe = str(tmp_path / "sky_shortcuts_check")
+    subprocess.run(["g++", "-O2", "-fopenmp", "-ffp-contract=off", "-o", exe, os.path.join(ROOT, "tests", "native", "sky_shortcuts_check.cpp")],
+                   check=True, capture_output=True)
+    out = subprocess.run([exe], check=True, capture_output=True, text=True).stdout
+    assert out.startswith("OK"), out
