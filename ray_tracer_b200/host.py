@@ -74,6 +74,8 @@ def hostlib():
         # texture-extension loaders and PNG i/o
         L.rth_scene_from_model_uv.argtypes = [C.c_char_p]
         L.rth_scene_from_model_uv.restype = vp
+        L.rth_scene_from_glb_graph.argtypes = [C.c_char_p]
+        L.rth_scene_from_glb_graph.restype = vp
         L.rth_png_load.argtypes = [C.c_char_p, C.POINTER(u32), C.POINTER(u32)]
         L.rth_png_load.restype = vp
         L.rth_image_copy.argtypes = [vp, vp]
@@ -189,6 +191,13 @@ def load_model(path):
 def load_model_uv(path):
     """Texture extension: load_model that keeps `vt` / TEXCOORD_0 in the Vertex padding words."""
     s = Scene._from_handle(hostlib().rth_scene_from_model_uv(os.fsencode(path)))
+    return s.vertices, s.indices, s.meshes
+
+
+def load_scene_glb(path):
+    """Scene-graph import of a .glb (extension, upstream ignores node transforms and materials): vertices in world
+    space, one Mesh per primitive instance at pos 0 with the material's colour / smoothness / emission / texture handles."""
+    s = Scene._from_handle(hostlib().rth_scene_from_glb_graph(os.fsencode(path)))
     return s.vertices, s.indices, s.meshes
 
 

@@ -167,6 +167,14 @@ void* rth_scene_from_model_uv(const char* path)               // texture extensi
         return s;
     } catch (const std::exception& e) { g_err = e.what(); return nullptr; }
 }
+void* rth_scene_from_glb_graph(const char* path)             // scene-graph import: node transforms + materials (extension)
+{
+    try {
+        rtb::Scene* s = new rtb::Scene();
+        try { rtb::load_scene_glb(path, s->vertices, s->indices, s->meshes); } catch (...) { delete s; throw; }
+        return s;
+    } catch (const std::exception& e) { g_err = e.what(); return nullptr; }
+}
 // PNG in / out. rth_png_load returns a handle (NULL on error); *w, *h receive the size.
 void* rth_png_load(const char* path, uint32_t* w, uint32_t* h)
 {

@@ -7,6 +7,7 @@
 // pos = (mesh_count*3, 0, 0), colour (0.2,0.2,1,1), specular 0.5, triangulated and
 // single-indexed OBJ (resource.rs:57-63), node transforms ignored for .glb (:228-276),
 // positions scaled by the running mesh count for .gltf (:180), normals required.
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -263,7 +264,9 @@ void load_model_obj(const std::string& path, std::vector<rt_vertex>& vertices, s
     }
 }
 
-void load_model_glb(const std::string& path, std::vector<rt_vertex>& vertices, std::vector<uint32_t>& indices, std::vector<rt_mesh>& meshes)
+namespace {
+// GLB container: JSON chunk + first BIN chunk; buffers[] resolved like resource.rs:203-216
+void read_glb(const std::string& path, Json& g, std::vector<std::string>& buffers)
 {
     std::string data = read_file(path, true);
     if (data.size() < 20 || memcmp(data.data(), "glTF", 4) != 0) throw std::runtime_error("GLB: bad magic");
@@ -276,16 +279,142 @@ void load_model_glb(const std::string& path, std::vector<rt_vertex>& vertices, s
         else if (ctype == 0x004E4942u && !have_blob) { blob.assign(data, off + 8, clen); have_blob = true; }
         off += 8 + (size_t)clen;
     }
-    Json g = parse_json(json);
-    std::vector<std::string> buffers;
+    g = parse_json(json);
     if (const Json* jb = g.get("buffers"))
         for (const Json& b : jb->arr) {
             if (const Json* uri = b.get("uri")) buffers.push_back(read_file(sibling(path, uri->str), true));
             else { if (!have_blob) throw std::runtime_error("Missing blob"); buffers.push_back(blob); }   // resource.rs:211-216
         }
+}
+} // namespace
+
+void load_model_glb(const std::string& path, std::vector<rt_vertex>& vertices, std::vector<uint32_t>& indices, std::vector<rt_mesh>& meshes)
+{
+    Json g; std::vector<std::string> buffers;
+    read_glb(path, g, buffers);
     if (const Json* jm = g.get("meshes"))
         for (const Json& mesh : jm->arr)
             for (const Json& prim : mesh.at("primitives").arr) append_primitive(g, buffers, prim, false, vertices, indices, meshes);
+}
+
+// ---- scene-graph import (extension; upstream ignores node transforms and materials, resource.rs:228-276) ----
+namespace {
+struct Mat4 { float m[16]; };                                     // column-major, as glTF stores matrices
+Mat4 mat_identity() { Mat4 r{}; r.m[0] = r.m[5] = r.m[10] = r.m[15] = 1.0f; return r; }
+Mat4 mat_mul(const Mat4& a, const Mat4& b)
+{
+    Mat4 r{};
+    for (int c = 0; c < 4; c++)
+        for (int rw = 0; rw < 4; rw++) {
+            float acc = 0.0f;
+            for (int k = 0; k < 4; k++) acc += a.m[k * 4 + rw] * b.m[c * 4 + k];
+            r.m[c * 4 + rw] = acc;
+        }
+    return r;
+}
+float num_or(const Json* j, size_t k, float d) { return (j && k < j->arr.size()) ? (float)j->arr[k].num : d; }
+Mat4 node_local(const Json& node)
+{
+    if (const Json* jm = node.get("matrix")) {
+        Mat4 r{};
+        for (size_t k = 0; k < 16; k++) r.m[k] = num_or(jm, k, (k % 5 == 0) ? 1.0f : 0.0f);
+        return r;
+    }
+    const Json *jt = node.get("translation"), *jr = node.get("rotation"), *js = node.get("scale");
+    const float tx = num_or(jt, 0, 0.f), ty = num_or(jt, 1, 0.f), tz = num_or(jt, 2, 0.f);
+    const float x = num_or(jr, 0, 0.f), y = num_or(jr, 1, 0.f), z = num_or(jr, 2, 0.f), w = num_or(jr, 3, 1.f);
+    const float sx = num_or(js, 0, 1.f), sy = num_or(js, 1, 1.f), sz = num_or(js, 2, 1.f);
+    Mat4 r{};                                                      // T * R * S
+    r.m[0] = (1.f - 2.f * (y * y + z * z)) * sx; r.m[1] = (2.f * (x * y + z * w)) * sx;       r.m[2] = (2.f * (x * z - y * w)) * sx;
+    r.m[4] = (2.f * (x * y - z * w)) * sy;       r.m[5] = (1.f - 2.f * (x * x + z * z)) * sy; r.m[6] = (2.f * (y * z + x * w)) * sy;
+    r.m[8] = (2.f * (x * z + y * w)) * sz;       r.m[9] = (2.f * (y * z - x * w)) * sz;       r.m[10] = (1.f - 2.f * (x * x + y * y)) * sz;
+    r.m[12] = tx; r.m[13] = ty; r.m[14] = tz; r.m[15] = 1.f;
+    return r;
+}
+// material -> Mesh record: base colour factor, smoothness = 1 - roughness, emissive factor, texture handles
+// (handle = image index + 1, the order load_glb_images returns them in)
+void apply_material(const Json& g, const Json& prim, rt_mesh& m)
+{
+    const Json* jmi = prim.get("material");
+    const Json* mats = g.get("materials");
+    if (!jmi || !mats || (size_t)jmi->num >= mats->arr.size()) return;
+    const Json& mat = mats->arr[(size_t)jmi->num];
+    auto image_handle = [&](const Json* texref) -> uint32_t {
+        if (!texref) return 0u;
+        const Json* ji = texref->get("index"); const Json* texs = g.get("textures");
+        if (!ji || !texs || (size_t)ji->num >= texs->arr.size()) return 0u;
+        const Json* src = texs->arr[(size_t)ji->num].get("source");
+        return src ? (uint32_t)src->num + 1u : 0u;
+    };
+    if (const Json* pbr = mat.get("pbrMetallicRoughness")) {
+        if (const Json* bc = pbr->get("baseColorFactor")) for (size_t k = 0; k < 4; k++) m.color[k] = num_or(bc, k, 1.0f);
+        else { m.color[0] = m.color[1] = m.color[2] = m.color[3] = 1.0f; }
+        const Json* jr = pbr->get("roughnessFactor");
+        float smooth = 1.0f - (jr ? (float)jr->num : 1.0f);
+        m.specular = smooth < 0.0f ? 0.0f : (smooth > 1.0f ? 1.0f : smooth);
+        m.diffuse_tex = image_handle(pbr->get("baseColorTexture"));
+    }
+    m.normal_tex = image_handle(mat.get("normalTexture"));
+    if (const Json* je = mat.get("emissiveFactor")) {
+        const float e0 = num_or(je, 0, 0.f), e1 = num_or(je, 1, 0.f), e2 = num_or(je, 2, 0.f);
+        if (e0 != 0.f || e1 != 0.f || e2 != 0.f) { m.emission_color[0] = e0; m.emission_color[1] = e1; m.emission_color[2] = e2; m.emission_color[3] = 1.0f; m.emission_strength = 1.0f; }
+    }
+}
+void visit_node(const Json& g, const std::vector<std::string>& buffers, size_t ni, const Mat4& parent, int depth,
+                std::vector<rt_vertex>& vertices, std::vector<uint32_t>& indices, std::vector<rt_mesh>& meshes)
+{
+    const Json& nodes = g.at("nodes");
+    if (ni >= nodes.arr.size() || depth > 256) throw std::runtime_error("GLB: bad node reference");
+    const Json& node = nodes.arr[ni];
+    const Mat4 world = mat_mul(parent, node_local(node));
+    if (const Json* jm = node.get("mesh")) {
+        // inverse transpose of the upper 3x3 for normals = cofactor matrix / det; the normalisation removes the scale
+        const float* a = world.m;
+        const float c00 = a[5] * a[10] - a[6] * a[9], c01 = a[6] * a[8] - a[4] * a[10], c02 = a[4] * a[9] - a[5] * a[8];
+        const float c10 = a[2] * a[9] - a[1] * a[10], c11 = a[0] * a[10] - a[2] * a[8], c12 = a[1] * a[8] - a[0] * a[9];
+        const float c20 = a[1] * a[6] - a[2] * a[5], c21 = a[2] * a[4] - a[0] * a[6], c22 = a[0] * a[5] - a[1] * a[4];
+        const float det = a[0] * c00 + a[1] * c01 + a[2] * c02;
+        for (const Json& prim : g.at("meshes").arr.at((size_t)jm->num).at("primitives").arr) {
+            const size_t v0 = vertices.size();
+            append_primitive(g, buffers, prim, false, vertices, indices, meshes);
+            rt_mesh& m = meshes.back();
+            m.pos[0] = m.pos[1] = m.pos[2] = 0.0f;                 // the node transform places the mesh, not resource.rs:75's (3k, 0, 0)
+            apply_material(g, prim, m);
+            for (size_t k = v0; k < vertices.size(); k++) {
+                rt_vertex& v = vertices[k];
+                const float px = v.pos[0], py = v.pos[1], pz = v.pos[2];
+                v.pos[0] = a[0] * px + a[4] * py + a[8] * pz + a[12];
+                v.pos[1] = a[1] * px + a[5] * py + a[9] * pz + a[13];
+                v.pos[2] = a[2] * px + a[6] * py + a[10] * pz + a[14];
+                if (det != 0.0f) {
+                    const float nx = v.normal[0], ny = v.normal[1], nz = v.normal[2];
+                    float qx = c00 * nx + c10 * ny + c20 * nz, qy = c01 * nx + c11 * ny + c21 * nz, qz = c02 * nx + c12 * ny + c22 * nz;
+                    if (det < 0.0f) { qx = -qx; qy = -qy; qz = -qz; }
+                    const float len = sqrtf(qx * qx + qy * qy + qz * qz);
+                    if (len > 0.0f) { v.normal[0] = qx / len; v.normal[1] = qy / len; v.normal[2] = qz / len; }
+                }
+            }
+            if (det < 0.0f)                                        // a mirroring transform flips the winding the one-sided test relies on
+                for (size_t t = m.first; t + 2 < m.first + 3 * (size_t)m.triangles; t += 3) std::swap(indices[t + 1], indices[t + 2]);
+        }
+    }
+    if (const Json* jc = node.get("children"))
+        for (const Json& c : jc->arr) visit_node(g, buffers, (size_t)c.num, world, depth + 1, vertices, indices, meshes);
+}
+} // namespace
+
+void load_scene_glb(const std::string& path, std::vector<rt_vertex>& vertices, std::vector<uint32_t>& indices, std::vector<rt_mesh>& meshes)
+{
+    struct Guard { Guard() { g_keep_uv = true; } ~Guard() { g_keep_uv = false; } } guard;
+    Json g; std::vector<std::string> buffers;
+    read_glb(path, g, buffers);
+    const Json* scenes = g.get("scenes");
+    if (!scenes || scenes->arr.empty()) { load_model_glb(path, vertices, indices, meshes); return; }   // no scene graph: every mesh once, untransformed
+    const Json* def = g.get("scene");
+    const size_t si = def ? (size_t)def->num : 0;
+    if (si >= scenes->arr.size()) throw std::runtime_error("GLB: bad default scene");
+    if (const Json* roots = scenes->arr[si].get("nodes"))
+        for (const Json& r : roots->arr) visit_node(g, buffers, (size_t)r.num, mat_identity(), 0, vertices, indices, meshes);
 }
 
 void load_model_gltf(const std::string& path, std::vector<rt_vertex>& vertices, std::vector<uint32_t>& indices, std::vector<rt_mesh>& meshes)

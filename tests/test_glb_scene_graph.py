@@ -1,0 +1,117 @@
+"""Scene-graph import of a .glb (host extension): node transforms (matrix and T*R*S, nested),
+materials and mirrored instances, against a numpy evaluation of the same file."""
+import json
+import struct
+
+import numpy as np
+import pytest
+
+
+def _write_glb(path, gltf, blob):
+    js = json.dumps(gltf).encode()
+    js += b" " * (-len(js) % 4)
+    blob += b"\0" * (-len(blob) % 4)
+    with open(path, "wb") as f:
+        f.write(b"glTF" + struct.pack("<II", 2, 12 + 8 + len(js) + 8 + len(blob)))
+        f.write(struct.pack("<I", len(js)) + b"JSON" + js)
+        f.write(struct.pack("<I", len(blob)) + b"BIN\0" + blob)
+
+
+def _quat(axis, deg):
+    a = np.asarray(axis, np.float64) / np.linalg.norm(axis)
+    h = np.radians(deg) / 2
+    return [*(a * np.sin(h)), np.cos(h)]
+
+
+def _trs(t, q, s):
+    x, y, z, w = q
+    r = np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w)],
+                  [2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w)],
+                  [2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)]])
+    m = np.eye(4)
+    m[:3, :3] = r @ np.diag(s)
+    m[:3, 3] = t
+    return m
+
+
+@pytest.fixture()
+def glb(tmp_path):
+    pos = np.array([[0, 0, 0], [1, 0, 0], [1, 1, 0], [0, 1, 0]], np.float32)
+    nrm = np.array([[0, 0, 1]] * 4, np.float32)
+    uv = np.array([[0, 0], [1, 0], [1, 1], [0, 1]], np.float32)
+    idx = np.array([0, 1, 2, 0, 2, 3], np.uint16)
+    blob = pos.tobytes() + nrm.tobytes() + uv.tobytes() + idx.tobytes()
+    q = _quat([0, 1, 0], 90)
+    parent = _trs([1, 2, 3], _quat([1, 0, 0], 30), [2, 2, 2])
+    mirror = np.diag([-1.0, 1.0, 1.0, 1.0])
+    mirror[:3, 3] = [5, 0, 0]
+    gltf = {
+        "asset": {"version": "2.0"}, "scene": 0, "scenes": [{"nodes": [0, 2]}],
+        "nodes": [
+            {"translation": [1, 2, 3], "rotation": _quat([1, 0, 0], 30), "scale": [2, 2, 2], "children": [1]},
+            {"mesh": 0, "translation": [0, 0, -1], "rotation": q},
+            {"mesh": 0, "matrix": [float(v) for v in mirror.T.reshape(-1)]},
+        ],
+        "meshes": [{"primitives": [{"attributes": {"POSITION": 0, "NORMAL": 1, "TEXCOORD_0": 2}, "indices": 3, "material": 0}]}],
+        "materials": [{"pbrMetallicRoughness": {"baseColorFactor": [0.8, 0.1, 0.2, 1.0], "roughnessFactor": 0.25,
+                                                "baseColorTexture": {"index": 0}},
+                       "normalTexture": {"index": 1}, "emissiveFactor": [0.0, 0.5, 0.0]}],
+        "textures": [{"source": 1}, {"source": 0}], "images": [{"uri": "a.png"}, {"uri": "b.png"}],
+        "buffers": [{"byteLength": len(blob)}],
+        "bufferViews": [{"buffer": 0, "byteOffset": 0, "byteLength": 48}, {"buffer": 0, "byteOffset": 48, "byteLength": 48},
+                        {"buffer": 0, "byteOffset": 96, "byteLength": 32}, {"buffer": 0, "byteOffset": 128, "byteLength": 12}],
+        "accessors": [{"bufferView": 0, "componentType": 5126, "count": 4, "type": "VEC3"},
+                      {"bufferView": 1, "componentType": 5126, "count": 4, "type": "VEC3"},
+                      {"bufferView": 2, "componentType": 5126, "count": 4, "type": "VEC2"},
+                      {"bufferView": 3, "componentType": 5123, "count": 6, "type": "SCALAR"}],
+    }
+    path = str(tmp_path / "graph.glb")
+    _write_glb(path, gltf, blob)
+    worlds = [parent @ _trs([0, 0, -1], q, [1, 1, 1]), mirror]
+    return path, pos, nrm, uv, idx, worlds
+
+
+def test_node_transforms_materials_and_mirrored_instances(glb):
+    from ray_tracer_b200 import host
+    path, pos, nrm, uv, idx, worlds = glb
+    vs, ix, ms = host.load_scene_glb(path)
+    assert len(ms) == 2 and len(vs) == 8 and len(ix) == 12
+    for k, world in enumerate(worlds):
+        m = ms[k]
+        assert m["triangles"] == 2 and m["first"] == 6 * k and m["offset"] == 4 * k
+        assert np.all(m["pos"][:3] == 0)
+        np.testing.assert_allclose(m["color"], [0.8, 0.1, 0.2, 1.0], rtol=1e-6)
+        assert m["specular"] == np.float32(0.75)
+        np.testing.assert_allclose(m["emission_color"][:3], [0.0, 0.5, 0.0]); assert m["emission_strength"] == 1.0
+        assert m["diffuse_tex"] == 2 and m["normal_tex"] == 1          # image index + 1
+        v = vs[4 * k: 4 * k + 4]
+        want = (world[:3, :3] @ pos.T.astype(np.float64)).T + world[:3, 3]
+        np.testing.assert_allclose(v["pos"][:, :3] if v["pos"].ndim == 2 else np.stack([v["pos"]]), want, rtol=1e-5, atol=1e-5)
+        n_want = np.linalg.inv(world[:3, :3]).T @ nrm[0].astype(np.float64)
+        n_want /= np.linalg.norm(n_want)
+        np.testing.assert_allclose(v["normal"][:, :3], np.tile(n_want, (4, 1)), rtol=1e-5, atol=1e-5)
+        np.testing.assert_array_equal(np.stack([v["tu"], v["tv"]], 1), uv)
+        tri = ix[6 * k: 6 * k + 6].reshape(2, 3)
+        if np.linalg.det(world[:3, :3]) < 0:                            # mirrored: winding flipped so the face normal still agrees
+            np.testing.assert_array_equal(tri, idx.reshape(2, 3)[:, [0, 2, 1]])
+        else:
+            np.testing.assert_array_equal(tri, idx.reshape(2, 3))
+        p = v["pos"][:, :3].astype(np.float64)
+        for t in tri:
+            face = np.cross(p[t[1]] - p[t[0]], p[t[2]] - p[t[0]])
+            assert np.dot(face, n_want) > 0                              # geometric and shading normal on the same side
+
+
+def test_glb_without_scene_graph_falls_back_to_plain_loader(tmp_path, glb):
+    from ray_tracer_b200 import host
+    path = glb[0]
+    import json as js
+    data = open(path, "rb").read()
+    jl = struct.unpack("<I", data[12:16])[0]
+    g = js.loads(data[20:20 + jl])
+    del g["scenes"], g["scene"]
+    p2 = str(tmp_path / "flat.glb")
+    _write_glb(p2, g, data[20 + jl + 8:])
+    vs, ix, ms = host.load_scene_glb(p2)
+    v0, i0, m0 = host.load_model_uv(p2)
+    assert np.array_equal(vs.view(np.uint8), v0.view(np.uint8)) and np.array_equal(ix, i0) and np.array_equal(ms.view(np.uint8), m0.view(np.uint8))
