@@ -178,7 +178,7 @@ void* rth_scene_from_glb_graph(const char* path)             // scene-graph impo
 // PNG in / out. rth_png_load returns a handle (NULL on error); *w, *h receive the size.
 void* rth_png_load(const char* path, uint32_t* w, uint32_t* h)
 {
-    try { rtb::Image* im = new rtb::Image(rtb::load_png(path)); *w = im->width; *h = im->height; return im; }
+    try { rtb::Image* im = new rtb::Image(rtb::load_image(path)); *w = im->width; *h = im->height; return im; }
     catch (const std::exception& e) { g_err = e.what(); return nullptr; }
 }
 void rth_image_copy(const void* im, uint8_t* rgba) { const rtb::Image* i = (const rtb::Image*)im; if (!i->rgba.empty()) memcpy(rgba, i->rgba.data(), i->rgba.size()); }

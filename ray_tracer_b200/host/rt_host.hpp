@@ -102,7 +102,9 @@ void load_scene_glb(const std::string& path, std::vector<rt_vertex>& vertices, s
 struct Image { uint32_t width = 0, height = 0; std::vector<uint8_t> rgba; };
 Image load_png(const std::string& path);                            // 8/16-bit grey, grey+alpha, RGB, RGBA, palette; no interlace
 Image decode_png(const uint8_t* data, size_t size);
-std::vector<Image> load_glb_images(const std::string& path);        // PNG images embedded in a .glb (JPEG entries come back empty)
+Image decode_jpeg(const uint8_t* data, size_t size);                // baseline sequential JPEG (8 bit, Huffman); progressive files throw
+Image load_image(const std::string& path);                          // PNG or JPEG by signature
+std::vector<Image> load_glb_images(const std::string& path);        // PNG / baseline-JPEG images embedded in a .glb (others come back empty)
 void write_png(const std::string& path, const uint8_t* rgba, uint32_t width, uint32_t height);
 // the hard-coded record each loaded primitive gets (resource.rs:73-85)
 rt_mesh loader_mesh(uint32_t mesh_count, uint32_t n_indices, uint32_t first, uint32_t offset);

@@ -499,6 +499,174 @@ Image decode_png(const uint8_t* d, size_t size)
     return img;
 }
 
+// ---- baseline JPEG (ITU T.81 sequential DCT, Huffman, 8 bit; grey or YCbCr, any sampling factors; restart
+// intervals).  Progressive / arithmetic / 12-bit files are refused.  Chroma is upsampled bilinearly (the
+// triangle filter libjpeg calls "fancy upsampling"), the inverse DCT is evaluated in float. --------------------
+namespace {
+struct JpegHuff { uint16_t code_first[17]; int val_first[17]; int count[17]; uint8_t vals[256]; bool set = false; };
+struct JpegBits {
+    const uint8_t* p; const uint8_t* e; uint32_t acc = 0; int n = 0;
+    int bit()
+    {
+        if (n == 0) {
+            uint8_t b = p < e ? *p++ : 0;
+            if (b == 0xFF) { uint8_t b2 = p < e ? *p : 0; if (b2 == 0) p++; else { p--; b = 0; } }   // stuffed zero, or a marker: feed zeros
+            acc = b; n = 8;
+        }
+        return (acc >> --n) & 1;
+    }
+    int bits(int k) { int v = 0; while (k--) v = (v << 1) | bit(); return v; }
+    void reset() { n = 0; }
+};
+int jpeg_decode(JpegBits& br, const JpegHuff& h)
+{
+    int code = 0;
+    for (int len = 1; len <= 16; len++) {
+        code = (code << 1) | br.bit();
+        if (h.count[len] && code >= h.code_first[len] && code < h.code_first[len] + h.count[len]) return h.vals[h.val_first[len] + code - h.code_first[len]];
+    }
+    throw std::runtime_error("JPEG: bad Huffman code");
+}
+int jpeg_extend(int v, int t) { return (t && v < (1 << (t - 1))) ? v - (1 << t) + 1 : v; }
+const uint8_t kZigzag[64] = {0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18, 11, 4, 5, 12, 19, 26, 33, 40, 48, 41, 34, 27, 20, 13, 6, 7, 14, 21, 28,
+                             35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23, 30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
+void jpeg_idct(const float* in, uint8_t* out, size_t stride)
+{
+    static float c[8][8]; static bool init = false;
+    if (!init) { for (int x = 0; x < 8; x++) for (int u = 0; u < 8; u++) c[x][u] = (u == 0 ? 0.35355339059327379f : 0.5f) * (float)cos((2 * x + 1) * u * 3.14159265358979323846 / 16.0); init = true; }
+    float tmp[64];
+    for (int v = 0; v < 8; v++) for (int x = 0; x < 8; x++) { float a = 0; for (int u = 0; u < 8; u++) a += c[x][u] * in[v * 8 + u]; tmp[v * 8 + x] = a; }
+    for (int x = 0; x < 8; x++) for (int y = 0; y < 8; y++) {
+        float a = 0; for (int v = 0; v < 8; v++) a += c[y][v] * tmp[v * 8 + x];
+        float r = floorf(a + 128.5f);
+        out[y * stride + x] = (uint8_t)(r < 0 ? 0 : (r > 255 ? 255 : r));
+    }
+}
+} // namespace
+
+Image decode_jpeg(const uint8_t* d, size_t size)
+{
+    if (size < 4 || d[0] != 0xFF || d[1] != 0xD8) throw std::runtime_error("JPEG: bad signature");
+    uint16_t qt[4][64] = {}; JpegHuff hdc[4], hac[4];
+    struct Comp { int id = 0, h = 1, v = 1, tq = 0, td = 0, ta = 0, pred = 0; size_t w = 0, hgt = 0; std::vector<uint8_t> px; } comp[3];
+    int ncomp = 0, W = 0, H = 0, hmax = 1, vmax = 1, restart = 0;
+    size_t i = 2;
+    for (;;) {
+        if (i + 4 > size || d[i] != 0xFF) throw std::runtime_error("JPEG: marker expected");
+        const int m = d[i + 1];
+        if (m == 0xFF) { i++; continue; }
+        const size_t len = ((size_t)d[i + 2] << 8) | d[i + 3];
+        if (len < 2 || i + 2 + len > size) throw std::runtime_error("JPEG: truncated segment");
+        const uint8_t* s = d + i + 4; const size_t n = len - 2;
+        if (m == 0xDB) {
+            for (size_t k = 0; k < n;) {
+                const int pq = s[k] >> 4, tq = s[k] & 15; k++;
+                if (tq > 3 || k + (pq ? 128u : 64u) > n) throw std::runtime_error("JPEG: bad DQT");
+                for (int z = 0; z < 64; z++) { qt[tq][z] = pq ? (uint16_t)((s[k] << 8) | s[k + 1]) : s[k]; k += pq ? 2 : 1; }
+            }
+        } else if (m == 0xC0 || m == 0xC1) {
+            if (n < 6 || s[0] != 8) throw std::runtime_error("JPEG: only 8-bit samples");
+            H = (s[1] << 8) | s[2]; W = (s[3] << 8) | s[4]; ncomp = s[5];
+            if ((ncomp != 1 && ncomp != 3) || n < 6 + 3 * (size_t)ncomp || W == 0 || H == 0) throw std::runtime_error("JPEG: unsupported frame");
+            for (int k = 0; k < ncomp; k++) {
+                comp[k].id = s[6 + 3 * k]; comp[k].h = s[7 + 3 * k] >> 4; comp[k].v = s[7 + 3 * k] & 15; comp[k].tq = s[8 + 3 * k] & 3;
+                if (comp[k].h < 1 || comp[k].h > 4 || comp[k].v < 1 || comp[k].v > 4) throw std::runtime_error("JPEG: bad sampling factor");
+                hmax = comp[k].h > hmax ? comp[k].h : hmax; vmax = comp[k].v > vmax ? comp[k].v : vmax;
+            }
+        } else if (m == 0xC2 || (m >= 0xC3 && m <= 0xCF && m != 0xC4 && m != 0xC8 && m != 0xCC)) {
+            throw std::runtime_error("JPEG: progressive / lossless / arithmetic coding is not supported");
+        } else if (m == 0xC4) {
+            for (size_t k = 0; k < n;) {
+                const int tc = s[k] >> 4, th = s[k] & 15; k++;
+                if (tc > 1 || th > 3 || k + 16 > n) throw std::runtime_error("JPEG: bad DHT");
+                JpegHuff& h = tc ? hac[th] : hdc[th];
+                int total = 0, code = 0;
+                for (int l = 1; l <= 16; l++) { h.count[l] = s[k + l - 1]; h.val_first[l] = total; h.code_first[l] = (uint16_t)code; total += h.count[l]; code = (code + h.count[l]) << 1; }
+                k += 16;
+                if (total > 256 || k + (size_t)total > n) throw std::runtime_error("JPEG: bad DHT");
+                memcpy(h.vals, s + k, (size_t)total); k += (size_t)total; h.set = true;
+            }
+        } else if (m == 0xDD) {
+            if (n < 2) throw std::runtime_error("JPEG: bad DRI");
+            restart = (s[0] << 8) | s[1];
+        } else if (m == 0xDA) {
+            if (!W || n < 1 || s[0] != ncomp || n < 1 + 2 * (size_t)ncomp) throw std::runtime_error("JPEG: unsupported scan");
+            for (int k = 0; k < ncomp; k++) {
+                int c = -1; for (int q = 0; q < ncomp; q++) if (comp[q].id == s[1 + 2 * k]) c = q;
+                if (c < 0) throw std::runtime_error("JPEG: scan component");
+                comp[c].td = s[2 + 2 * k] >> 4; comp[c].ta = s[2 + 2 * k] & 15;
+                if (comp[c].td > 3 || comp[c].ta > 3 || !hdc[comp[c].td].set || !hac[comp[c].ta].set) throw std::runtime_error("JPEG: missing Huffman table");
+            }
+            i += 2 + len;
+            break;
+        }
+        i += 2 + len;
+    }
+    const size_t mcux = ((size_t)W + 8 * hmax - 1) / (8 * hmax), mcuy = ((size_t)H + 8 * vmax - 1) / (8 * vmax);
+    for (int k = 0; k < ncomp; k++) { comp[k].w = mcux * 8 * comp[k].h; comp[k].hgt = mcuy * 8 * comp[k].v; comp[k].px.assign(comp[k].w * comp[k].hgt, 0); }
+    JpegBits br{d + i, d + size};
+    int until_restart = restart;
+    for (size_t my = 0; my < mcuy; my++)
+        for (size_t mx = 0; mx < mcux; mx++) {
+            if (restart && until_restart == 0) {
+                br.reset();
+                while (br.p + 1 < br.e && !(br.p[0] == 0xFF && br.p[1] >= 0xD0 && br.p[1] <= 0xD7)) br.p++;
+                if (br.p + 1 < br.e) br.p += 2;
+                for (int k = 0; k < ncomp; k++) comp[k].pred = 0;
+                until_restart = restart;
+            }
+            for (int k = 0; k < ncomp; k++)
+                for (int by = 0; by < comp[k].v; by++)
+                    for (int bx = 0; bx < comp[k].h; bx++) {
+                        float blk[64] = {};
+                        const int t = jpeg_decode(br, hdc[comp[k].td]);
+                        if (t > 11) throw std::runtime_error("JPEG: bad DC size");
+                        comp[k].pred += jpeg_extend(br.bits(t), t);
+                        blk[0] = (float)(comp[k].pred * (int)qt[comp[k].tq][0]);
+                        for (int z = 1; z < 64;) {
+                            const int rs = jpeg_decode(br, hac[comp[k].ta]), r = rs >> 4, sz = rs & 15;
+                            if (sz == 0) { if (r == 15) { z += 16; continue; } break; }
+                            z += r;
+                            if (z > 63) throw std::runtime_error("JPEG: bad AC run");
+                            blk[kZigzag[z]] = (float)(jpeg_extend(br.bits(sz), sz) * (int)qt[comp[k].tq][z]);
+                            z++;
+                        }
+                        jpeg_idct(blk, comp[k].px.data() + ((my * comp[k].v + by) * 8) * comp[k].w + (mx * comp[k].h + bx) * 8, comp[k].w);
+                    }
+            if (restart) until_restart--;
+        }
+    Image img; img.width = (uint32_t)W; img.height = (uint32_t)H; img.rgba.resize((size_t)W * H * 4);
+    auto sample = [&](const Comp& c, int x, int y) -> float {        // bilinear at the full-resolution pixel centre
+        if (c.h == hmax && c.v == vmax) return (float)c.px[(size_t)y * c.w + x];
+        const float fx = ((float)x + 0.5f) * (float)c.h / (float)hmax - 0.5f, fy = ((float)y + 0.5f) * (float)c.v / (float)vmax - 0.5f;
+        const size_t cw = ((size_t)W * c.h + hmax - 1) / hmax, ch = ((size_t)H * c.v + vmax - 1) / vmax;   // valid samples
+        int x0 = (int)floorf(fx), y0 = (int)floorf(fy); const float ax = fx - (float)x0, ay = fy - (float)y0;
+        auto at = [&](int xx, int yy) { xx = xx < 0 ? 0 : (xx >= (int)cw ? (int)cw - 1 : xx); yy = yy < 0 ? 0 : (yy >= (int)ch ? (int)ch - 1 : yy); return (float)c.px[(size_t)yy * c.w + xx]; };
+        return (at(x0, y0) * (1 - ax) + at(x0 + 1, y0) * ax) * (1 - ay) + (at(x0, y0 + 1) * (1 - ax) + at(x0 + 1, y0 + 1) * ax) * ay;
+    };
+    auto clamp8 = [](float v) { v = floorf(v + 0.5f); return (uint8_t)(v < 0 ? 0 : (v > 255 ? 255 : v)); };
+    for (int y = 0; y < H; y++)
+        for (int x = 0; x < W; x++) {
+            uint8_t* o = &img.rgba[((size_t)y * W + x) * 4];
+            const float Y = sample(comp[0], x, y);
+            if (ncomp == 1) { o[0] = o[1] = o[2] = clamp8(Y); }
+            else {
+                const float cb = sample(comp[1], x, y) - 128.0f, cr = sample(comp[2], x, y) - 128.0f;
+                o[0] = clamp8(Y + 1.402f * cr); o[1] = clamp8(Y - 0.344136f * cb - 0.714136f * cr); o[2] = clamp8(Y + 1.772f * cb);
+            }
+            o[3] = 255;
+        }
+    return img;
+}
+
+Image load_image(const std::string& path)
+{
+    std::string data = read_file(path, true);
+    const uint8_t* p = (const uint8_t*)data.data();
+    if (data.size() >= 2 && p[0] == 0xFF && p[1] == 0xD8) return decode_jpeg(p, data.size());
+    return decode_png(p, data.size());
+}
+
 Image load_png(const std::string& path)
 {
     std::string data = read_file(path, true);
@@ -546,11 +714,13 @@ std::vector<Image> load_glb_images(const std::string& path)
         for (const Json& im : ji->arr) {
             Image img;
             const Json* bv = im.get("bufferView"); const Json* mt = im.get("mimeType");
-            if (bv && mt && mt->str == "image/png") {
+            if (bv && mt && (mt->str == "image/png" || mt->str == "image/jpeg")) {
                 const Json& v = g.at("bufferViews").arr.at((size_t)bv->num);
                 size_t off = (size_t)v.integer("byteOffset", 0), len = (size_t)v.integer("byteLength", 0);
                 if (off + len > blob.size()) throw std::runtime_error("GLB: image outside the binary chunk");
-                img = decode_png((const uint8_t*)blob.data() + off, len);
+                const uint8_t* q = (const uint8_t*)blob.data() + off;
+                if (mt->str == "image/png") img = decode_png(q, len);
+                else { try { img = decode_jpeg(q, len); } catch (const std::exception&) { img = Image(); } }   // progressive JPEGs stay empty
             }
             out.push_back(std::move(img));
         }

@@ -134,3 +134,26 @@ def test_context_input_policy_and_png(tmp_path):
     ctx.save_png(p, mirror_x=True)
     assert np.array_equal(np.asarray(Image.open(p).convert("RGBA")), png[:, ::-1])
     ctx.close()
+
+
+@pytest.mark.parametrize("mode,subsampling,size", [("RGB", 2, (67, 45)), ("RGB", 0, (64, 48)), ("RGB", 1, (50, 33)), ("L", 0, (40, 24))])
+def test_baseline_jpeg_decoder_against_pil(tmp_path, mode, subsampling, size):
+    """host decode_jpeg (baseline Huffman, 4:2:0 / 4:2:2 / 4:4:4 / grey, sizes that are not MCU multiples) vs Pillow:
+    different IDCT and chroma filters may differ by a few levels, never more."""
+    PIL = pytest.importorskip("PIL.Image")
+    from ray_tracer_b200 import host
+    w, h = size
+    yy, xx = np.mgrid[0:h, 0:w].astype(np.float64)
+    rgb = np.stack([127 + 120 * np.sin(xx / 9.0), 127 + 120 * np.cos(yy / 7.0), 127 + 100 * np.sin((xx + yy) / 13.0)], -1)
+    img = PIL.fromarray(rgb.clip(0, 255).astype(np.uint8), "RGB").convert(mode)
+    path = str(tmp_path / "t.jpg")
+    kw = {} if mode == "L" else {"subsampling": subsampling}
+    img.save(path, quality=92, **kw)
+    got = host.load_png(path)                                        # load_image: PNG or JPEG by signature
+    want = np.asarray(PIL.open(path).convert("RGBA"))
+    assert got.shape == want.shape
+    d = np.abs(got.astype(int) - want.astype(int))
+    assert d.max() <= 6 and d.mean() < 0.6, (d.max(), d.mean())
+    img.save(path, quality=92, progressive=True, **kw)
+    with pytest.raises(host.HostError):
+        host.load_png(path)
