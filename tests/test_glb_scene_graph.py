@@ -115,3 +115,64 @@ def test_glb_without_scene_graph_falls_back_to_plain_loader(tmp_path, glb):
     vs, ix, ms = host.load_scene_glb(p2)
     v0, i0, m0 = host.load_model_uv(p2)
     assert np.array_equal(vs.view(np.uint8), v0.view(np.uint8)) and np.array_equal(ix, i0) and np.array_equal(ms.view(np.uint8), m0.view(np.uint8))
+
+
+@pytest.mark.gpu
+def test_glb_with_embedded_textures_renders_like_the_oracle(tmp_path, rtlib, oracle):
+    """The whole extension chain on the GPU: a .glb with nested transforms, a material and an embedded PNG + baseline
+    JPEG -> load_scene_glb + load_glb_images -> rt_upload_scene / rt_upload_textures -> image == oracle, bit for bit."""
+    PIL = pytest.importorskip("PIL.Image")
+    import io
+    from ray_tracer_b200 import host
+    rng = np.random.default_rng(5)
+    yy, xx = np.mgrid[0:32, 0:32]
+    diffuse = np.stack([128 + 100 * np.sin(xx / 3.0), 128 + 100 * np.cos(yy / 4.0), 200 + 0 * xx], -1).clip(0, 255).astype(np.uint8)
+    normal = np.stack([128 + 40 * np.sin(xx / 2.0), 128 + 40 * np.cos(yy / 2.5), 230 + 0 * xx], -1).clip(0, 255).astype(np.uint8)
+    b1, b2 = io.BytesIO(), io.BytesIO()
+    PIL.fromarray(diffuse, "RGB").save(b1, format="JPEG", quality=95)
+    PIL.fromarray(normal, "RGB").save(b2, format="PNG")
+    pos = np.array([[-1, -1, 0], [1, -1, 0], [1, 1, 0], [-1, 1, 0]], np.float32)
+    nrm = np.array([[0, 0, 1]] * 4, np.float32)
+    uv = np.array([[0, 0], [2, 0], [2, 2], [0, 2]], np.float32)
+    idx = np.array([0, 1, 2, 0, 2, 3], np.uint16)
+    parts = [pos.tobytes(), nrm.tobytes(), uv.tobytes(), idx.tobytes() + b"\0\0\0\0"[:(-idx.nbytes) % 4], b1.getvalue(), b2.getvalue()]
+    views, off = [], 0
+    for p in parts:
+        views.append({"buffer": 0, "byteOffset": off, "byteLength": len(p)})
+        off += len(p) + (-len(p)) % 4
+    blob = b"".join(p + b"\0" * ((-len(p)) % 4) for p in parts)
+    views[3]["byteLength"] = idx.nbytes
+    gltf = {
+        "asset": {"version": "2.0"}, "scene": 0, "scenes": [{"nodes": [0]}],
+        "nodes": [{"translation": [0, 0, -4], "rotation": _quat([0, 1, 0], 25), "children": [1]},
+                  {"mesh": 0, "scale": [1.5, 1.0, 1.0], "rotation": _quat([1, 0, 0], -20)}],
+        "meshes": [{"primitives": [{"attributes": {"POSITION": 0, "NORMAL": 1, "TEXCOORD_0": 2}, "indices": 3, "material": 0}]}],
+        "materials": [{"pbrMetallicRoughness": {"baseColorFactor": [1.0, 0.9, 0.8, 1.0], "roughnessFactor": 0.6, "baseColorTexture": {"index": 0}},
+                       "normalTexture": {"index": 1}}],
+        "textures": [{"source": 0}, {"source": 1}],
+        "images": [{"bufferView": 4, "mimeType": "image/jpeg"}, {"bufferView": 5, "mimeType": "image/png"}],
+        "buffers": [{"byteLength": len(blob)}], "bufferViews": views,
+        "accessors": [{"bufferView": 0, "componentType": 5126, "count": 4, "type": "VEC3"}, {"bufferView": 1, "componentType": 5126, "count": 4, "type": "VEC3"},
+                      {"bufferView": 2, "componentType": 5126, "count": 4, "type": "VEC2"}, {"bufferView": 3, "componentType": 5123, "count": 6, "type": "SCALAR"}],
+    }
+    path = str(tmp_path / "textured.glb")
+    _write_glb(path, gltf, blob)
+    vs, ix, ms = host.load_scene_glb(path)
+    textures = host.load_glb_images(path)
+    assert [t.shape for t in textures] == [(32, 32, 4), (32, 32, 4)] and ms["diffuse_tex"][0] == 1 and ms["normal_tex"][0] == 2
+    assert np.array_equal(textures[1][..., :3], normal)                      # PNG is lossless
+    w, h = 96, 64
+    base = host.Scene.balls(np.float32(w) / np.float32(h))                    # camera + the light sphere of the built-in scene
+    cam, sp = base.camera_uniform(), base.spheres
+    tr = rtlib.RayTracer(0, w, h)
+    tr.upload_scene(sp, vs, ix, ms); tr.upload_textures(textures); tr.set_camera(cam)
+    tr.set_params(number_of_bounces=4, rays_per_pixel=1, skybox=1, frames=0)
+    tr.set_option(rtlib._lib.RT_OPT_PRIMARY_IDS, 1)
+    tr.render_frames(0, 2)
+    img, ids = tr.read_accum(), tr.read_primary_ids()
+    tr.close()
+    assert (ids >= len(sp)).sum() > 100, "the camera does not see the quad"
+    sc = (cam.view(oracle.CAMERA_DT), sp.view(oracle.SPHERE_DT), vs.view(oracle.VERTEX_DT), ix, ms.view(oracle.MESH_DT))
+    ref = oracle.render(sc, w, h, 2, 4, 1, 1, 0, textures=textures)
+    from util import assert_bits_equal
+    assert_bits_equal(img, ref, "glb scene graph with embedded textures")
