@@ -93,7 +93,7 @@ void load_model_glb(const std::string& path, std::vector<rt_vertex>& v, std::vec
 // that image row 0 is the top row).
 void load_model_uv(const std::string& path, std::vector<rt_vertex>& vertices, std::vector<uint32_t>& indices,
                    std::vector<rt_mesh>& meshes);
-// Scene-graph import of a .glb (extension): walks the default scene, applies every node's transform
+// Scene-graph import of a .glb or .gltf (extension): walks the default scene, applies every node's transform
 // (matrix or T*R*S, parents first) to positions and normals, one Mesh record per primitive INSTANCE at
 // pos = 0, colour / smoothness / emission from the material (baseColorFactor, 1 - roughnessFactor,
 // emissiveFactor), texture handles = image index + 1 (the order of load_glb_images), UVs kept.

@@ -407,9 +407,18 @@ void load_scene_glb(const std::string& path, std::vector<rt_vertex>& vertices, s
 {
     struct Guard { Guard() { g_keep_uv = true; } ~Guard() { g_keep_uv = false; } } guard;
     Json g; std::vector<std::string> buffers;
-    read_glb(path, g, buffers);
+    if (ends_with(path, ".gltf")) {                                // JSON file + external buffers (data: URIs are not decoded)
+        g = parse_json(read_file(path, false));
+        if (const Json* jb = g.get("buffers"))
+            for (const Json& b : jb->arr) { const Json* uri = b.get("uri"); buffers.push_back(uri ? read_file(sibling(path, uri->str), true) : std::string()); }
+    } else read_glb(path, g, buffers);
     const Json* scenes = g.get("scenes");
-    if (!scenes || scenes->arr.empty()) { load_model_glb(path, vertices, indices, meshes); return; }   // no scene graph: every mesh once, untransformed
+    if (!scenes || scenes->arr.empty()) {                          // no scene graph: every mesh once, untransformed
+        if (const Json* jm = g.get("meshes"))
+            for (const Json& mesh : jm->arr)
+                for (const Json& prim : mesh.at("primitives").arr) append_primitive(g, buffers, prim, false, vertices, indices, meshes);
+        return;
+    }
     const Json* def = g.get("scene");
     const size_t si = def ? (size_t)def->num : 0;
     if (si >= scenes->arr.size()) throw std::runtime_error("GLB: bad default scene");

@@ -117,6 +117,20 @@ def test_glb_without_scene_graph_falls_back_to_plain_loader(tmp_path, glb):
     assert np.array_equal(vs.view(np.uint8), v0.view(np.uint8)) and np.array_equal(ix, i0) and np.array_equal(ms.view(np.uint8), m0.view(np.uint8))
 
 
+def test_gltf_with_external_buffer_imports_like_the_glb(tmp_path, glb):
+    from ray_tracer_b200 import host
+    path = glb[0]
+    data = open(path, "rb").read()
+    jl = struct.unpack("<I", data[12:16])[0]
+    g = json.loads(data[20:20 + jl])
+    g["buffers"][0]["uri"] = "graph.bin"
+    (tmp_path / "graph.bin").write_bytes(data[20 + jl + 8:])
+    (tmp_path / "graph.gltf").write_text(json.dumps(g))
+    a, b = host.load_scene_glb(str(tmp_path / "graph.gltf")), host.load_scene_glb(path)
+    for x, y in zip(a, b):
+        assert np.array_equal(x.view(np.uint8), y.view(np.uint8))
+
+
 @pytest.mark.gpu
 def test_glb_with_embedded_textures_renders_like_the_oracle(tmp_path, rtlib, oracle):
     """The whole extension chain on the GPU: a .glb with nested transforms, a material and an embedded PNG + baseline
