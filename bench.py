@@ -32,6 +32,9 @@ sys.path.insert(0, ROOT)
 
 METRIC = "Mrays/s (all bounces) at 1080p teapot"
 CPU_STRIDE = 8          # CPU arms trace every 8th pixel in x and y (1/64 of the image)
+# other configs: strides that keep a brute-force step within seconds on the box's host cores
+# (C1 is six spheres: every pixel; C2 is 428 triangles: every 2nd; C5 is 1.1 M primitives per ray: every 128th)
+CPU_STRIDES = {"c1_balls": 1, "c2_cube": 2, "c2_cube_plain": 2, "c5_stress": 128}
 
 # algorithmic flops per unit (DESIGN.md "Roofline"): FMA = 2
 F_BOX_PAIR = 48         # one node visit = two slab tests (2 x 24)
@@ -144,6 +147,7 @@ def run_reference(args, rank, world):
     from ray_tracer_b200 import configs
     scene, meta = configs.build(args.config)
     p = meta["params"]
+    CPU_STRIDE = CPU_STRIDES.get(args.config, globals()["CPU_STRIDE"])
     from oracle import rt_oracle as ro
     ro.build()
     for w in range(args.warmup):
@@ -153,8 +157,8 @@ def run_reference(args, rank, world):
         _, r, dt, threads = cpu_sample(scene, p, k, 1, CPU_STRIDE)
         rays += r; secs += dt
     value = rays / secs / 1e6
-    sample = "1 dispatch (2 spp) over every %dth pixel in x and y of %dx%d per step, brute force over %d triangles" % (
-        CPU_STRIDE, p["width"], p["height"], int(scene.meshes["triangles"].sum()))
+    sample = "1 dispatch (2 spp) over every %dth pixel in x and y of %dx%d per step, brute force over %d spheres + %d triangles" % (
+        CPU_STRIDE, p["width"], p["height"], int(scene.spheres.size), int(scene.meshes["triangles"].sum()))
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": secs / max(args.steps, 1) * 1e3,
@@ -344,10 +348,12 @@ def run_ours(args, rank, world, local_rank):
         if world == 1:
             from oracle import rt_oracle as ro
             ro.build()
+            CPU_STRIDE = CPU_STRIDES.get(args.config, globals()["CPU_STRIDE"])
             cpu_sample(scene, p, 0, 1, CPU_STRIDE * 4)
-            v, r, dt, threads = cpu_sample(scene, p, 0, 2, CPU_STRIDE)
+            nd = D if args.config == "c1_balls" else 2          # C1 is CPU-runnable in full (8 dispatches = 16 spp)
+            v, r, dt, threads = cpu_sample(scene, p, 0, nd, CPU_STRIDE)
             line["cpu_baseline"] = {"value": v, "unit": "Mrays/s", "cores": threads, "kind": "port",
-                                    "sample": "2 dispatches (4 spp) over every %dth pixel in x and y (%d rays, %.1f s), brute force" % (CPU_STRIDE, r, dt)}
+                                    "sample": "%d dispatches (%d spp) over every %dth pixel in x and y (%d rays, %.1f s), brute force" % (nd, 2 * nd, CPU_STRIDE, r, dt)}
         print(json.dumps(line), file=_JSON_OUT, flush=True)
     tr.close()
     if world > 1:

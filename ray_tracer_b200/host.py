@@ -85,6 +85,9 @@ def hostlib():
         L.rth_glb_images.restype = vp
         L.rth_glb_image.argtypes = [vp, u32, C.POINTER(u32), C.POINTER(u32), vp]
         L.rth_glb_images_free.argtypes = [vp]
+        L.rth_image_rmse.argtypes = [vp, vp, C.c_size_t]
+        L.rth_image_rmse.restype = C.c_double
+        L.rth_image_flip.argtypes = [vp, vp, u32, u32, C.c_double, vp, C.POINTER(C.c_double)]
         _hl = L
     return _hl
 
@@ -241,6 +244,41 @@ def load_glb_images(path):
     finally:
         L.rth_glb_images_free(lst)
     return out
+
+
+def tonemap(accum):
+    """What render.wgsl:34-39 + the sRGB swapchain display of an RGBA32F accumulation image: clamp to [0, 1] and
+    the sRGB OETF, as float RGB (the 8-bit form is rt_read_rgba8).  numpy, for comparing images on the host."""
+    c = np.clip(np.asarray(accum, dtype=np.float64)[..., :3], 0.0, 1.0)
+    return np.where(c <= 0.0031308, c * 12.92, 1.055 * np.power(c, 1.0 / 2.4) - 0.055).astype(np.float32)
+
+
+FLIP_PPD = 0.7 * 3840 / 0.7 * np.pi / 180      # the FLIP paper's default viewing condition: 67.02 pixels per degree
+
+
+def image_rmse(a, b):
+    """Root mean square difference over every value of two equally shaped float images."""
+    a, b = np.ascontiguousarray(a, dtype=np.float32), np.ascontiguousarray(b, dtype=np.float32)
+    if a.shape != b.shape:
+        raise HostError("image_rmse: shapes differ %s %s" % (a.shape, b.shape))
+    return float(hostlib().rth_image_rmse(_ptr(a), _ptr(b), a.size))
+
+
+def image_flip(ref, test, ppd=FLIP_PPD, want_map=False):
+    """Mean LDR-FLIP of two sRGB-encoded images ((H, W, 3+) float in [0, 1], or uint8); with want_map also the
+    per-pixel error map.  C++ restatement of the published metric (host/rt_imgdiff.cpp)."""
+    def prep(x):
+        x = np.asarray(x)
+        x = x.astype(np.float32) / np.float32(255) if x.dtype == np.uint8 else x.astype(np.float32)
+        return np.ascontiguousarray(x[..., :3])
+    r, t = prep(ref), prep(test)
+    if r.shape != t.shape or r.ndim != 3:
+        raise HostError("image_flip: shapes differ or not (H, W, 3): %s %s" % (r.shape, t.shape))
+    emap = np.empty(r.shape[:2], np.float32) if want_map else None
+    mean = C.c_double()
+    if hostlib().rth_image_flip(_ptr(r), _ptr(t), r.shape[1], r.shape[0], float(ppd), _ptr(emap), C.byref(mean)) != 0:
+        raise _err()
+    return (mean.value, emap) if want_map else mean.value
 
 
 KEYS = {"W": 0, "S": 1, "A": 2, "D": 3, "Up": 4, "Down": 5, "Left": 6, "Right": 7, "Space": 8, "LShift": 9, "Other": 10}

@@ -196,6 +196,11 @@ void rth_glb_image(const void* list, uint32_t k, uint32_t* w, uint32_t* h, uint8
     *w = i.width; *h = i.height;
     if (rgba && !i.rgba.empty()) memcpy(rgba, i.rgba.data(), i.rgba.size());
 }
+double rth_image_rmse(const float* a, const float* b, size_t n_values) { return rtb::image_rmse(a, b, n_values); }
+int rth_image_flip(const float* ref_srgb, const float* test_srgb, uint32_t w, uint32_t h, double ppd, float* error_map, double* mean)
+{
+    RTH_TRY(*mean = rtb::image_flip(ref_srgb, test_srgb, w, h, ppd, error_map));
+}
 void rth_glb_images_free(void* list) { delete (std::vector<rtb::Image>*)list; }
 void rth_scene_free(void* s) { delete (rtb::Scene*)s; }
 void rth_scene_counts(const void* h, uint32_t* ns, uint32_t* nv, uint32_t* ni, uint32_t* nm)

@@ -106,6 +106,11 @@ Image decode_jpeg(const uint8_t* data, size_t size);                // baseline 
 Image load_image(const std::string& path);                          // PNG or JPEG by signature
 std::vector<Image> load_glb_images(const std::string& path);        // PNG / baseline-JPEG images embedded in a .glb (others come back empty)
 void write_png(const std::string& path, const uint8_t* rgba, uint32_t width, uint32_t height);
+// Image comparison (rt_imgdiff.cpp; SURVEY §8(c) tiers T2/T3, §8(f3)): RMSE over n_values floats; mean LDR-FLIP
+// (Andersson et al. 2020) of two sRGB-encoded [0,1] RGB images, optional per-pixel error map (width*height floats).
+double image_rmse(const float* a, const float* b, size_t n_values);
+double image_flip(const float* ref_srgb, const float* test_srgb, uint32_t width, uint32_t height, double pixels_per_degree,
+                  float* error_map);
 // the hard-coded record each loaded primitive gets (resource.rs:73-85)
 rt_mesh loader_mesh(uint32_t mesh_count, uint32_t n_indices, uint32_t first, uint32_t offset);
 
