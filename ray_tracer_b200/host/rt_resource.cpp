@@ -48,6 +48,39 @@ std::string sibling(const std::string& path, const std::string& name)
     return p == std::string::npos ? name : path.substr(0, p + 1) + name;
 }
 
+// RFC 4648 base64 (padding optional, whitespace skipped); anything else throws
+std::string base64_decode(const char* s, size_t n)
+{
+    std::string out; out.reserve(n / 4 * 3);
+    uint32_t acc = 0; int bits = 0;
+    for (size_t i = 0; i < n; i++) {
+        const unsigned char c = (unsigned char)s[i];
+        int v;
+        if (c >= 'A' && c <= 'Z') v = c - 'A';
+        else if (c >= 'a' && c <= 'z') v = c - 'a' + 26;
+        else if (c >= '0' && c <= '9') v = c - '0' + 52;
+        else if (c == '+' || c == '-') v = 62;
+        else if (c == '/' || c == '_') v = 63;
+        else if (c == '=' ) break;
+        else if (c == ' ' || c == '\n' || c == '\r' || c == '\t') continue;
+        else throw std::runtime_error("glTF: bad character in a base64 data: URI");
+        acc = (acc << 6) | (uint32_t)v; bits += 6;
+        if (bits >= 8) { bits -= 8; out.push_back((char)((acc >> bits) & 0xffu)); }
+    }
+    return out;
+}
+
+// Scene-graph import only (extension): a glTF `uri` is a sibling file or an RFC 2397 `data:` URI with a base64
+// payload.  Upstream's loaders treat every uri as a file name (resource.rs:129-132, 211-214) and so do ours.
+std::string resolve_uri(const std::string& path, const std::string& uri)
+{
+    if (uri.compare(0, 5, "data:") != 0) return read_file(sibling(path, uri), true);
+    const size_t comma = uri.find(',');
+    if (comma == std::string::npos) throw std::runtime_error("glTF: data: URI without a payload");
+    if (uri.compare(comma >= 7 ? comma - 7 : 0, 7, ";base64") != 0) throw std::runtime_error("glTF: data: URI is not base64");
+    return base64_decode(uri.data() + comma + 1, uri.size() - comma - 1);
+}
+
 // ---- minimal JSON (enough for glTF) ----------------------------------------------------
 struct Json {
     enum Kind { Null, Bool, Num, Str, Arr, Obj } kind = Null;
@@ -407,10 +440,10 @@ void load_scene_glb(const std::string& path, std::vector<rt_vertex>& vertices, s
 {
     struct Guard { Guard() { g_keep_uv = true; } ~Guard() { g_keep_uv = false; } } guard;
     Json g; std::vector<std::string> buffers;
-    if (ends_with(path, ".gltf")) {                                // JSON file + external buffers (data: URIs are not decoded)
+    if (ends_with(path, ".gltf")) {                                // JSON file + external buffers or base64 data: URIs
         g = parse_json(read_file(path, false));
         if (const Json* jb = g.get("buffers"))
-            for (const Json& b : jb->arr) { const Json* uri = b.get("uri"); buffers.push_back(uri ? read_file(sibling(path, uri->str), true) : std::string()); }
+            for (const Json& b : jb->arr) { const Json* uri = b.get("uri"); buffers.push_back(uri ? resolve_uri(path, uri->str) : std::string()); }
     } else read_glb(path, g, buffers);
     const Json* scenes = g.get("scenes");
     if (!scenes || scenes->arr.empty()) {                          // no scene graph: every mesh once, untransformed
@@ -668,12 +701,16 @@ Image decode_jpeg(const uint8_t* d, size_t size)
     return img;
 }
 
+Image decode_image(const uint8_t* p, size_t size)
+{
+    if (size >= 2 && p[0] == 0xFF && p[1] == 0xD8) return decode_jpeg(p, size);
+    return decode_png(p, size);
+}
+
 Image load_image(const std::string& path)
 {
     std::string data = read_file(path, true);
-    const uint8_t* p = (const uint8_t*)data.data();
-    if (data.size() >= 2 && p[0] == 0xFF && p[1] == 0xD8) return decode_jpeg(p, data.size());
-    return decode_png(p, data.size());
+    return decode_image((const uint8_t*)data.data(), data.size());
 }
 
 Image load_png(const std::string& path)
@@ -707,30 +744,28 @@ void write_png(const std::string& path, const uint8_t* rgba, uint32_t W, uint32_
 
 std::vector<Image> load_glb_images(const std::string& path)
 {
-    std::string data = read_file(path, true);
-    if (data.size() < 20 || memcmp(data.data(), "glTF", 4) != 0) throw std::runtime_error("GLB: bad magic");
-    std::string json, blob;
-    for (size_t off = 12; off + 8 <= data.size();) {
-        uint32_t clen, ctype; memcpy(&clen, &data[off], 4); memcpy(&ctype, &data[off + 4], 4);
-        if (off + 8 + clen > data.size()) throw std::runtime_error("GLB: truncated chunk");
-        if (ctype == 0x4E4F534Au) json.assign(data, off + 8, clen);
-        else if (ctype == 0x004E4942u && blob.empty()) blob.assign(data, off + 8, clen);
-        off += 8 + (size_t)clen;
-    }
-    Json g = parse_json(json);
+    Json g; std::vector<std::string> buffers;
+    const bool text = ends_with(path, ".gltf");
+    if (text) {
+        g = parse_json(read_file(path, false));
+        if (const Json* jb = g.get("buffers"))
+            for (const Json& b : jb->arr) { const Json* uri = b.get("uri"); buffers.push_back(uri ? resolve_uri(path, uri->str) : std::string()); }
+    } else read_glb(path, g, buffers);
     std::vector<Image> out;
     if (const Json* ji = g.get("images"))
         for (const Json& im : ji->arr) {
             Image img;
-            const Json* bv = im.get("bufferView"); const Json* mt = im.get("mimeType");
-            if (bv && mt && (mt->str == "image/png" || mt->str == "image/jpeg")) {
+            std::string bytes;
+            if (const Json* bv = im.get("bufferView")) {                       // embedded: a bufferView of one of the buffers
                 const Json& v = g.at("bufferViews").arr.at((size_t)bv->num);
-                size_t off = (size_t)v.integer("byteOffset", 0), len = (size_t)v.integer("byteLength", 0);
-                if (off + len > blob.size()) throw std::runtime_error("GLB: image outside the binary chunk");
-                const uint8_t* q = (const uint8_t*)blob.data() + off;
-                if (mt->str == "image/png") img = decode_png(q, len);
-                else { try { img = decode_jpeg(q, len); } catch (const std::exception&) { img = Image(); } }   // progressive JPEGs stay empty
+                const size_t bi = (size_t)v.integer("buffer", 0), off = (size_t)v.integer("byteOffset", 0), len = (size_t)v.integer("byteLength", 0);
+                if (bi >= buffers.size() || off + len > buffers[bi].size()) throw std::runtime_error("GLB: image outside its buffer");
+                bytes.assign(buffers[bi], off, len);
+            } else if (const Json* uri = im.get("uri")) {                      // .gltf: sibling file or data: URI; a missing file leaves the entry empty
+                try { bytes = resolve_uri(path, uri->str); } catch (const std::exception&) { bytes.clear(); }
             }
+            // by signature, not by mimeType (optional for uri images); unsupported encodings (progressive JPEG, KTX, WebP) stay empty
+            try { if (!bytes.empty()) img = decode_image((const uint8_t*)bytes.data(), bytes.size()); } catch (const std::exception&) { img = Image(); }
             out.push_back(std::move(img));
         }
     return out;

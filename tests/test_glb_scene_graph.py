@@ -131,6 +131,39 @@ def test_gltf_with_external_buffer_imports_like_the_glb(tmp_path, glb):
         assert np.array_equal(x.view(np.uint8), y.view(np.uint8))
 
 
+def test_gltf_with_data_uris_for_buffer_and_images(tmp_path, glb):
+    """A .gltf whose buffer and images are base64 `data:` URIs (or sibling image files) imports like the .glb."""
+    import base64
+    import io
+    from PIL import Image
+    from ray_tracer_b200 import host
+    path = glb[0]
+    data = open(path, "rb").read()
+    jl = struct.unpack("<I", data[12:16])[0]
+    gltf, blob = json.loads(data[20:20 + jl]), data[20 + jl + 8:]
+    rng = np.random.default_rng(5)
+    tex = rng.integers(0, 256, (8, 8, 4), dtype=np.uint8)
+    tex[..., 3] = 255
+    png = io.BytesIO(); Image.fromarray(tex, "RGBA").save(png, "PNG")
+    (tmp_path / "side.png").write_bytes(png.getvalue())
+    g = json.loads(json.dumps(gltf))
+    g["buffers"] = [{"byteLength": len(blob), "uri": "data:application/octet-stream;base64," + base64.b64encode(blob).decode()}]
+    g["images"] = [{"uri": "data:image/png;base64," + base64.b64encode(png.getvalue()).decode()}, {"uri": "side.png"}, {"uri": "missing.png"}]
+    (tmp_path / "inline.gltf").write_text(json.dumps(g))
+    a, b = host.load_scene_glb(str(tmp_path / "inline.gltf")), host.load_scene_glb(path)
+    for x, y in zip(a, b):
+        assert x.tobytes() == y.tobytes()
+    ims = host.load_glb_images(str(tmp_path / "inline.gltf"))
+    assert len(ims) == 3 and np.array_equal(ims[0], tex) and np.array_equal(ims[1], tex) and ims[2].size == 0
+    # upstream's own loader keeps treating a uri as a file name (resource.rs:129-132): a data: URI is a missing file there
+    with pytest.raises(host.HostError):
+        host.load_model(str(tmp_path / "inline.gltf"))
+    g["buffers"][0]["uri"] = "data:application/octet-stream;base64,@@@@"
+    (tmp_path / "bad.gltf").write_text(json.dumps(g))
+    with pytest.raises(host.HostError):
+        host.load_scene_glb(str(tmp_path / "bad.gltf"))
+
+
 @pytest.mark.gpu
 def test_glb_with_embedded_textures_renders_like_the_oracle(tmp_path, rtlib, oracle):
     """The whole extension chain on the GPU: a .glb with nested transforms, a material and an embedded PNG + baseline
