@@ -218,6 +218,21 @@ int rt_clear(rt_ctx* ctx);
 int rt_set_shard(rt_ctx* ctx, uint32_t tile_rank, uint32_t tile_world,
                  uint32_t frame_rank, uint32_t frame_world);
 
+/* In-process combine of the shards (one rt_ctx per device, one host thread driving them all, as a single-process
+ * host like the reference's event loop would): folds the accumulation images of ctxs[0..n-1] into ctxs[0]'s image
+ * with ONE kernel on ctxs[0]'s device that reads the other images out of their devices' memory through NVLink peer
+ * loads (cudaDeviceEnablePeerAccess; contexts on the same device need none).  For every pixel only the contexts
+ * whose tile shard owns it are read; each enters with weights[k], or with 1 / frame_world of its rt_set_shard when
+ * weights == NULL (the count-weighted mean of equally long sample shards), summed in array order.  A pure tile
+ * partition therefore reproduces the single-GPU image bit for bit.  Pixels no context owns keep ctxs[0]'s value.
+ * Ordered after everything queued on every context's stream; later work on any of them waits for the combine.
+ * All contexts must have the same size; 1 <= n <= 16.  (Multi-process hosts combine with NCCL on
+ * rt_accum_device_ptr instead, as bench.py does.) */
+int rt_combine_peers(rt_ctx* const* ctxs, uint32_t n, const float* weights);
+/* The same combine fused with the display transform of rt_read_rgba8 (clamp, sRGB OETF, 8 bit) and the copy to the
+ * host: no context's accumulation image is modified.  Synchronous. */
+int rt_combine_peers_rgba8(rt_ctx* const* ctxs, uint32_t n, const float* weights, uint8_t* rgba, size_t n_bytes);
+
 int rt_set_option(rt_ctx* ctx, int option, int64_t value);
 int rt_get_option(const rt_ctx* ctx, int option, int64_t* value);
 

@@ -75,6 +75,8 @@ SYMBOLS = {
     "rt_resize": (C.c_int, [_vp, _u32, _u32]),
     "rt_clear": (C.c_int, [_vp]),
     "rt_set_shard": (C.c_int, [_vp, _u32, _u32, _u32, _u32]),
+    "rt_combine_peers": (C.c_int, [C.POINTER(_vp), _u32, _vp]),
+    "rt_combine_peers_rgba8": (C.c_int, [C.POINTER(_vp), _u32, _vp, _vp, _sz]),
     "rt_set_option": (C.c_int, [_vp, C.c_int, _i64]),
     "rt_get_option": (C.c_int, [_vp, C.c_int, C.POINTER(_i64)]),
     "rt_read_accum": (C.c_int, [_vp, _vp, _sz]),

@@ -448,6 +448,74 @@ int rt_set_shard(rt_ctx* c, uint32_t tile_rank, uint32_t tile_world, uint32_t fr
     return RT_OK;
 }
 
+namespace {
+// shared body of rt_combine_peers / rt_combine_peers_rgba8
+int combine_peers(rt_ctx* const* ctxs, uint32_t n, const float* weights, uint8_t* host_rgba8, size_t n_bytes, const char* who)
+{
+    if (!ctxs || n == 0 || !ctxs[0]) return RT_ERR_INVALID_ARGUMENT;
+    rt_ctx* c = ctxs[0];
+    if (n > RT_MAX_PEERS) return fail(c, RT_ERR_INVALID_ARGUMENT, std::string(who) + ": at most 16 contexts");
+    const size_t npx = (size_t)c->width * c->height;
+    if (host_rgba8 && n_bytes != npx * 4) return fail(c, RT_ERR_INVALID_ARGUMENT, std::string(who) + ": size must be W*H*4");
+    rt::PeerSet ps{};
+    ps.n = n;
+    for (uint32_t k = 0; k < n; k++) {
+        rt_ctx* p = ctxs[k];
+        if (!p) return fail(c, RT_ERR_INVALID_ARGUMENT, std::string(who) + ": NULL context");
+        if (p->width != c->width || p->height != c->height) return fail(c, RT_ERR_INVALID_ARGUMENT, std::string(who) + ": contexts differ in size");
+        for (uint32_t j = 0; j < k; j++) if (ctxs[j] == p) return fail(c, RT_ERR_INVALID_ARGUMENT, std::string(who) + ": a context is listed twice");
+        ps.p[k].accum = p->accum; ps.p[k].tile_rank = p->tile_rank; ps.p[k].tile_world = p->tile_world;
+        ps.p[k].weight = weights ? weights[k] : 1.0f / (float)p->frame_world;
+    }
+    if (npx == 0) return RT_OK;
+    DeviceGuard g(c->device);
+    // peer access + ordering: the combine waits for every shard's stream, and the shards wait for the combine
+    std::vector<cudaEvent_t> events;
+    auto drop = [&]() { for (cudaEvent_t e : events) cudaEventDestroy(e); };
+    for (uint32_t k = 1; k < n; k++) {
+        rt_ctx* p = ctxs[k];
+        if (p->device != c->device) {
+            int can = 0;
+            CU(c, cudaDeviceCanAccessPeer(&can, c->device, p->device));
+            if (!can) { drop(); return fail(c, RT_ERR_UNSUPPORTED, std::string(who) + ": device " + std::to_string(c->device) + " has no peer access to device " + std::to_string(p->device)); }
+            cudaError_t e = cudaDeviceEnablePeerAccess(p->device, 0);
+            if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+            else if (e != cudaSuccess) { drop(); return cuda_fail(c, e, "cudaDeviceEnablePeerAccess"); }
+        }
+        cudaEvent_t ev = nullptr;
+        cudaError_t e;
+        { DeviceGuard gp(p->device); e = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming); if (e == cudaSuccess) { events.push_back(ev); e = cudaEventRecord(ev, p->stream); } }
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(c->stream, ev, 0);
+        if (e != cudaSuccess) { drop(); return cuda_fail(c, e, "combine: ordering after a shard's stream"); }
+    }
+    uint8_t* d8 = nullptr;
+    if (host_rgba8) { cudaError_t e = cudaMallocAsync((void**)&d8, npx * 4, c->stream); if (e != cudaSuccess) { drop(); return cuda_fail(c, e, "cudaMallocAsync rgba8"); } }
+    cudaError_t e = rt::launch_combine(ps, c->accum, d8, c->width, c->height, c->n_sms, c->stream);
+    cudaEvent_t done = nullptr;
+    if (e == cudaSuccess && n > 1) e = cudaEventCreateWithFlags(&done, cudaEventDisableTiming);
+    if (done) events.push_back(done);
+    if (e == cudaSuccess && done) e = cudaEventRecord(done, c->stream);
+    for (uint32_t k = 1; k < n && e == cudaSuccess; k++) { DeviceGuard gp(ctxs[k]->device); e = cudaStreamWaitEvent(ctxs[k]->stream, done, 0); }
+    if (e == cudaSuccess && host_rgba8) e = cudaMemcpyAsync(host_rgba8, d8, npx * 4, cudaMemcpyDeviceToHost, c->stream);
+    if (d8) cudaFreeAsync(d8, c->stream);
+    if (e == cudaSuccess && host_rgba8) e = cudaStreamSynchronize(c->stream);
+    drop();
+    if (e != cudaSuccess) return cuda_fail(c, e, who);
+    return RT_OK;
+}
+} // namespace
+
+int rt_combine_peers(rt_ctx* const* ctxs, uint32_t n, const float* weights)
+{
+    return combine_peers(ctxs, n, weights, nullptr, 0, "rt_combine_peers");
+}
+
+int rt_combine_peers_rgba8(rt_ctx* const* ctxs, uint32_t n, const float* weights, uint8_t* rgba, size_t n_bytes)
+{
+    if (!rgba) return (ctxs && n && ctxs[0]) ? fail(ctxs[0], RT_ERR_INVALID_ARGUMENT, "rt_combine_peers_rgba8: NULL") : RT_ERR_INVALID_ARGUMENT;
+    return combine_peers(ctxs, n, weights, rgba, n_bytes, "rt_combine_peers_rgba8");
+}
+
 int rt_set_option(rt_ctx* c, int option, int64_t value)
 {
     if (!c) return RT_ERR_INVALID_ARGUMENT;

@@ -105,4 +105,12 @@ cudaError_t launch_blend(const LaunchParams& lp, const float4* staging, float4* 
 
 cudaError_t launch_tonemap(const float4* accum, uint8_t* rgba8, size_t n_pixels, cudaStream_t stream);
 
+// ---- multi-GPU image combine over peer memory (rt_combine.cu) -----------------------------------
+#define RT_MAX_PEERS 16
+struct PeerSrc { const float4* accum; uint32_t tile_rank, tile_world; float weight; };
+struct PeerSet { PeerSrc p[RT_MAX_PEERS]; uint32_t n; };
+// out (RGBA32F, may alias p[0].accum) or, when rgba8 != nullptr, the tone-mapped image (out is then only read
+// for pixels no shard owns); runs on `stream` of the device that owns out / rgba8.
+cudaError_t launch_combine(const PeerSet& ps, float4* out, uint8_t* rgba8, uint32_t width, uint32_t height, int n_sms, cudaStream_t stream);
+
 } // namespace rt

@@ -177,3 +177,27 @@ class RayTracer:
     @property
     def device(self):
         return self._L.rt_device(self._h)
+
+
+def _peer_args(tracers, weights):
+    tracers = list(tracers)
+    arr = (C.c_void_p * len(tracers))(*[t._h for t in tracers])
+    w = None if weights is None else np.ascontiguousarray(weights, dtype=np.float32)
+    if w is not None and w.size != len(tracers):
+        raise RtError(_lib.RT_ERR_INVALID_ARGUMENT, "combine_peers: one weight per context")
+    return tracers, arr, w
+
+
+def combine_peers(tracers, weights=None):
+    """rt_combine_peers: fold the shards' images into tracers[0]'s with one kernel over NVLink peer memory."""
+    tracers, arr, w = _peer_args(tracers, weights)
+    tracers[0]._ck(tracers[0]._L.rt_combine_peers(arr, len(tracers), _ptr(w) if w is not None else None))
+
+
+def combine_peers_rgba8(tracers, weights=None):
+    """rt_combine_peers_rgba8: the combine fused with the display transform -> (H, W, 4) uint8 on the host."""
+    tracers, arr, w = _peer_args(tracers, weights)
+    t0 = tracers[0]
+    out = np.empty((t0.height, t0.width, 4), np.uint8)
+    t0._ck(t0._L.rt_combine_peers_rgba8(arr, len(tracers), _ptr(w) if w is not None else None, _ptr(out), out.size))
+    return out

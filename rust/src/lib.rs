@@ -61,6 +61,8 @@ extern "C" {
     pub fn rt_resize(ctx: *mut RtCtx, width: u32, height: u32) -> c_int;
     pub fn rt_clear(ctx: *mut RtCtx) -> c_int;
     pub fn rt_set_shard(ctx: *mut RtCtx, tile_rank: u32, tile_world: u32, frame_rank: u32, frame_world: u32) -> c_int;
+    pub fn rt_combine_peers(ctxs: *const *mut RtCtx, n: u32, weights: *const f32) -> c_int;
+    pub fn rt_combine_peers_rgba8(ctxs: *const *mut RtCtx, n: u32, weights: *const f32, rgba: *mut u8, n_bytes: usize) -> c_int;
     pub fn rt_set_option(ctx: *mut RtCtx, option: c_int, value: i64) -> c_int;
     pub fn rt_get_option(ctx: *const RtCtx, option: c_int, value: *mut i64) -> c_int;
     pub fn rt_read_accum(ctx: *mut RtCtx, rgba: *mut f32, n_floats: usize) -> c_int;
@@ -140,3 +142,19 @@ impl RayTracer {
     pub fn counters(&self) -> Result<Counters> { let mut c = Counters::default(); self.check(unsafe { rt_get_counters(self.ctx, &mut c) })?; Ok(c) }
 }
 impl Drop for RayTracer { fn drop(&mut self) { unsafe { rt_destroy(self.ctx) } } }
+
+/// Several GPUs from one process (one `RayTracer` per device, sharded with `set_shard`): folds every shard's image
+/// into `shards[0]`'s with one kernel over NVLink peer memory. `weights = None`: 1 / frame_world of each shard.
+pub fn combine_peers(shards: &[&RayTracer], weights: Option<&[f32]>) -> Result<()> {
+    let ptrs: Vec<*mut RtCtx> = shards.iter().map(|s| s.ctx).collect();
+    let w = weights.map_or(std::ptr::null(), |w| w.as_ptr());
+    shards[0].check(unsafe { rt_combine_peers(ptrs.as_ptr(), ptrs.len() as u32, w) })
+}
+/// The same combine fused with the display transform (clamp, sRGB OETF, 8 bit), straight to host memory.
+pub fn combine_peers_rgba8(shards: &[&RayTracer], weights: Option<&[f32]>) -> Result<Vec<u8>> {
+    let ptrs: Vec<*mut RtCtx> = shards.iter().map(|s| s.ctx).collect();
+    let w = weights.map_or(std::ptr::null(), |w| w.as_ptr());
+    let mut v = vec![0u8; shards[0].width as usize * shards[0].height as usize * 4];
+    shards[0].check(unsafe { rt_combine_peers_rgba8(ptrs.as_ptr(), ptrs.len() as u32, w, v.as_mut_ptr(), v.len()) })?;
+    Ok(v)
+}

@@ -1,0 +1,108 @@
+"""GPU tests of rt_combine_peers / rt_combine_peers_rgba8: the shards' images folded into one by a single kernel
+(over NVLink peer memory when the contexts live on different devices; the same kernel on one device otherwise).
+No reference counterpart (upstream is single-device): the checks are against the single-context image, bit for
+bit for tile shards, and against the weighted sum evaluated in numpy for sample shards."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from util import assert_bits_equal
+
+pytestmark = pytest.mark.gpu
+W, H, BOUNCES = 88, 56, 4
+
+
+def _devices(n):
+    """n device indices: distinct GPUs when the box has them, else all on device 0."""
+    import torch
+    have = torch.cuda.device_count()
+    return [k % max(have, 1) for k in range(n)]
+
+
+def _tracer(rt, dev, scene, **shard):
+    cam, sp, vs, ix, ms = scene
+    tr = rt.RayTracer(dev, W, H)
+    tr.upload_scene(sp, vs, ix, ms)
+    tr.set_camera(cam)
+    tr.set_params(number_of_bounces=BOUNCES, rays_per_pixel=1, skybox=1, frames=0)
+    tr.set_shard(**shard)
+    return tr
+
+
+def _scene(name):
+    from oracle import host_ref as hr
+    return getattr(hr, "scene_" + name)(np.float32(W) / np.float32(H))
+
+
+def test_tile_shards_combine_to_the_single_context_image_bit_for_bit(rtlib):
+    scene, frames = _scene("room"), 4
+    one = _tracer(rtlib, 0, scene); one.render_frames(0, frames); full = one.read_accum(); full8 = one.read_rgba8(); one.close()
+    for world in (2, 3):
+        trs = [_tracer(rtlib, d, scene, tile_rank=r, tile_world=world) for r, d in enumerate(_devices(world))]
+        for t in trs:
+            t.render_frames(0, frames)                     # asynchronous on every context's stream
+        got8 = rtlib.combine_peers_rgba8(trs)               # fused combine + tone-map, accumulation images untouched
+        assert np.array_equal(got8, full8)
+        part0 = trs[0].read_accum()
+        assert not np.array_equal(part0, full)
+        rtlib.combine_peers(trs)
+        assert_bits_equal(trs[0].read_accum(), full, "tile shards, world %d" % world)
+        # the other contexts keep their own tiles and can go on rendering
+        trs[1].render_frames(frames, 1); trs[1].sync()
+        for t in trs:
+            t.close()
+
+
+def test_tile_and_sample_shards_combine_like_the_weighted_sum(rtlib):
+    scene, frames = _scene("balls"), 6
+    T, F = 2, 2
+    trs = [_tracer(rtlib, d, scene, tile_rank=k % T, tile_world=T, frame_rank=k // T, frame_world=F)
+           for k, d in enumerate(_devices(T * F))]
+    for t in trs:
+        t.render_frames(0, frames)
+    parts = [t.read_accum() for t in trs]
+    from ray_tracer_b200 import sharding
+    owner = sharding.tile_owner(W, H, T)
+    want = np.zeros_like(parts[0])
+    seen = np.zeros((H, W), bool)
+    half = np.float32(1.0) / np.float32(F)
+    for k, p in enumerate(parts):                           # array order, separately rounded multiply and add
+        m = owner == k % T
+        term = (p * half).astype(np.float32)
+        want[m] = np.where(seen[m][:, None], (want[m] + term[m]).astype(np.float32), term[m])
+        seen |= m
+    rtlib.combine_peers(trs)
+    got = trs[0].read_accum()
+    assert_bits_equal(got, want, "2 tile x 2 sample shards")
+    one = _tracer(rtlib, 0, scene); one.render_frames(0, frames); full = one.read_accum(); one.close()
+    assert np.allclose(got, full, rtol=2e-6, atol=1e-6)     # equal to the sequential running mean up to f32 rounding
+    # explicit weights: 3 frames of shard 0 against 1 of shard 1
+    for t in trs:
+        t.close()
+    a = _tracer(rtlib, 0, scene); a.render_frames(0, 3)
+    b = _tracer(rtlib, _devices(2)[1], scene); b.set_params(number_of_bounces=BOUNCES, rays_per_pixel=1, skybox=1, frames=-3); b.dispatch()
+    pa, pb = a.read_accum(), b.read_accum()
+    rtlib.combine_peers([a, b], weights=[0.75, 0.25])
+    assert_bits_equal(a.read_accum(), ((pa * np.float32(0.75)).astype(np.float32) + (pb * np.float32(0.25)).astype(np.float32)).astype(np.float32), "weighted")
+    one = _tracer(rtlib, 0, scene); one.render_frames(0, 4); full4 = one.read_accum(); one.close()
+    assert np.allclose(a.read_accum(), full4, rtol=2e-6, atol=1e-6)
+    a.close(); b.close()
+
+
+def test_combine_errors(rtlib):
+    scene = _scene("balls")
+    a = _tracer(rtlib, 0, scene)
+    b = rtlib.RayTracer(0, W + 8, H)
+    with pytest.raises(rtlib.RtError):
+        rtlib.combine_peers([a, b])                         # sizes differ
+    with pytest.raises(rtlib.RtError):
+        rtlib.combine_peers([a, a])                         # listed twice
+    with pytest.raises(rtlib.RtError):
+        rtlib.combine_peers([a] + [b] * 16)                 # more than 16
+    assert rtlib._lib.lib().rt_combine_peers(None, 0, None) == rtlib._lib.RT_ERR_INVALID_ARGUMENT
+    rtlib.combine_peers([a])                                # one context: weight 1, image unchanged
+    a.render_frames(0, 2); img = a.read_accum()
+    rtlib.combine_peers([a])
+    assert_bits_equal(a.read_accum(), img, "single context")
+    a.close(); b.close()
