@@ -170,12 +170,15 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
                     // camera ray, wgsl:313-321
                     const uint32_t py = lp.div_width.div(pix), px = pix - py * lp.width;
                     float aax = rand01(rng), aay = rand01(rng);
-                    float posx = ((float)px + aax) / sw, posy = ((float)py + aay) / sh;
+                                        float posx = ((float)px + aax) / sw, posy = ((float)py + aay) / sh;
                     float rdx, rdy;
                     for (;;) {                                   // rand_in_unit_disk, wgsl:216-227
                         float r1 = rand01(rng) * 2.0f, r2 = rand01(rng) * 2.0f;
                         rdx = r1 - 1.0f; rdy = r2 - 1.0f;
-                        if (length3(f3(rdx, rdy, 0.0f)) <= 1.0f) break;
+                        // wgsl:222 `length(p) <= 1.0` without the square root: for a correctly rounded sqrt, sqrt(x) <= 1 exactly when
+                        // x <= 1 + 2^-23 (sqrt(1 + 2^-23) rounds to 1, sqrt(1 + 2^-22) to 1 + 2^-23; checked in tests/test_oracle_math.py).
+                        // The loop runs until the last lane of the warp accepts, so its body is paid about three times per pass.
+                        if (dot3(f3(rdx, rdy, 0.0f), f3(rdx, rdy, 0.0f)) <= 1.00000011920928955078125f) break;
                     }
                     rdx = rdx * cam.lens_radius; rdy = rdy * cam.lens_radius;
                     float3 offset = fma3(cam.v, rdy, cam.u * rdx);

@@ -359,7 +359,7 @@ wave_miss(CameraDev cam, WaveDev wv, LaunchParams lp, float4* __restrict__ stagi
                 for (;;) {                                   // rand_in_unit_disk, wgsl:216-227
                     float r1 = rand01(rng) * 2.0f, r2 = rand01(rng) * 2.0f;
                     rdx = r1 - 1.0f; rdy = r2 - 1.0f;
-                    if (length3(f3(rdx, rdy, 0.0f)) <= 1.0f) break;
+                    if (dot3(f3(rdx, rdy, 0.0f), f3(rdx, rdy, 0.0f)) <= 1.00000011920928955078125f) break;   // == length(p) <= 1.0, see rt_trace.cu
                 }
                 rdx = rdx * cam.lens_radius; rdy = rdy * cam.lens_radius;
                 float3 offset = fma3(cam.v, rdy, cam.u * rdx);

@@ -55,3 +55,18 @@ def test_exp2_and_pow(oracle):
     got = np.array([L.rto_pow(C.c_float(float(x)), C.c_float(500.0)) for x in xs[xs > 0.9]], np.float64)
     want = xs[xs > 0.9].astype(np.float64) ** 500.0
     assert (np.abs(got - want) <= 2e-4 * want + 1e-30).all()   # 500 x the log's rounding error, as GLSL's definition implies
+
+
+def test_unit_disk_acceptance_without_the_square_root():
+    """The trace kernel accepts a lens sample when dot(p, p) <= 1 + 2^-23 instead of wgsl:222's length(p) <= 1.0:
+    with a correctly rounded square root the two tests agree for every float (sqrt is monotonic, sqrt(1 + 2^-23) rounds
+    to 1, sqrt(1 + 2^-22) to 1 + 2^-23).  Checked on every float of [0.5, 2] and samples of the rest of the range."""
+    one = np.float32(1.0)
+    bound = np.nextafter(one, np.float32(2.0))
+    assert float(bound) == 1.00000011920928955078125
+    xs = np.arange(np.float32(0.5).view(np.uint32), np.float32(2.0).view(np.uint32) + 1, dtype=np.uint32).view(np.float32)
+    assert np.array_equal(np.sqrt(xs) <= one, xs <= bound)
+    rest = np.concatenate([np.float32([0.0, 1e-45, 1e-38, 1e-20, 0.25, 0.4999999, 2.0000002, 4.0, 8.0, 3e38, np.inf]),
+                           np.random.RandomState(5).uniform(0, 8, 200000).astype(np.float32)])
+    assert np.array_equal(np.sqrt(rest) <= one, rest <= bound)
+    assert not (np.float32(np.nan) <= bound)                    # NaN is rejected by both forms
