@@ -1,5 +1,5 @@
-# GPU-box A/B helper: the same sweep on tuning builds (ray_tracer_b200/variants/librt_b200_<name>.so) and the in-tree build
-# usage: bash scripts/gpu_ab.sh "base main" ["combos"]
+# GPU-box A/B helper: the same sweep on tuning builds (ray_tracer_b200/variants/librt_b200_<name>.so, made by
+# scripts/build_variant.sh) and the in-tree build ("main"): bash scripts/gpu_ab.sh "base main" ["n_stay,s_min;..."]
 mkdir -p gpurun_out/ab
 COMBOS=${2:-"8,22"}
 for rep in 1 2; do
