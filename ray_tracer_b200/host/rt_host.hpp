@@ -102,11 +102,11 @@ void load_scene_glb(const std::string& path, std::vector<rt_vertex>& vertices, s
 struct Image { uint32_t width = 0, height = 0; std::vector<uint8_t> rgba; };
 Image load_png(const std::string& path);                            // 8/16-bit grey, grey+alpha, RGB, RGBA, palette; no interlace
 Image decode_png(const uint8_t* data, size_t size);
-Image decode_jpeg(const uint8_t* data, size_t size);                // baseline sequential JPEG (8 bit, Huffman); progressive files throw
+Image decode_jpeg(const uint8_t* data, size_t size);                // sequential and progressive DCT JPEG (8 bit, Huffman); arithmetic / lossless files throw
 Image decode_image(const uint8_t* data, size_t size);               // PNG or JPEG by signature
 Image load_image(const std::string& path);
 // images[] of a .glb (bufferViews of the binary chunk) or a .gltf (bufferViews, sibling files, base64 data: URIs), in order;
-// entries this decoder does not read (progressive JPEG, other formats, missing files) come back empty
+// entries this decoder does not read (other formats, arithmetic-coded JPEG, missing files) come back empty
 std::vector<Image> load_glb_images(const std::string& path);
 void write_png(const std::string& path, const uint8_t* rgba, uint32_t width, uint32_t height);
 // Image comparison (rt_imgdiff.cpp; SURVEY §8(c) tiers T2/T3, §8(f3)): RMSE over n_values floats; mean LDR-FLIP

@@ -541,9 +541,11 @@ Image decode_png(const uint8_t* d, size_t size)
     return img;
 }
 
-// ---- baseline JPEG (ITU T.81 sequential DCT, Huffman, 8 bit; grey or YCbCr, any sampling factors; restart
-// intervals).  Progressive / arithmetic / 12-bit files are refused.  Chroma is upsampled bilinearly (the
-// triangle filter libjpeg calls "fancy upsampling"), the inverse DCT is evaluated in float. --------------------
+// ---- JPEG (ITU T.81 DCT-based, Huffman, 8 bit): baseline / extended sequential (SOF0, SOF1) and progressive (SOF2:
+// spectral selection + successive approximation, Annex G), grey or YCbCr with any sampling factors, interleaved and
+// non-interleaved scans, restart intervals.  Arithmetic coding, lossless and 12-bit files are refused.  All scans are
+// gathered into coefficient arrays first; chroma is upsampled bilinearly (the triangle filter libjpeg calls "fancy
+// upsampling"), the inverse DCT is evaluated in float. --------------------------------------------------------------
 namespace {
 struct JpegHuff { uint16_t code_first[17]; int val_first[17]; int count[17]; uint8_t vals[256]; bool set = false; };
 struct JpegBits {
@@ -584,30 +586,116 @@ void jpeg_idct(const float* in, uint8_t* out, size_t stride)
         out[y * stride + x] = (uint8_t)(r < 0 ? 0 : (r > 255 ? 255 : r));
     }
 }
+struct JpegComp {
+    int id = 0, h = 1, v = 1, tq = 0, td = 0, ta = 0, pred = 0;
+    size_t w = 0, hgt = 0;            // padded plane size (whole MCUs)
+    size_t bw = 0, bh = 0;            // blocks that carry image samples (the block grid of a non-interleaved scan, T.81 A.2.2)
+    size_t bstride = 0;               // blocks per padded row
+    std::vector<int16_t> coef;        // 64 per block, zigzag order, as decoded (not dequantised)
+    std::vector<uint8_t> px;
+};
+// one block of one scan into `blk` (zigzag order).  progressive == false: the sequential procedure of F.2.2.
+void jpeg_block(JpegBits& br, JpegComp& c, const JpegHuff* hdc, const JpegHuff* hac, int16_t* blk, bool progressive,
+                int ss, int se, int ah, int al, int& eobrun)
+{
+    if (!progressive) {
+        const int t = jpeg_decode(br, hdc[c.td]);
+        if (t > 11) throw std::runtime_error("JPEG: bad DC size");
+        c.pred += jpeg_extend(br.bits(t), t);
+        blk[0] = (int16_t)c.pred;
+        for (int z = 1; z < 64;) {
+            const int rs = jpeg_decode(br, hac[c.ta]), r = rs >> 4, sz = rs & 15;
+            if (sz == 0) { if (r == 15) { z += 16; continue; } break; }
+            z += r;
+            if (z > 63) throw std::runtime_error("JPEG: bad AC run");
+            blk[z] = (int16_t)jpeg_extend(br.bits(sz), sz);
+            z++;
+        }
+        return;
+    }
+    if (ss == 0) {                                                   // DC scan (G.1.2.1)
+        if (ah == 0) {
+            const int t = jpeg_decode(br, hdc[c.td]);
+            if (t > 11) throw std::runtime_error("JPEG: bad DC size");
+            c.pred += jpeg_extend(br.bits(t), t);
+            blk[0] = (int16_t)(c.pred * (1 << al));
+        } else if (br.bit()) blk[0] = (int16_t)(blk[0] | (1 << al));
+        return;
+    }
+    const JpegHuff& h = hac[c.ta];
+    if (ah == 0) {                                                   // AC first pass (G.1.2.2)
+        if (eobrun > 0) { eobrun--; return; }
+        for (int k = ss; k <= se; k++) {
+            const int rs = jpeg_decode(br, h), r = rs >> 4, sz = rs & 15;
+            if (sz == 0) {
+                if (r < 15) { eobrun = (1 << r) - 1; if (r) eobrun += br.bits(r); break; }
+                k += 15;
+            } else {
+                k += r;
+                if (k > se) throw std::runtime_error("JPEG: bad AC run");
+                blk[k] = (int16_t)(jpeg_extend(br.bits(sz), sz) * (1 << al));
+            }
+        }
+        return;
+    }
+    // AC refinement (G.1.2.3): correction bits for the coefficients that are already non-zero, new +-1 << al values between them
+    const int p1 = 1 << al, m1 = -(1 << al);
+    auto refine = [&](int16_t& v) { if (br.bit() && (v & p1) == 0) v = (int16_t)(v + (v >= 0 ? p1 : m1)); };
+    int k = ss;
+    if (eobrun == 0) {
+        for (; k <= se; k++) {
+            const int rs = jpeg_decode(br, h);
+            int r = rs >> 4; const int sz = rs & 15;
+            int value = 0;
+            if (sz == 0) {
+                if (r < 15) { eobrun = 1 << r; if (r) eobrun += br.bits(r); break; }
+            } else {
+                if (sz != 1) throw std::runtime_error("JPEG: bad refinement code");
+                value = br.bit() ? p1 : m1;
+            }
+            for (; k <= se; k++) {
+                if (blk[k] != 0) refine(blk[k]);
+                else if (--r < 0) break;
+            }
+            if (value) { if (k > se) throw std::runtime_error("JPEG: bad refinement run"); blk[k] = (int16_t)value; }
+        }
+    }
+    if (eobrun > 0) {
+        for (; k <= se; k++) if (blk[k] != 0) refine(blk[k]);
+        eobrun--;
+    }
+}
 } // namespace
 
 Image decode_jpeg(const uint8_t* d, size_t size)
 {
     if (size < 4 || d[0] != 0xFF || d[1] != 0xD8) throw std::runtime_error("JPEG: bad signature");
     uint16_t qt[4][64] = {}; JpegHuff hdc[4], hac[4];
-    struct Comp { int id = 0, h = 1, v = 1, tq = 0, td = 0, ta = 0, pred = 0; size_t w = 0, hgt = 0; std::vector<uint8_t> px; } comp[3];
+    JpegComp comp[3];
     int ncomp = 0, W = 0, H = 0, hmax = 1, vmax = 1, restart = 0;
+    bool progressive = false, any_scan = false;
+    size_t mcux = 0, mcuy = 0;
     size_t i = 2;
     for (;;) {
-        if (i + 4 > size || d[i] != 0xFF) throw std::runtime_error("JPEG: marker expected");
+        if (i + 2 <= size && d[i] == 0xFF && d[i + 1] == 0xD9) break;                         // EOI
+        if (i + 4 > size) { if (any_scan) break; throw std::runtime_error("JPEG: truncated"); }  // a missing EOI is tolerated after a scan
+        if (d[i] != 0xFF) { if (any_scan) { i++; continue; } throw std::runtime_error("JPEG: marker expected"); }
         const int m = d[i + 1];
-        if (m == 0xFF) { i++; continue; }
+        if (m == 0xFF || m == 0x00 || (m >= 0xD0 && m <= 0xD7)) { i += (m == 0xFF) ? 1 : 2; continue; }   // fill bytes, leftovers of a scan
         const size_t len = ((size_t)d[i + 2] << 8) | d[i + 3];
         if (len < 2 || i + 2 + len > size) throw std::runtime_error("JPEG: truncated segment");
         const uint8_t* s = d + i + 4; const size_t n = len - 2;
+        i += 2 + len;
         if (m == 0xDB) {
             for (size_t k = 0; k < n;) {
                 const int pq = s[k] >> 4, tq = s[k] & 15; k++;
                 if (tq > 3 || k + (pq ? 128u : 64u) > n) throw std::runtime_error("JPEG: bad DQT");
                 for (int z = 0; z < 64; z++) { qt[tq][z] = pq ? (uint16_t)((s[k] << 8) | s[k + 1]) : s[k]; k += pq ? 2 : 1; }
             }
-        } else if (m == 0xC0 || m == 0xC1) {
+        } else if (m == 0xC0 || m == 0xC1 || m == 0xC2) {
+            if (W) throw std::runtime_error("JPEG: more than one frame");
             if (n < 6 || s[0] != 8) throw std::runtime_error("JPEG: only 8-bit samples");
+            progressive = m == 0xC2;
             H = (s[1] << 8) | s[2]; W = (s[3] << 8) | s[4]; ncomp = s[5];
             if ((ncomp != 1 && ncomp != 3) || n < 6 + 3 * (size_t)ncomp || W == 0 || H == 0) throw std::runtime_error("JPEG: unsupported frame");
             for (int k = 0; k < ncomp; k++) {
@@ -615,8 +703,15 @@ Image decode_jpeg(const uint8_t* d, size_t size)
                 if (comp[k].h < 1 || comp[k].h > 4 || comp[k].v < 1 || comp[k].v > 4) throw std::runtime_error("JPEG: bad sampling factor");
                 hmax = comp[k].h > hmax ? comp[k].h : hmax; vmax = comp[k].v > vmax ? comp[k].v : vmax;
             }
-        } else if (m == 0xC2 || (m >= 0xC3 && m <= 0xCF && m != 0xC4 && m != 0xC8 && m != 0xCC)) {
-            throw std::runtime_error("JPEG: progressive / lossless / arithmetic coding is not supported");
+            mcux = ((size_t)W + 8 * hmax - 1) / (8 * hmax); mcuy = ((size_t)H + 8 * vmax - 1) / (8 * vmax);
+            for (int k = 0; k < ncomp; k++) {
+                JpegComp& c = comp[k];
+                c.w = mcux * 8 * c.h; c.hgt = mcuy * 8 * c.v; c.bstride = mcux * c.h;
+                c.bw = ((((size_t)W * c.h + hmax - 1) / hmax) + 7) / 8; c.bh = ((((size_t)H * c.v + vmax - 1) / vmax) + 7) / 8;
+                c.coef.assign(c.bstride * mcuy * c.v * 64, 0);
+            }
+        } else if (m >= 0xC3 && m <= 0xCF && m != 0xC4 && m != 0xC8 && m != 0xCC) {
+            throw std::runtime_error("JPEG: lossless / hierarchical / arithmetic coding is not supported");
         } else if (m == 0xC4) {
             for (size_t k = 0; k < n;) {
                 const int tc = s[k] >> 4, th = s[k] & 15; k++;
@@ -632,51 +727,86 @@ Image decode_jpeg(const uint8_t* d, size_t size)
             if (n < 2) throw std::runtime_error("JPEG: bad DRI");
             restart = (s[0] << 8) | s[1];
         } else if (m == 0xDA) {
-            if (!W || n < 1 || s[0] != ncomp || n < 1 + 2 * (size_t)ncomp) throw std::runtime_error("JPEG: unsupported scan");
-            for (int k = 0; k < ncomp; k++) {
+            if (!W || n < 1) throw std::runtime_error("JPEG: scan before frame");
+            const int ns = s[0];
+            if (ns < 1 || ns > ncomp || n < 4 + 2 * (size_t)ns) throw std::runtime_error("JPEG: unsupported scan");
+            int order[3];
+            for (int k = 0; k < ns; k++) {
                 int c = -1; for (int q = 0; q < ncomp; q++) if (comp[q].id == s[1 + 2 * k]) c = q;
                 if (c < 0) throw std::runtime_error("JPEG: scan component");
                 comp[c].td = s[2 + 2 * k] >> 4; comp[c].ta = s[2 + 2 * k] & 15;
-                if (comp[c].td > 3 || comp[c].ta > 3 || !hdc[comp[c].td].set || !hac[comp[c].ta].set) throw std::runtime_error("JPEG: missing Huffman table");
+                if (comp[c].td > 3 || comp[c].ta > 3) throw std::runtime_error("JPEG: bad table selector");
+                order[k] = c;
             }
-            i += 2 + len;
-            break;
-        }
-        i += 2 + len;
-    }
-    const size_t mcux = ((size_t)W + 8 * hmax - 1) / (8 * hmax), mcuy = ((size_t)H + 8 * vmax - 1) / (8 * vmax);
-    for (int k = 0; k < ncomp; k++) { comp[k].w = mcux * 8 * comp[k].h; comp[k].hgt = mcuy * 8 * comp[k].v; comp[k].px.assign(comp[k].w * comp[k].hgt, 0); }
-    JpegBits br{d + i, d + size};
-    int until_restart = restart;
-    for (size_t my = 0; my < mcuy; my++)
-        for (size_t mx = 0; mx < mcux; mx++) {
-            if (restart && until_restart == 0) {
-                br.reset();
-                while (br.p + 1 < br.e && !(br.p[0] == 0xFF && br.p[1] >= 0xD0 && br.p[1] <= 0xD7)) br.p++;
-                if (br.p + 1 < br.e) br.p += 2;
-                for (int k = 0; k < ncomp; k++) comp[k].pred = 0;
-                until_restart = restart;
+            int ss = s[1 + 2 * ns], se = s[2 + 2 * ns], ah = s[3 + 2 * ns] >> 4, al = s[3 + 2 * ns] & 15;
+            if (!progressive) { ss = 0; se = 63; ah = 0; al = 0; }
+            else if (ss > se || se > 63 || (ss == 0 && se != 0) || (ss > 0 && ns != 1) || al > 13 || (ah != 0 && ah != al + 1))
+                throw std::runtime_error("JPEG: bad progressive scan parameters");
+            for (int k = 0; k < ns; k++) {
+                const JpegComp& c = comp[order[k]];
+                if ((ss == 0 && ah == 0 && !hdc[c.td].set) || ((se > 0) && !hac[c.ta].set)) throw std::runtime_error("JPEG: missing Huffman table");
             }
-            for (int k = 0; k < ncomp; k++)
-                for (int by = 0; by < comp[k].v; by++)
-                    for (int bx = 0; bx < comp[k].h; bx++) {
-                        float blk[64] = {};
-                        const int t = jpeg_decode(br, hdc[comp[k].td]);
-                        if (t > 11) throw std::runtime_error("JPEG: bad DC size");
-                        comp[k].pred += jpeg_extend(br.bits(t), t);
-                        blk[0] = (float)(comp[k].pred * (int)qt[comp[k].tq][0]);
-                        for (int z = 1; z < 64;) {
-                            const int rs = jpeg_decode(br, hac[comp[k].ta]), r = rs >> 4, sz = rs & 15;
-                            if (sz == 0) { if (r == 15) { z += 16; continue; } break; }
-                            z += r;
-                            if (z > 63) throw std::runtime_error("JPEG: bad AC run");
-                            blk[kZigzag[z]] = (float)(jpeg_extend(br.bits(sz), sz) * (int)qt[comp[k].tq][z]);
-                            z++;
-                        }
-                        jpeg_idct(blk, comp[k].px.data() + ((my * comp[k].v + by) * 8) * comp[k].w + (mx * comp[k].h + bx) * 8, comp[k].w);
+            JpegBits br{d + i, d + size};
+            for (int k = 0; k < ncomp; k++) comp[k].pred = 0;
+            int eobrun = 0, until_restart = restart;
+            auto maybe_restart = [&]() {
+                if (!restart) return;
+                if (until_restart == 0) {
+                    br.reset();
+                    while (br.p + 1 < br.e && !(br.p[0] == 0xFF && br.p[1] >= 0xD0 && br.p[1] <= 0xD7)) br.p++;
+                    if (br.p + 1 < br.e) br.p += 2;
+                    for (int k = 0; k < ncomp; k++) comp[k].pred = 0;
+                    eobrun = 0; until_restart = restart;
+                }
+                until_restart--;
+            };
+            bool truncated = false;
+            try {
+            if (ns == 1) {                                           // non-interleaved: the component's own block raster
+                JpegComp& c = comp[order[0]];
+                for (size_t by = 0; by < c.bh; by++)
+                    for (size_t bx = 0; bx < c.bw; bx++) {
+                        maybe_restart();
+                        jpeg_block(br, c, hdc, hac, &c.coef[(by * c.bstride + bx) * 64], progressive, ss, se, ah, al, eobrun);
                     }
-            if (restart) until_restart--;
+            } else {
+                for (size_t my = 0; my < mcuy; my++)
+                    for (size_t mx = 0; mx < mcux; mx++) {
+                        maybe_restart();
+                        for (int k = 0; k < ns; k++) {
+                            JpegComp& c = comp[order[k]];
+                            for (int by = 0; by < c.v; by++)
+                                for (int bx = 0; bx < c.h; bx++)
+                                    jpeg_block(br, c, hdc, hac, &c.coef[((my * c.v + by) * c.bstride + mx * c.h + bx) * 64], progressive, ss, se, ah, al, eobrun);
+                        }
+                    }
+            }
+            } catch (const std::runtime_error&) {
+                if (br.p + 2 < br.e) throw;                          // corrupt data in the middle of the file
+                truncated = true;                                    // the file ends inside this scan: keep what was decoded (a coarser image)
+            }
+            any_scan = true;
+            if (truncated) break;
+            // skip the entropy-coded data up to the next marker that is not a stuffed zero or a restart marker
+            i = (size_t)(br.p - d);
+            while (i + 1 < size && !(d[i] == 0xFF && d[i + 1] != 0x00 && d[i + 1] != 0xFF && !(d[i + 1] >= 0xD0 && d[i + 1] <= 0xD7))) i++;
         }
+    }
+    if (!W || !any_scan) throw std::runtime_error("JPEG: no image data");
+    // dequantise + inverse DCT
+    for (int k = 0; k < ncomp; k++) {
+        JpegComp& c = comp[k];
+        c.px.assign(c.w * c.hgt, 0);
+        const size_t rows = mcuy * c.v;
+        for (size_t by = 0; by < rows; by++)
+            for (size_t bx = 0; bx < c.bstride; bx++) {
+                const int16_t* q = &c.coef[(by * c.bstride + bx) * 64];
+                float blk[64];
+                for (int z = 0; z < 64; z++) blk[kZigzag[z]] = (float)((int)q[z] * (int)qt[c.tq][z]);
+                jpeg_idct(blk, c.px.data() + (by * 8) * c.w + bx * 8, c.w);
+            }
+    }
+    typedef JpegComp Comp;
     Image img; img.width = (uint32_t)W; img.height = (uint32_t)H; img.rgba.resize((size_t)W * H * 4);
     auto sample = [&](const Comp& c, int x, int y) -> float {        // bilinear at the full-resolution pixel centre
         if (c.h == hmax && c.v == vmax) return (float)c.px[(size_t)y * c.w + x];
@@ -764,7 +894,7 @@ std::vector<Image> load_glb_images(const std::string& path)
             } else if (const Json* uri = im.get("uri")) {                      // .gltf: sibling file or data: URI; a missing file leaves the entry empty
                 try { bytes = resolve_uri(path, uri->str); } catch (const std::exception&) { bytes.clear(); }
             }
-            // by signature, not by mimeType (optional for uri images); unsupported encodings (progressive JPEG, KTX, WebP) stay empty
+            // by signature, not by mimeType (optional for uri images); unsupported encodings (arithmetic-coded JPEG, KTX, WebP) stay empty
             try { if (!bytes.empty()) img = decode_image((const uint8_t*)bytes.data(), bytes.size()); } catch (const std::exception&) { img = Image(); }
             out.push_back(std::move(img));
         }

@@ -154,6 +154,38 @@ def test_baseline_jpeg_decoder_against_pil(tmp_path, mode, subsampling, size):
     assert got.shape == want.shape
     d = np.abs(got.astype(int) - want.astype(int))
     assert d.max() <= 6 and d.mean() < 0.6, (d.max(), d.mean())
-    img.save(path, quality=92, progressive=True, **kw)
+    # progressive (SOF2: spectral selection + successive approximation) of the same image and settings carries the same
+    # quantised coefficients in another order: the decode must be identical, byte for byte
+    for extra in ({"progressive": True}, {"progressive": True, "optimize": True}):
+        img.save(path, quality=92, **extra, **kw)
+        assert b"\xff\xc2" in open(path, "rb").read(1000)
+        assert np.array_equal(host.load_png(path), got)
+
+
+def test_progressive_jpeg_larger_image_and_restarts(tmp_path):
+    """A noisy 203x131 progressive file (long EOB runs, every scan type, correction bits) at two qualities, and a
+    baseline file with restart intervals: progressive == baseline byte for byte, both within a few levels of Pillow."""
+    PIL = pytest.importorskip("PIL.Image")
+    from ray_tracer_b200 import host
+    rng = np.random.default_rng(11)
+    w, h = 203, 131
+    yy, xx = np.mgrid[0:h, 0:w].astype(np.float64)
+    rgb = np.stack([127 + 100 * np.sin(xx / 5.0) * np.cos(yy / 11.0), 40 + xx, 200 - yy], -1) + rng.normal(0, 25, (h, w, 3))
+    img = PIL.fromarray(rgb.clip(0, 255).astype(np.uint8), "RGB")
+    for quality, sub in ((35, 2), (97, 0)):
+        pb, pp = str(tmp_path / "b.jpg"), str(tmp_path / "p.jpg")
+        img.save(pb, quality=quality, subsampling=sub)
+        img.save(pp, quality=quality, subsampling=sub, progressive=True)
+        base, prog = host.load_png(pb), host.load_png(pp)
+        assert np.array_equal(base, prog)
+        want = np.asarray(PIL.open(pp).convert("RGBA"))
+        d = np.abs(prog.astype(int) - want.astype(int))
+        assert d.max() <= 8 and d.mean() < 0.8, (d.max(), d.mean())
+    # truncated progressive file: later scans missing -> still decodes (coarser), no exception; garbage -> HostError
+    data = open(pp, "rb").read()
+    cut = str(tmp_path / "cut.jpg")
+    open(cut, "wb").write(data[: len(data) * 2 // 3])
+    assert host.load_png(cut).shape == prog.shape
+    open(cut, "wb").write(data[:2] + b"\x00" * 64)
     with pytest.raises(host.HostError):
-        host.load_png(path)
+        host.load_png(cut)
