@@ -54,6 +54,8 @@ def hostlib():
         L.rth_context_run_frames.argtypes = [vp, u32]
         L.rth_context_resize.argtypes = [vp, u32, u32]
         L.rth_context_set_scene.argtypes = [vp, C.c_int]
+        L.rth_context_set_shard.argtypes = [vp, u32, u32, u32, u32]
+        L.rth_context_combine.argtypes = [C.POINTER(vp), u32]
         L.rth_context_set_scene_arrays.argtypes = [vp, vp, vp, u32, vp, u32, vp, u32, vp, u32]
         L.rth_context_get_params.argtypes = [vp, vp]
         L.rth_context_set_params.argtypes = [vp, vp]
@@ -401,6 +403,17 @@ class Context:
 
     def sync(self):
         self._ck(self._L.rth_context_sync(self._h))
+
+    def set_shard(self, tile_rank=0, tile_world=1, frame_rank=0, frame_world=1):
+        """Multi-GPU in one process: this context renders only its share of the tiles / frames (rt_set_shard)."""
+        self._ck(self._L.rth_context_set_shard(self._h, tile_rank, tile_world, frame_rank, frame_world))
+
+    @staticmethod
+    def combine(shards):
+        """Fold the shard contexts' images into shards[0]'s with one kernel over peer memory (rt_combine_peers)."""
+        shards = list(shards)
+        arr = (C.c_void_p * len(shards))(*[s._h for s in shards])
+        shards[0]._ck(shards[0]._L.rth_context_combine(arr, len(shards)))
 
     def read_texture(self):
         p = self.params

@@ -102,6 +102,19 @@ void Context::run_frames(uint32_t n)
     check(rt_render_frames(ctx_, first, n), "rt_render_frames");
 }
 
+void Context::set_shard(uint32_t tile_rank, uint32_t tile_world, uint32_t frame_rank, uint32_t frame_world)
+{
+    check(rt_set_shard(ctx_, tile_rank, tile_world, frame_rank, frame_world), "rt_set_shard");
+}
+
+void Context::combine(const std::vector<Context*>& shards)
+{
+    if (shards.empty() || !shards[0]) throw std::runtime_error("Context::combine: no shards");
+    std::vector<rt_ctx*> h;
+    for (Context* c : shards) { if (!c) throw std::runtime_error("Context::combine: null shard"); h.push_back(c->ctx_); }
+    shards[0]->check(rt_combine_peers(h.data(), (uint32_t)h.size(), nullptr), "rt_combine_peers");
+}
+
 void Context::set_scene(int id)
 {
     set_scene(Scene::by_id(id, (float)params.width / (float)params.height));   // context.rs:261-278
@@ -270,6 +283,11 @@ int rth_context_resize(void* c, uint32_t w, uint32_t h) { RTH_TRY(((rtb::Context
 int rth_context_clear_accululation(void* c) { RTH_TRY(((rtb::Context*)c)->clear_accululation()); }
 int rth_context_set_scene(void* c, int id) { RTH_TRY(((rtb::Context*)c)->set_scene(id)); }
 int rth_context_sync(void* c) { RTH_TRY(((rtb::Context*)c)->sync()); }
+int rth_context_set_shard(void* c, uint32_t tr, uint32_t tw, uint32_t fr, uint32_t fw) { RTH_TRY(((rtb::Context*)c)->set_shard(tr, tw, fr, fw)); }
+int rth_context_combine(void* const* ctxs, uint32_t n)
+{
+    RTH_TRY({ std::vector<rtb::Context*> v; for (uint32_t k = 0; k < n; k++) v.push_back((rtb::Context*)ctxs[k]); rtb::Context::combine(v); });
+}
 int rth_context_set_scene_arrays(void* c, const float* cam9_fov_aspect_etc /* origin3, look_at3, up3, fov, aspect, near, far, aperture, focus */,
                                  const rt_sphere* sp, uint32_t ns, const rt_vertex* vs, uint32_t nv, const uint32_t* ix,
                                  uint32_t ni, const rt_mesh* ms, uint32_t nm)

@@ -152,6 +152,11 @@ public:
     // N redraws (update + render each), fused on the device when nothing changes between them
     void run_frames(uint32_t n);
     void sync();
+    // Several GPUs from one process (no reference counterpart): every shard context gets the same scene,
+    // inputs and update()/run_frames() calls and renders only its share of the tiles / frames (rt_set_shard);
+    // combine() folds the shards' images into shards[0]'s with one kernel over NVLink peer memory (rt_combine_peers).
+    void set_shard(uint32_t tile_rank, uint32_t tile_world, uint32_t frame_rank, uint32_t frame_world);
+    static void combine(const std::vector<Context*>& shards);
     std::vector<float> read_texture();              // RGBA32F, row 0 = bottom
     rt_ctx* handle() { return ctx_; }
 

@@ -106,3 +106,30 @@ def test_combine_errors(rtlib):
     rtlib.combine_peers([a])
     assert_bits_equal(a.read_accum(), img, "single context")
     a.close(); b.close()
+
+
+def test_context_mirror_shards_and_combine(rtlib):
+    """The C++ Context mirror driven as two tile shards (same scene, same update / run_frames calls on both) and
+    Context.combine: the image equals the single Context's bit for bit (context.rs frame logic unchanged per shard)."""
+    from ray_tracer_b200 import host
+    devs = _devices(2)
+    one = host.Context(0, W, H)
+    one.set(number_of_bounces=BOUNCES, skybox=1)
+    one.set_scene(2)                                        # room (context.rs:261-278)
+    one.run_frames(5); one.sync()
+    full = one.read_texture(); frames_one = int(one.params["frames"][0]); one.close()
+    shards = []
+    for r in range(2):
+        c = host.Context(devs[r], W, H)
+        c.set(number_of_bounces=BOUNCES, skybox=1)
+        c.set_scene(2)
+        c.set_shard(tile_rank=r, tile_world=2)
+        shards.append(c)
+    for c in shards:
+        c.run_frames(5)
+    host.Context.combine(shards)
+    got = shards[0].read_texture()
+    assert int(shards[0].params["frames"][0]) == frames_one
+    assert_bits_equal(got, full, "two Context shards combined")
+    for c in shards:
+        c.close()
