@@ -133,3 +133,20 @@ def test_context_mirror_shards_and_combine(rtlib):
     assert_bits_equal(got, full, "two Context shards combined")
     for c in shards:
         c.close()
+
+
+def test_headless_render_driver(rtlib, tmp_path):
+    """python -m ray_tracer_b200.render: a built-in scene on one context and as two tile shards gives the same PNG;
+    a model file with a two-position turntable writes one image per position."""
+    from ray_tracer_b200 import host, render
+    a, b = str(tmp_path / "one.png"), str(tmp_path / "two.png")
+    render.main(["--scene", "room", "--size", str(W), str(H), "--frames", "3", "--sky", "--out", a])
+    render.main(["--scene", "room", "--size", str(W), str(H), "--frames", "3", "--sky", "--gpus", "2" if len(set(_devices(2))) == 2 else "1", "--out", b])
+    ia, ib = host.load_png(a), host.load_png(b)
+    assert ia.shape == (H, W, 4) and np.array_equal(ia, ib) and ia[..., :3].max() > 0
+    obj = tmp_path / "quad.obj"
+    obj.write_text("v -1 -1 0\nv 1 -1 0\nv 1 1 0\nv -1 1 0\nvn 0 0 1\nf 1//1 2//1 3//1\nf 1//1 3//1 4//1\n")
+    out = render.main(["--model", str(obj), "--size", "64", "48", "--frames", "2", "--turntable", "40", "--positions", "2",
+                       "--out", str(tmp_path / "t.png")])
+    imgs = [host.load_png(o["image"]) for o in out]
+    assert len(imgs) == 2 and imgs[0].shape == (48, 64, 4) and not np.array_equal(imgs[0], imgs[1])
