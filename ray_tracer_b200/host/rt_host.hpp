@@ -100,7 +100,7 @@ void load_model_uv(const std::string& path, std::vector<rt_vertex>& vertices, st
 void load_scene_glb(const std::string& path, std::vector<rt_vertex>& vertices, std::vector<uint32_t>& indices,
                     std::vector<rt_mesh>& meshes);
 struct Image { uint32_t width = 0, height = 0; std::vector<uint8_t> rgba; };
-Image load_png(const std::string& path);                            // 8/16-bit grey, grey+alpha, RGB, RGBA, palette; no interlace
+Image load_png(const std::string& path);                            // grey (1-16 bit), grey+alpha, RGB, RGBA, palette (1-8 bit); Adam7 interlace
 Image decode_png(const uint8_t* data, size_t size);
 Image decode_jpeg(const uint8_t* data, size_t size);                // sequential and progressive DCT JPEG (8 bit, Huffman); arithmetic / lossless files throw
 Image decode_image(const uint8_t* data, size_t size);               // PNG or JPEG by signature

@@ -509,34 +509,59 @@ Image decode_png(const uint8_t* d, size_t size)
         off += 12 + (size_t)len;
     }
     if (!W || !H || W > 32768 || H > 32768) throw std::runtime_error("PNG: missing or absurd IHDR");
-    if (interlace) throw std::runtime_error("PNG: interlaced images are not supported");
+    if (interlace > 1) throw std::runtime_error("PNG: unknown interlace method");
     int ch = ctype == 0 ? 1 : ctype == 2 ? 3 : ctype == 3 ? 1 : ctype == 4 ? 2 : ctype == 6 ? 4 : 0;
-    if (!ch || !(depth == 8 || (depth == 16 && ctype != 3))) throw std::runtime_error("PNG: unsupported colour type / bit depth");
-    const size_t bpp = (size_t)ch * depth / 8, stride = (size_t)W * bpp;
-    std::vector<uint8_t> raw((stride + 1) * H);
+    const bool small_ok = (ctype == 0 || ctype == 3) && (depth == 1 || depth == 2 || depth == 4);
+    if (!ch || !(depth == 8 || (depth == 16 && ctype != 3) || small_ok)) throw std::runtime_error("PNG: unsupported colour type / bit depth");
+    const size_t bits = (size_t)ch * depth, bpp = bits >= 8 ? bits / 8 : 1;          // filter distance in bytes
+    // one pass, or the seven passes of Adam7: (x0, y0, dx, dy)
+    static const int adam7[7][4] = {{0, 0, 8, 8}, {4, 0, 8, 8}, {0, 4, 4, 8}, {2, 0, 4, 4}, {0, 2, 2, 4}, {1, 0, 2, 2}, {0, 1, 1, 2}};
+    static const int whole[1][4] = {{0, 0, 1, 1}};
+    const int (*pass)[4] = interlace ? adam7 : whole;
+    const int n_pass = interlace ? 7 : 1;
+    size_t raw_size = 0;
+    for (int k = 0; k < n_pass; k++) {
+        if ((uint32_t)pass[k][0] >= W || (uint32_t)pass[k][1] >= H) continue;
+        const size_t pw = (W - pass[k][0] + pass[k][2] - 1) / pass[k][2], ph = (H - pass[k][1] + pass[k][3] - 1) / pass[k][3];
+        raw_size += ph * ((pw * bits + 7) / 8 + 1);
+    }
+    std::vector<uint8_t> raw(raw_size);
     uLongf out_len = (uLongf)raw.size();
     if (uncompress(raw.data(), &out_len, idat.data(), (uLong)idat.size()) != Z_OK || out_len != raw.size()) throw std::runtime_error("PNG: inflate failed");
-    std::vector<uint8_t> prev(stride, 0), cur(stride);
     Image img; img.width = W; img.height = H; img.rgba.resize((size_t)W * H * 4);
-    for (uint32_t y = 0; y < H; y++) {
-        const uint8_t* row = &raw[(stride + 1) * y];
-        const int f = row[0];
-        if (f > 4) throw std::runtime_error("PNG: bad filter type");
-        for (size_t i = 0; i < stride; i++) {
-            int a = i >= bpp ? cur[i - bpp] : 0, b = prev[i], c = i >= bpp ? prev[i - bpp] : 0, x = row[1 + i];
-            cur[i] = (uint8_t)(f == 0 ? x : f == 1 ? x + a : f == 2 ? x + b : f == 3 ? x + ((a + b) >> 1) : x + paeth(a, b, c));
+    const size_t st = depth >= 8 ? depth / 8 : 0;                                    // 16-bit samples: keep the high byte
+    const int grey_scale = depth < 8 ? 255 / ((1 << depth) - 1) : 1;
+    size_t pos = 0;
+    for (int k = 0; k < n_pass; k++) {
+        if ((uint32_t)pass[k][0] >= W || (uint32_t)pass[k][1] >= H) continue;
+        const size_t pw = (W - pass[k][0] + pass[k][2] - 1) / pass[k][2], ph = (H - pass[k][1] + pass[k][3] - 1) / pass[k][3];
+        const size_t stride = (pw * bits + 7) / 8;
+        std::vector<uint8_t> prev(stride, 0), cur(stride);
+        for (size_t py = 0; py < ph; py++) {
+            const uint8_t* row = &raw[pos]; pos += stride + 1;
+            const int f = row[0];
+            if (f > 4) throw std::runtime_error("PNG: bad filter type");
+            for (size_t i = 0; i < stride; i++) {
+                int a = i >= bpp ? cur[i - bpp] : 0, b = prev[i], c = i >= bpp ? prev[i - bpp] : 0, x = row[1 + i];
+                cur[i] = (uint8_t)(f == 0 ? x : f == 1 ? x + a : f == 2 ? x + b : f == 3 ? x + ((a + b) >> 1) : x + paeth(a, b, c));
+            }
+            const size_t y = pass[k][1] + py * pass[k][3];
+            for (size_t px = 0; px < pw; px++) {
+                const size_t xx = pass[k][0] + px * pass[k][2];
+                uint8_t* o = &img.rgba[(y * W + xx) * 4];
+                uint8_t small = 0;
+                const uint8_t* sp = &cur[0];
+                if (depth < 8) { const size_t bit = px * depth; small = (uint8_t)((cur[bit >> 3] >> (8 - depth - (bit & 7))) & ((1 << depth) - 1)); }
+                else sp = &cur[px * bpp];
+                if (ctype == 0) { o[0] = o[1] = o[2] = depth < 8 ? (uint8_t)(small * grey_scale) : sp[0]; o[3] = 255; }
+                else if (ctype == 2) { o[0] = sp[0]; o[1] = sp[st]; o[2] = sp[2 * st]; o[3] = 255; }
+                else if (ctype == 3) { size_t q = depth < 8 ? small : sp[0]; if (3 * q + 2 >= plte.size()) throw std::runtime_error("PNG: palette index out of range");
+                                       o[0] = plte[3 * q]; o[1] = plte[3 * q + 1]; o[2] = plte[3 * q + 2]; o[3] = q < trns.size() ? trns[q] : 255; }
+                else if (ctype == 4) { o[0] = o[1] = o[2] = sp[0]; o[3] = sp[st]; }
+                else { o[0] = sp[0]; o[1] = sp[st]; o[2] = sp[2 * st]; o[3] = sp[3 * st]; }
+            }
+            prev.swap(cur);
         }
-        for (uint32_t xx = 0; xx < W; xx++) {
-            const uint8_t* s = &cur[xx * bpp]; const size_t st = depth / 8;      // 16-bit samples: keep the high byte
-            uint8_t* o = &img.rgba[((size_t)y * W + xx) * 4];
-            if (ctype == 0) { o[0] = o[1] = o[2] = s[0]; o[3] = 255; }
-            else if (ctype == 2) { o[0] = s[0]; o[1] = s[st]; o[2] = s[2 * st]; o[3] = 255; }
-            else if (ctype == 3) { size_t k = s[0]; if (3 * k + 2 >= plte.size()) throw std::runtime_error("PNG: palette index out of range");
-                                   o[0] = plte[3 * k]; o[1] = plte[3 * k + 1]; o[2] = plte[3 * k + 2]; o[3] = k < trns.size() ? trns[k] : 255; }
-            else if (ctype == 4) { o[0] = o[1] = o[2] = s[0]; o[3] = s[st]; }
-            else { o[0] = s[0]; o[1] = s[st]; o[2] = s[2 * st]; o[3] = s[3 * st]; }
-        }
-        prev.swap(cur);
     }
     return img;
 }

@@ -189,3 +189,68 @@ def test_progressive_jpeg_larger_image_and_restarts(tmp_path):
     open(cut, "wb").write(data[:2] + b"\x00" * 64)
     with pytest.raises(host.HostError):
         host.load_png(cut)
+
+
+def _png_chunk(tag, body):
+    import struct, zlib
+    return struct.pack(">I", len(body)) + tag + body + struct.pack(">I", zlib.crc32(tag + body) & 0xFFFFFFFF)
+
+
+def _adam7_png(img, ctype, depth, palette=None):
+    """Encode (H, W[, C]) uint8/uint16 samples as an Adam7-interlaced PNG (filter 0 on every row)."""
+    import struct, zlib
+    h, w = img.shape[:2]
+    raw = b""
+    for x0, y0, dx, dy in ((0, 0, 8, 8), (4, 0, 8, 8), (0, 4, 4, 8), (2, 0, 4, 4), (0, 2, 2, 4), (1, 0, 2, 2), (0, 1, 1, 2)):
+        sub = img[y0::dy, x0::dx]
+        if sub.size == 0:
+            continue
+        for row in sub:
+            if depth == 16:
+                body = row.astype(">u2").tobytes()
+            elif depth == 8:
+                body = row.astype(np.uint8).tobytes()
+            else:                                        # pack `depth`-bit samples, most significant bits first
+                bits = np.unpackbits(row.astype(np.uint8).reshape(-1, 1), axis=1)[:, 8 - depth:].reshape(-1)
+                body = np.packbits(bits).tobytes()
+            raw += b"\x00" + body
+    out = b"\x89PNG\r\n\x1a\n" + _png_chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, depth, ctype, 0, 0, 1))
+    if palette is not None:
+        out += _png_chunk(b"PLTE", palette.astype(np.uint8).tobytes())
+    return out + _png_chunk(b"IDAT", zlib.compress(raw)) + _png_chunk(b"IEND", b"")
+
+
+def test_png_interlace_and_small_bit_depths(tmp_path):
+    """Adam7-interlaced files (hand-encoded: Pillow cannot write them; read back by Pillow as a cross-check) and 1 / 2 / 4-bit
+    grey and palette files, sizes that leave some passes empty."""
+    PIL = pytest.importorskip("PIL.Image")
+    from ray_tracer_b200 import host
+    rng = np.random.default_rng(21)
+    p = str(tmp_path / "i.png")
+    for (h, w) in ((13, 21), (1, 1), (2, 3), (8, 8), (5, 1)):
+        rgba = rng.integers(0, 256, (h, w, 4), dtype=np.uint8)
+        open(p, "wb").write(_adam7_png(rgba, 6, 8))
+        assert np.array_equal(host.load_png(p), rgba)
+        assert np.array_equal(np.asarray(PIL.open(p).convert("RGBA")), rgba)
+        rgb16 = rng.integers(0, 65536, (h, w, 3), dtype=np.uint16)
+        open(p, "wb").write(_adam7_png(rgb16, 2, 16))
+        got = host.load_png(p)
+        assert np.array_equal(got[..., :3], (rgb16 >> 8).astype(np.uint8)) and (got[..., 3] == 255).all()
+        for depth in (1, 2, 4):
+            g = rng.integers(0, 1 << depth, (h, w), dtype=np.uint8)
+            open(p, "wb").write(_adam7_png(g, 0, depth))
+            want = (g * (255 // ((1 << depth) - 1))).astype(np.uint8)
+            got = host.load_png(p)
+            assert np.array_equal(got[..., 0], want) and np.array_equal(got[..., 2], want)
+            assert np.array_equal(np.asarray(PIL.open(p).convert("L")), want)
+            pal = rng.integers(0, 256, (1 << depth, 3), dtype=np.uint8)
+            open(p, "wb").write(_adam7_png(g, 3, depth, pal))
+            assert np.array_equal(host.load_png(p)[..., :3], pal[g])
+    # non-interlaced small depths written by Pillow
+    bw = PIL.fromarray((rng.integers(0, 2, (9, 19)) * 255).astype(np.uint8), "L").convert("1")
+    bw.save(p)
+    assert np.array_equal(host.load_png(p)[..., 0], np.asarray(bw.convert("L")))
+    pim = PIL.fromarray(rng.integers(0, 4, (7, 11), dtype=np.uint8), "P")
+    pim.putpalette([int(v) for v in rng.integers(0, 256, 12)])
+    pim.save(p, bits=2)
+    assert np.array_equal(host.load_png(p), np.asarray(PIL.open(p).convert("RGBA")))
