@@ -97,6 +97,8 @@ void load_model_uv(const std::string& path, std::vector<rt_vertex>& vertices, st
 // (matrix or T*R*S, parents first) to positions and normals, one Mesh record per primitive INSTANCE at
 // pos = 0, colour / smoothness / emission from the material (baseColorFactor, 1 - roughnessFactor,
 // emissiveFactor), texture handles = image index + 1 (the order of load_glb_images), UVs kept.
+// An .obj path imports the file's .mtl instead: one Mesh per `usemtl` run (Kd, Ke, Ns -> colour, emission, smoothness;
+// map_Kd / map_Bump -> texture handles in the order load_glb_images returns the images).
 void load_scene_glb(const std::string& path, std::vector<rt_vertex>& vertices, std::vector<uint32_t>& indices,
                     std::vector<rt_mesh>& meshes);
 struct Image { uint32_t width = 0, height = 0; std::vector<uint8_t> rgba; };

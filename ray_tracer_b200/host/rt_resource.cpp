@@ -236,13 +236,44 @@ void load_model(const std::string& path, std::vector<rt_vertex>& v, std::vector<
     else throw std::runtime_error("Unsupported model format");     // resource.rs:43
 }
 
-void load_model_obj(const std::string& path, std::vector<rt_vertex>& vertices, std::vector<uint32_t>& indices, std::vector<rt_mesh>& meshes)
+namespace {
+// Wavefront MTL, the statements the scene import uses (extension: upstream never opens the .mtl, resource.rs:57-69
+// drops tobj's materials): Kd, Ke, Ns, map_Kd, map_Bump / bump / norm.
+struct ObjMaterial { std::string name; float kd[3] = {0.8f, 0.8f, 0.8f}, ke[3] = {0, 0, 0}, ns = 0.0f; std::string map_kd, map_bump; };
+std::vector<ObjMaterial> parse_mtl(const std::string& path)
+{
+    std::vector<ObjMaterial> out;
+    std::istringstream in(read_file(path, false));
+    std::string line;
+    while (std::getline(in, line)) {
+        while (!line.empty() && (line.back() == '\r' || line.back() == ' ')) line.pop_back();
+        std::istringstream ls(line);
+        std::string tag;
+        if (!(ls >> tag) || tag[0] == '#') continue;
+        if (tag == "newmtl") { out.emplace_back(); ls >> out.back().name; continue; }
+        if (out.empty()) continue;
+        ObjMaterial& m = out.back();
+        if (tag == "Kd") ls >> m.kd[0] >> m.kd[1] >> m.kd[2];
+        else if (tag == "Ke") ls >> m.ke[0] >> m.ke[1] >> m.ke[2];
+        else if (tag == "Ns") ls >> m.ns;
+        else if (tag == "map_Kd" || tag == "map_Bump" || tag == "map_bump" || tag == "bump" || tag == "norm") {
+            std::string tok, last;                                    // options (-bm 1.0, -s ...) come first, the file name last
+            while (ls >> tok) last = tok;
+            (tag == "map_Kd" ? m.map_kd : m.map_bump) = last;
+        }
+    }
+    return out;
+}
+struct ObjScene { std::vector<ObjMaterial> materials; std::vector<std::string> images; };   // images in handle order (handle = index + 1)
+
+void load_obj(const std::string& path, std::vector<rt_vertex>& vertices, std::vector<uint32_t>& indices, std::vector<rt_mesh>& meshes, ObjScene* scene)
 {
     std::istringstream in(read_file(path, false));
     std::vector<float> pos, nrm, tex;
-    struct Model { std::map<std::tuple<long, long, long>, uint32_t> map; std::vector<rt_vertex> v; std::vector<uint32_t> idx; };
+    struct Model { std::map<std::tuple<long, long, long>, uint32_t> map; std::vector<rt_vertex> v; std::vector<uint32_t> idx; std::string mtl; };
     std::vector<Model> models;
     std::unique_ptr<Model> cur;
+    std::string cur_mtl;
     auto flush = [&]() { if (cur && !cur->idx.empty()) models.push_back(std::move(*cur)); cur.reset(); };
     auto fix = [](long i, size_t n) -> long { return i > 0 ? i - 1 : (long)n + i; };
     std::string line;
@@ -253,9 +284,11 @@ void load_model_obj(const std::string& path, std::vector<rt_vertex>& vertices, s
         if (tag == "v") { float x, y, z; ls >> x >> y >> z; pos.insert(pos.end(), {x, y, z}); }
         else if (tag == "vn") { float x, y, z; ls >> x >> y >> z; nrm.insert(nrm.end(), {x, y, z}); }
         else if (tag == "vt") { float x = 0, y = 0; ls >> x >> y; tex.insert(tex.end(), {x, y}); }
-        else if (tag == "o" || tag == "g") { flush(); cur.reset(new Model()); }
+        else if (tag == "o" || tag == "g") { flush(); cur.reset(new Model()); cur->mtl = cur_mtl; }
+        else if (scene && tag == "mtllib") { std::string f; ls >> f; for (ObjMaterial& m : parse_mtl(sibling(path, f))) scene->materials.push_back(std::move(m)); }
+        else if (scene && tag == "usemtl") { ls >> cur_mtl; if (cur && !cur->idx.empty()) { flush(); } if (!cur) cur.reset(new Model()); cur->mtl = cur_mtl; }
         else if (tag == "f") {
-            if (!cur) cur.reset(new Model());
+            if (!cur) { cur.reset(new Model()); cur->mtl = cur_mtl; }
             std::vector<uint32_t> corner;
             std::string c;
             while (ls >> c) {
@@ -290,11 +323,37 @@ void load_model_obj(const std::string& path, std::vector<rt_vertex>& vertices, s
         }
     }
     flush();
+    auto image_handle = [&](const std::string& file) -> uint32_t {
+        if (file.empty()) return 0u;
+        for (size_t k = 0; k < scene->images.size(); k++) if (scene->images[k] == file) return (uint32_t)k + 1u;
+        scene->images.push_back(file);
+        return (uint32_t)scene->images.size();
+    };
     for (auto& mdl : models) {
-        meshes.push_back(loader_mesh((uint32_t)meshes.size(), (uint32_t)mdl.idx.size(), (uint32_t)indices.size(), (uint32_t)vertices.size()));
+        rt_mesh m = loader_mesh((uint32_t)meshes.size(), (uint32_t)mdl.idx.size(), (uint32_t)indices.size(), (uint32_t)vertices.size());
+        if (scene) {                                                 // material import: in place (pos 0), colours and textures from the .mtl
+            m.pos[0] = 0.0f;
+            const ObjMaterial* mat = nullptr;
+            for (const ObjMaterial& c : scene->materials) if (c.name == mdl.mtl) mat = &c;
+            if (mat) {
+                m.color[0] = mat->kd[0]; m.color[1] = mat->kd[1]; m.color[2] = mat->kd[2]; m.color[3] = 1.0f;
+                const float e = std::max(mat->ke[0], std::max(mat->ke[1], mat->ke[2]));
+                if (e > 0.0f) { m.emission_color[0] = mat->ke[0]; m.emission_color[1] = mat->ke[1]; m.emission_color[2] = mat->ke[2]; m.emission_color[3] = 1.0f; m.emission_strength = 1.0f; }
+                const float sm = std::sqrt(std::max(mat->ns, 0.0f) / 900.0f);          // Blender writes Ns = 900 (1 - roughness)^2
+                m.specular = sm > 1.0f ? 1.0f : sm;
+                m.diffuse_tex = image_handle(mat->map_kd); m.normal_tex = image_handle(mat->map_bump);
+            }
+        }
+        meshes.push_back(m);
         vertices.insert(vertices.end(), mdl.v.begin(), mdl.v.end());
         indices.insert(indices.end(), mdl.idx.begin(), mdl.idx.end());
     }
+}
+} // namespace
+
+void load_model_obj(const std::string& path, std::vector<rt_vertex>& vertices, std::vector<uint32_t>& indices, std::vector<rt_mesh>& meshes)
+{
+    load_obj(path, vertices, indices, meshes, nullptr);
 }
 
 namespace {
@@ -439,6 +498,7 @@ void visit_node(const Json& g, const std::vector<std::string>& buffers, size_t n
 void load_scene_glb(const std::string& path, std::vector<rt_vertex>& vertices, std::vector<uint32_t>& indices, std::vector<rt_mesh>& meshes)
 {
     struct Guard { Guard() { g_keep_uv = true; } ~Guard() { g_keep_uv = false; } } guard;
+    if (ends_with(path, ".obj")) { ObjScene sc; load_obj(path, vertices, indices, meshes, &sc); return; }   // OBJ + MTL material import
     Json g; std::vector<std::string> buffers;
     if (ends_with(path, ".gltf")) {                                // JSON file + external buffers or base64 data: URIs
         g = parse_json(read_file(path, false));
@@ -899,6 +959,14 @@ void write_png(const std::string& path, const uint8_t* rgba, uint32_t W, uint32_
 
 std::vector<Image> load_glb_images(const std::string& path)
 {
+    if (ends_with(path, ".obj")) {                                 // the map_Kd / map_Bump files of the .mtl, in handle order
+        struct Guard { Guard() { g_keep_uv = true; } ~Guard() { g_keep_uv = false; } } guard;
+        ObjScene sc; std::vector<rt_vertex> v; std::vector<uint32_t> i; std::vector<rt_mesh> m;
+        load_obj(path, v, i, m, &sc);
+        std::vector<Image> out;
+        for (const std::string& f : sc.images) { Image img; try { img = load_image(sibling(path, f)); } catch (const std::exception&) { img = Image(); } out.push_back(std::move(img)); }
+        return out;
+    }
     Json g; std::vector<std::string> buffers;
     const bool text = ends_with(path, ".gltf");
     if (text) {

@@ -223,3 +223,40 @@ def test_glb_with_embedded_textures_renders_like_the_oracle(tmp_path, rtlib, ora
     ref = oracle.render(sc, w, h, 2, 4, 1, 1, 0, textures=textures)
     from util import assert_bits_equal
     assert_bits_equal(img, ref, "glb scene graph with embedded textures")
+
+
+def test_obj_material_import(tmp_path):
+    """load_scene_glb on an .obj (extension): `mtllib` / `usemtl` split the file into one Mesh per material run, with
+    Kd / Ke / Ns and the map_Kd / map_Bump images as texture handles; upstream's own load_model on the same file keeps
+    its fixed colour and placement (resource.rs:73-85)."""
+    import io
+    from PIL import Image
+    from ray_tracer_b200 import host
+    rng = np.random.default_rng(9)
+    ta = rng.integers(0, 256, (4, 4, 3), dtype=np.uint8)
+    tb = rng.integers(0, 256, (2, 2, 3), dtype=np.uint8)
+    Image.fromarray(ta, "RGB").save(tmp_path / "a.png")
+    Image.fromarray(tb, "RGB").save(tmp_path / "n.png")
+    (tmp_path / "m.mtl").write_text(
+        "newmtl red\nNs 225.0\nKd 0.9 0.1 0.2\nKe 0 0 0\nmap_Kd a.png\nmap_Bump -bm 1.0 n.png\n"
+        "newmtl lamp\nKd 1 1 1\nKe 2.0 1.0 0.5\nNs 0\n")
+    (tmp_path / "s.obj").write_text(
+        "mtllib m.mtl\no quad\nv 0 0 0\nv 1 0 0\nv 1 1 0\nv 0 1 0\nvt 0 0\nvt 1 0\nvt 1 1\nvt 0 1\nvn 0 0 1\n"
+        "usemtl red\nf 1/1/1 2/2/1 3/3/1\nusemtl lamp\nf 1/1/1 3/3/1 4/4/1\nusemtl missing\nf 2/2/1 3/3/1 4/4/1\n")
+    path = str(tmp_path / "s.obj")
+    vs, ix, ms = host.load_scene_glb(path)
+    assert len(ms) == 3 and [int(t) for t in ms["triangles"]] == [1, 1, 1] and len(ix) == 9
+    assert np.all(ms["pos"] == 0)
+    assert np.allclose(ms["color"][0], [0.9, 0.1, 0.2, 1.0]) and np.isclose(ms["specular"][0], 0.5)      # sqrt(225 / 900)
+    assert ms["diffuse_tex"][0] == 1 and ms["normal_tex"][0] == 2
+    assert np.allclose(ms["emission_color"][1], [2.0, 1.0, 0.5, 1.0]) and ms["emission_strength"][1] == 1.0 and ms["specular"][1] == 0.0
+    assert ms["diffuse_tex"][1] == 0 and ms["normal_tex"][1] == 0
+    assert np.allclose(ms["color"][2], [0.2, 0.2, 1.0, 1.0]) and ms["specular"][2] == 0.5               # unknown material: the loader's default record
+    first = vs[int(ms["offset"][0]):int(ms["offset"][1])]
+    assert np.allclose(first["tu"], [0, 1, 1]) and np.allclose(first["tv"], [1, 1, 0])                    # (u, 1 - v)
+    images = host.load_glb_images(path)
+    assert len(images) == 2 and np.array_equal(images[0][..., :3], ta) and np.array_equal(images[1][..., :3], tb)
+    # upstream's loader on the same file: one model (usemtl is not a split for this mirror), fixed colour, no UVs
+    v0, i0, m0 = host.load_model(path)
+    assert len(m0) == 1 and int(m0["triangles"][0]) == 3 and np.allclose(m0["color"][0], [0.2, 0.2, 1.0, 1.0])
+    assert np.all(v0["tu"] == 0) and np.all(v0["tv"] == 0)
