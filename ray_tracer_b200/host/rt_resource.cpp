@@ -88,7 +88,11 @@ struct Json {
     std::vector<Json> arr; std::vector<std::pair<std::string, Json>> obj;
     const Json* get(const char* k) const { for (auto& p : obj) if (p.first == k) return &p.second; return nullptr; }
     const Json& at(const char* k) const { const Json* j = get(k); if (!j) throw std::runtime_error(std::string("glTF: missing key ") + k); return *j; }
-    long integer(const char* k, long dflt) const { const Json* j = get(k); return j ? (long)j->num : dflt; }
+    // numbers as integers, saturating (a cast of an out-of-range double is undefined behaviour): NaN -> 0, clamp to +-2^62
+    static long long to_ll(double v) { if (!(v == v)) return 0; if (v >= 4.6e18) return 1ll << 62; if (v <= -4.6e18) return -(1ll << 62); return (long long)v; }
+    long long integer(const char* k, long long dflt) const { const Json* j = get(k); return j ? to_ll(j->num) : dflt; }
+    // an array index: anything negative or absurd becomes SIZE_MAX, which every bounds test and .at() rejects
+    size_t index() const { const long long v = to_ll(num); return v < 0 ? (size_t)-1 : (size_t)v; }
 };
 
 struct JsonParser {
@@ -155,21 +159,28 @@ Json parse_json(const std::string& s) { JsonParser jp{s.data(), s.data() + s.siz
 // ---- glTF accessors --------------------------------------------------------------------
 struct Accessor { const unsigned char* base; size_t stride, count; int comp, ncomp; };
 
-Accessor accessor(const Json& g, const std::vector<std::string>& buffers, long k)
+Accessor accessor(const Json& g, const std::vector<std::string>& buffers, size_t k)
 {
-    const Json& a = g.at("accessors").arr.at((size_t)k);
-    const Json& bv = g.at("bufferViews").arr.at((size_t)a.integer("bufferView", 0));
+    const Json& a = g.at("accessors").arr.at(k);
+    const long long j_view = a.integer("bufferView", 0);
+    const Json& bv = g.at("bufferViews").arr.at(j_view < 0 ? (size_t)-1 : (size_t)j_view);
     int comp = (int)a.integer("componentType", 0);
     const std::string& type = a.at("type").str;
     int nc = type == "SCALAR" ? 1 : type == "VEC2" ? 2 : type == "VEC3" ? 3 : type == "VEC4" ? 4 : type == "MAT4" ? 16 : 0;
     size_t sz = (comp == 5120 || comp == 5121) ? 1 : (comp == 5122 || comp == 5123) ? 2 : (comp == 5125 || comp == 5126) ? 4 : 0;
     if (!nc || !sz) throw std::runtime_error("glTF: unsupported accessor type");
-    size_t stride = (size_t)bv.integer("byteStride", 0);
-    if (!stride) stride = sz * (size_t)nc;
-    size_t off = (size_t)bv.integer("byteOffset", 0) + (size_t)a.integer("byteOffset", 0);
-    size_t count = (size_t)a.integer("count", 0);
-    const std::string& buf = buffers.at((size_t)bv.integer("buffer", 0));
-    if (count && off + (count - 1) * stride + sz * (size_t)nc > buf.size()) throw std::runtime_error("glTF: accessor outside its buffer");
+    const long long j_stride = bv.integer("byteStride", 0), j_bo = bv.integer("byteOffset", 0), j_ao = a.integer("byteOffset", 0),
+                    j_count = a.integer("count", 0), j_buf = bv.integer("buffer", 0);
+    if (j_stride < 0 || j_bo < 0 || j_ao < 0 || j_count < 0 || j_buf < 0 || j_stride > (1 << 20)) throw std::runtime_error("glTF: negative or absurd accessor field");
+    const size_t elem = sz * (size_t)nc;
+    size_t stride = (size_t)j_stride;
+    if (!stride) stride = elem;
+    const size_t count = (size_t)j_count;
+    const std::string& buf = buffers.at((size_t)j_buf);
+    // overflow-safe: off <= size, elem <= size - off, (count - 1) * stride <= size - off - elem
+    if ((unsigned long long)j_bo > buf.size() || (unsigned long long)j_ao > buf.size() - (size_t)j_bo) throw std::runtime_error("glTF: accessor outside its buffer");
+    const size_t off = (size_t)j_bo + (size_t)j_ao;
+    if (count && (elem > buf.size() - off || (count - 1) > (buf.size() - off - elem) / stride)) throw std::runtime_error("glTF: accessor outside its buffer");
     return Accessor{(const unsigned char*)buf.data() + off, stride, count, comp, nc};
 }
 
@@ -179,11 +190,11 @@ void append_primitive(const Json& g, const std::vector<std::string>& buffers, co
     const Json& attrs = prim.at("attributes");
     const Json* jp = attrs.get("POSITION"); const Json* jn = attrs.get("NORMAL");
     if (!jp || !jn) throw std::runtime_error("glTF: primitive without POSITION/NORMAL (the reference unwraps both)");  // resource.rs:149-150
-    Accessor ap = accessor(g, buffers, (long)jp->num), an = accessor(g, buffers, (long)jn->num);
+    Accessor ap = accessor(g, buffers, jp->index()), an = accessor(g, buffers, jn->index());
     if (ap.comp != 5126 || an.comp != 5126 || ap.ncomp != 3 || an.ncomp != 3) throw std::runtime_error("glTF: POSITION/NORMAL must be f32 VEC3");
     std::vector<uint32_t> idx;
     if (const Json* ji = prim.get("indices")) {
-        Accessor ai = accessor(g, buffers, (long)ji->num);
+        Accessor ai = accessor(g, buffers, ji->index());
         idx.resize(ai.count);
         for (size_t r = 0; r < ai.count; r++) {
             const unsigned char* q = ai.base + r * ai.stride;
@@ -202,7 +213,7 @@ void append_primitive(const Json& g, const std::vector<std::string>& buffers, co
     Accessor at{nullptr, 0, 0, 0, 0};
     if (g_keep_uv)
         if (const Json* jt = attrs.get("TEXCOORD_0")) {
-            at = accessor(g, buffers, (long)jt->num);
+            at = accessor(g, buffers, jt->index());
             if (at.comp != 5126 || at.ncomp != 2) at.base = nullptr;     // only f32 VEC2 coordinates are kept
         }
     for (size_t r = 0; r < n; r++) {
@@ -429,14 +440,14 @@ void apply_material(const Json& g, const Json& prim, rt_mesh& m)
 {
     const Json* jmi = prim.get("material");
     const Json* mats = g.get("materials");
-    if (!jmi || !mats || (size_t)jmi->num >= mats->arr.size()) return;
-    const Json& mat = mats->arr[(size_t)jmi->num];
+    if (!jmi || !mats || jmi->index() >= mats->arr.size()) return;
+    const Json& mat = mats->arr[jmi->index()];
     auto image_handle = [&](const Json* texref) -> uint32_t {
         if (!texref) return 0u;
         const Json* ji = texref->get("index"); const Json* texs = g.get("textures");
-        if (!ji || !texs || (size_t)ji->num >= texs->arr.size()) return 0u;
-        const Json* src = texs->arr[(size_t)ji->num].get("source");
-        return src ? (uint32_t)src->num + 1u : 0u;
+        if (!ji || !texs || ji->index() >= texs->arr.size()) return 0u;
+        const Json* src = texs->arr[ji->index()].get("source");
+        return (src && src->index() < 0xffffffu) ? (uint32_t)src->index() + 1u : 0u;
     };
     if (const Json* pbr = mat.get("pbrMetallicRoughness")) {
         if (const Json* bc = pbr->get("baseColorFactor")) for (size_t k = 0; k < 4; k++) m.color[k] = num_or(bc, k, 1.0f);
@@ -466,7 +477,7 @@ void visit_node(const Json& g, const std::vector<std::string>& buffers, size_t n
         const float c10 = a[2] * a[9] - a[1] * a[10], c11 = a[0] * a[10] - a[2] * a[8], c12 = a[1] * a[8] - a[0] * a[9];
         const float c20 = a[1] * a[6] - a[2] * a[5], c21 = a[2] * a[4] - a[0] * a[6], c22 = a[0] * a[5] - a[1] * a[4];
         const float det = a[0] * c00 + a[1] * c01 + a[2] * c02;
-        for (const Json& prim : g.at("meshes").arr.at((size_t)jm->num).at("primitives").arr) {
+        for (const Json& prim : g.at("meshes").arr.at(jm->index()).at("primitives").arr) {
             const size_t v0 = vertices.size();
             append_primitive(g, buffers, prim, false, vertices, indices, meshes);
             rt_mesh& m = meshes.back();
@@ -491,7 +502,7 @@ void visit_node(const Json& g, const std::vector<std::string>& buffers, size_t n
         }
     }
     if (const Json* jc = node.get("children"))
-        for (const Json& c : jc->arr) visit_node(g, buffers, (size_t)c.num, world, depth + 1, vertices, indices, meshes);
+        for (const Json& c : jc->arr) visit_node(g, buffers, c.index(), world, depth + 1, vertices, indices, meshes);
 }
 } // namespace
 
@@ -513,10 +524,10 @@ void load_scene_glb(const std::string& path, std::vector<rt_vertex>& vertices, s
         return;
     }
     const Json* def = g.get("scene");
-    const size_t si = def ? (size_t)def->num : 0;
+    const size_t si = def ? def->index() : 0;
     if (si >= scenes->arr.size()) throw std::runtime_error("GLB: bad default scene");
     if (const Json* roots = scenes->arr[si].get("nodes"))
-        for (const Json& r : roots->arr) visit_node(g, buffers, (size_t)r.num, mat_identity(), 0, vertices, indices, meshes);
+        for (const Json& r : roots->arr) visit_node(g, buffers, r.index(), mat_identity(), 0, vertices, indices, meshes);
 }
 
 void load_model_gltf(const std::string& path, std::vector<rt_vertex>& vertices, std::vector<uint32_t>& indices, std::vector<rt_mesh>& meshes)
@@ -531,10 +542,10 @@ void load_model_gltf(const std::string& path, std::vector<rt_vertex>& vertices, 
     if (const Json* js = g.get("scenes"))
         for (const Json& sc : js->arr)
             for (const Json& ni : sc.at("nodes").arr) {
-                const Json& node = g.at("nodes").arr.at((size_t)ni.num);
+                const Json& node = g.at("nodes").arr.at(ni.index());
                 const Json* jm = node.get("mesh");
                 if (!jm) throw std::runtime_error("Failed to get mesh");   // resource.rs:142
-                for (const Json& prim : g.at("meshes").arr.at((size_t)jm->num).at("primitives").arr)
+                for (const Json& prim : g.at("meshes").arr.at(jm->index()).at("primitives").arr)
                     append_primitive(g, buffers, prim, true, vertices, indices, meshes);
             }
 }
@@ -980,9 +991,11 @@ std::vector<Image> load_glb_images(const std::string& path)
             Image img;
             std::string bytes;
             if (const Json* bv = im.get("bufferView")) {                       // embedded: a bufferView of one of the buffers
-                const Json& v = g.at("bufferViews").arr.at((size_t)bv->num);
-                const size_t bi = (size_t)v.integer("buffer", 0), off = (size_t)v.integer("byteOffset", 0), len = (size_t)v.integer("byteLength", 0);
-                if (bi >= buffers.size() || off + len > buffers[bi].size()) throw std::runtime_error("GLB: image outside its buffer");
+                const Json& v = g.at("bufferViews").arr.at(bv->index());
+                const long long jb = v.integer("buffer", 0), jo = v.integer("byteOffset", 0), jl = v.integer("byteLength", 0);
+                if (jb < 0 || jo < 0 || jl < 0 || (size_t)jb >= buffers.size() || (unsigned long long)jo > buffers[(size_t)jb].size() ||
+                    (unsigned long long)jl > buffers[(size_t)jb].size() - (size_t)jo) throw std::runtime_error("GLB: image outside its buffer");
+                const size_t bi = (size_t)jb, off = (size_t)jo, len = (size_t)jl;
                 bytes.assign(buffers[bi], off, len);
             } else if (const Json* uri = im.get("uri")) {                      // .gltf: sibling file or data: URI; a missing file leaves the entry empty
                 try { bytes = resolve_uri(path, uri->str); } catch (const std::exception&) { bytes.clear(); }

@@ -260,3 +260,46 @@ def test_obj_material_import(tmp_path):
     v0, i0, m0 = host.load_model(path)
     assert len(m0) == 1 and int(m0["triangles"][0]) == 3 and np.allclose(m0["color"][0], [0.2, 0.2, 1.0, 1.0])
     assert np.all(v0["tu"] == 0) and np.all(v0["tv"] == 0)
+
+
+def test_malformed_gltf_fields_are_rejected_not_followed(tmp_path, glb):
+    """Negative / absurd byteOffset, count, buffer, bufferView and accessor numbers (a negative byteOffset used to wrap the
+    bounds test around: found by fuzzing the loaders under AddressSanitizer) and a few hundred random byte mutations of the
+    file: every call returns or raises HostError."""
+    from ray_tracer_b200 import host
+    data = open(glb[0], "rb").read()
+    jl = struct.unpack("<I", data[12:16])[0]
+    base, blob = json.loads(data[20:20 + jl]), data[20 + jl + 8:]
+    (tmp_path / "g.bin").write_bytes(blob)
+    cases = [("bufferViews", 2, "byteOffset", -1), ("bufferViews", 0, "byteOffset", 2 ** 63), ("bufferViews", 1, "byteStride", -12),
+             ("bufferViews", 3, "buffer", 7), ("bufferViews", 3, "buffer", -1), ("accessors", 0, "count", 10 ** 12), ("accessors", 3, "count", -6),
+             ("accessors", 1, "bufferView", -3), ("accessors", 2, "byteOffset", 1e300), ("accessors", 0, "bufferView", 1e30)]
+    for arr, k, field, value in cases:
+        g = json.loads(json.dumps(base))
+        g["buffers"][0]["uri"] = "g.bin"
+        g[arr][k][field] = value
+        p = tmp_path / "bad.gltf"
+        p.write_text(json.dumps(g))
+        with pytest.raises(host.HostError):
+            host.load_scene_glb(str(p))
+    g = json.loads(json.dumps(base)); g["buffers"][0]["uri"] = "g.bin"
+    g["meshes"][0]["primitives"][0]["attributes"]["POSITION"] = -2
+    (tmp_path / "bad.gltf").write_text(json.dumps(g))
+    with pytest.raises(host.HostError):
+        host.load_scene_glb(str(tmp_path / "bad.gltf"))
+    rng = np.random.default_rng(17)
+    for it in range(300):
+        d = bytearray(data)
+        for _ in range(int(rng.integers(1, 5))):
+            q = int(rng.integers(12, len(d)))
+            if rng.integers(0, 2):
+                d[q] = int(rng.integers(0, 256))
+            else:
+                del d[q:q + int(rng.integers(1, 9))]
+        p = tmp_path / "mut.glb"
+        p.write_bytes(bytes(d))
+        for fn in (host.load_scene_glb, host.load_model, host.load_glb_images):
+            try:
+                fn(str(p))
+            except host.HostError:
+                pass
