@@ -14,7 +14,9 @@
  * path and cannot be executed in this environment, so this oracle is
  * pinned only by self-derived known answers (RNG stream, seed formula, camera uniform,
  * struct offsets, analytic intersections) => "parity unpinned" against the reference's
- * own GPU output, as DESIGN.md states.
+ * own GPU output, as DESIGN.md states.  Its own transcription is cross-checked by a second
+ * restatement of the same WGSL written independently in scalar Python
+ * (tests/test_oracle_restatement.py: equal bit for bit on balls / metal / room pixels).
  *
  * EXTENSION (no reference counterpart, SURVEY.md §8(a')): diffuse / tangent-space normal-map
  * textures.  UVs ride in the two padding floats of `Vertex`, 1-based texture handles in
