@@ -152,8 +152,12 @@ struct SceneView {
     const rto_texture* textures; uint32_t ntex;
 };
 
+struct Counters { uint64_t segments = 0, sphere_tests = 0, tri_tests = 0, rng_draws = 0, samples = 0; };
+static thread_local Counters* g_ctr = nullptr;   /* the running row's counters (RNG draws are counted where they happen) */
+
 /* wgsl:205-210 */
 inline uint32_t next_random_number(uint32_t* seed) {
+    if (g_ctr) g_ctr->rng_draws++;
     *seed = *seed * 747796405u + 2891336453u;
     uint32_t result = ((*seed >> ((*seed >> 28u) + 4u)) ^ *seed) * 277803737u;
     result = (result >> 22u) ^ result;
@@ -198,7 +202,7 @@ inline Hit ray_sphere(const Ray& ray, V3 pos, float radius) {
     float a = dot3(ray.dir, ray.dir);
     float b = 2.0f * dot3(oc, ray.dir);
     float c = dot3(oc, oc) - radius * radius;          /* pow(radius,2.0) */
-    float discriminant = fmaf(b, b, -((4.0f * a) * c));
+    float discriminant = b * b - (4.0f * a) * c;       /* scalar arithmetic is never fused */
     if (discriminant >= 0.0f) {
         float dst = (-b - sqrtf(discriminant)) / (2.0f * a);
         if (dst >= 0.0f) {
@@ -299,7 +303,6 @@ inline Material mesh_material(const rto_mesh& m) {
     return Material{v4(m.color), v4(m.emission_color), m.emission_strength, m.smoothness};
 }
 
-struct Counters { uint64_t segments = 0, sphere_tests = 0, tri_tests = 0; };
 
 /* wgsl:149-185 — brute force, spheres then meshes in order, strict '<' keeps the earliest */
 inline Hit calculate_ray_collions(const SceneView& sc, const Ray& ray, Counters* ctr) {
@@ -445,6 +448,7 @@ inline V4 frag(const SceneView& sc, const rto_params& params, const rto_camera& 
         Ray ray;
         ray.origin = co + offset;
         ray.dir = fma3(ver, posy, fma3(hor, posx, llc)) - ray.origin;
+        if (ctr) ctr->samples++;
         V4 t = trace(sc, params, ray, &rng_state, ctr, (j == 0) ? first_prim : nullptr);
         total = total + t;
     }
@@ -453,6 +457,8 @@ inline V4 frag(const SceneView& sc, const rto_params& params, const rto_camera& 
 }
 
 } /* namespace */
+
+static uint64_t* g_stats = nullptr;
 
 extern "C" {
 
@@ -506,14 +512,15 @@ int rto_dispatch_tex(const rto_params* params, const rto_camera* camera,
     if (y_step < 1) y_step = 1;
     const uint32_t W = params->width, H = params->height;
     SceneView sc{spheres, ns, vertices, nv, indices, ni, meshes, nm, textures, ntex};
-    uint64_t tot_seg = 0, tot_sph = 0, tot_tri = 0;
+    uint64_t tot_seg = 0, tot_sph = 0, tot_tri = 0, tot_rng = 0, tot_smp = 0;
 #ifdef _OPENMP
     if (nthreads <= 0) nthreads = omp_get_max_threads();
-#pragma omp parallel for schedule(dynamic, 1) num_threads(nthreads) reduction(+ : tot_seg, tot_sph, tot_tri)
+#pragma omp parallel for schedule(dynamic, 1) num_threads(nthreads) reduction(+ : tot_seg, tot_sph, tot_tri, tot_rng, tot_smp)
 #endif
     for (int64_t yy = 0; yy < (int64_t)H; yy += y_step) {
         uint32_t y = (uint32_t)yy;
         Counters ctr;
+        g_ctr = &ctr;
         for (uint32_t x = 0; x < W; x += (uint32_t)x_step) {
             uint32_t prim = 0xFFFFFFFFu;
             V4 f = frag(sc, *params, *camera, x, y, &ctr, &prim);
@@ -530,11 +537,17 @@ int rto_dispatch_tex(const rto_params* params, const rto_camera* camera,
             }
             if (primary_ids) primary_ids[(size_t)y * W + x] = prim;
         }
-        tot_seg += ctr.segments; tot_sph += ctr.sphere_tests; tot_tri += ctr.tri_tests;
+        g_ctr = nullptr;
+        tot_seg += ctr.segments; tot_sph += ctr.sphere_tests; tot_tri += ctr.tri_tests; tot_rng += ctr.rng_draws; tot_smp += ctr.samples;
     }
     if (counters) { counters[0] += tot_seg; counters[1] += tot_sph; counters[2] += tot_tri; }
+    if (g_stats) { g_stats[0] += tot_rng; g_stats[1] += tot_smp; }
     return 0;
 }
+
+/* Optional extra totals for tests: when set, every dispatch ADDS {RNG draws (next_random_number calls),
+ * camera paths (trace calls)} to stats[0..1].  Pass NULL to stop. */
+void rto_set_stats(uint64_t* stats) { g_stats = stats; }
 
 int rto_max_threads(void)
 {

@@ -81,6 +81,7 @@ def lib():
         L.rto_dispatch_tex.restype = C.c_int
         L.rto_sample_texture.argtypes = [vp, f32, f32, vp]
         L.rto_max_threads.restype = C.c_int
+        L.rto_set_stats.argtypes = [vp]
         L.rto_next_random_number.argtypes = [C.POINTER(u32)]
         L.rto_next_random_number.restype = u32
         L.rto_rand.argtypes = [C.POINTER(u32)]
@@ -110,6 +111,20 @@ def _ptr(a):
 
 def _f32(a):
     return np.ascontiguousarray(a, dtype=np.float32)
+
+
+class stats:
+    """with stats() as s: ... -> s.rng_draws, s.samples summed over the dispatches inside the block."""
+
+    def __enter__(self):
+        self._buf = np.zeros(2, np.uint64)
+        lib().rto_set_stats(_ptr(self._buf))
+        return self
+
+    def __exit__(self, *exc):
+        lib().rto_set_stats(None)
+        self.rng_draws, self.samples = int(self._buf[0]), int(self._buf[1])
+        return False
 
 
 def max_threads():

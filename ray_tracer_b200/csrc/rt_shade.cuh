@@ -25,7 +25,7 @@ __device__ __forceinline__ void test_sphere(float3 o, float3 d, float4 q0, float
     float a = dot3(d, d);
     float b = 2.0f * dot3(oc, d);
     float c = dot3(oc, oc) - q1.y;                       // q1.y = radius*radius
-    float disc = __fmaf_rn(b, b, -((4.0f * a) * c));
+    float disc = b * b - (4.0f * a) * c;                  // scalar arithmetic is never fused (contract)
     if (disc >= 0.0f) {
         float dst = (-b - sqrtf(disc)) / (2.0f * a);
         if (dst >= 0.0f && (dst < best.dst || (dst == best.dst && id < best.id && dst != RT_FLT_MAX))) {

@@ -1,8 +1,11 @@
 """Freezes small oracle renders as golden vectors:  python tests/golden/make_oracle_goldens.py
 
-The reference cannot be run (no Rust / WGSL / graphics stack), so these are outputs of the
-CPU oracle itself; they pin the oracle against compiler / flag / host-CPU drift and give the
-GPU tests a fixture that does not depend on the oracle being built on the box.
+The reference's WGSL cannot be executed by any tool in this image, so its shader text is translated
+mechanically to C++ at build time (oracle/make_ref.py -> oracle/_ref, contract build) and RUN here:
+every case below except the texture extension (`c2_cube`, no reference counterpart) is rendered by that
+translation and must equal the hand oracle's render bit for bit before it is frozen
+(`<case>/pinned_by_wgsl_ref` = 1).  The fixtures pin both against compiler / flag / host-CPU drift and give
+the GPU tests a reference output that does not need /root/reference on the box.
 """
 import os
 import sys
@@ -52,10 +55,26 @@ def render_case(name):
     return img, ids, int(ctr[0])
 
 
+def render_case_wgsl_ref(name):
+    """The same case through oracle/_ref (the translated reference shader, contract build)."""
+    from oracle import wgsl_ref as wr
+    kind, w, h, frames, bounces, rpp, sky, first = CASES[name]
+    ids = np.full((h, w), 0xFFFFFFFF, np.uint32)
+    ctr = np.zeros(3, np.uint64)
+    img = wr.render(scene_for(name, kind, w, h), w, h, frames, bounces, rpp, sky, first, ids, ctr, contract=True)
+    return img, ids, int(ctr[0])
+
+
 if __name__ == "__main__":
     out = {}
     for name in CASES:
         img, ids, rays = render_case(name)
+        pinned = 0
+        if name != "c2_cube":
+            img_r, ids_r, rays_r = render_case_wgsl_ref(name)
+            assert rays == rays_r and np.array_equal(ids, ids_r) and np.array_equal(img.view(np.uint32), img_r.view(np.uint32)), name
+            pinned = 1
+        out[name + "/pinned_by_wgsl_ref"] = np.array([pinned], np.uint8)
         out[name + "/image_bits"] = img.view(np.uint32)
         out[name + "/ids"] = ids
         out[name + "/rays"] = np.array([rays], np.uint64)

@@ -105,7 +105,7 @@ class Shader:
         a = dot3(d, d)
         b = F(2.0) * dot3(oc, d)
         c = dot3(oc, oc) - radius * radius
-        disc = fma(b, b, -((F(4.0) * a) * c))
+        disc = b * b - (F(4.0) * a) * c
         if disc >= ZERO:
             dst = (-b - np.sqrt(disc)) / (F(2.0) * a)
             if dst >= ZERO:
