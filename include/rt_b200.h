@@ -125,17 +125,20 @@ enum {
 /* ---- options ------------------------------------------------------------------------ */
 enum {
     RT_OPT_TRAVERSAL = 1,        /* 0 = LBVH (default), 1 = exhaustive brute force (validation) */
-    RT_OPT_SEED_MODE = 2,        /* 0 = strict: f32->u32 saturates (WGSL rule; default) */
+    RT_OPT_SEED_MODE = 2,        /* the seed's f32->u32 conversion (wgsl:308) of values >= 2^32, i.e. at 3840x2160 every row from 518 on:
+                                    0 = strict (default): saturates, the WGSL rule - those pixels share one RNG stream per dispatch;
+                                    1 = wide: wraps modulo 2^32 (a labelled deviation; identical to strict below 2^32, e.g. at 1080p) */
     RT_OPT_PRIMARY_IDS = 3,      /* 1 = record the primary-hit AOV on the next render call */
     RT_OPT_DETAIL_COUNTERS = 4,  /* 1 = count node visits / primitive tests (slower kernel) */
-    RT_OPT_FRAMES_PER_LAUNCH = 5,/* max reference dispatches fused into one kernel launch (default 128; 1 = one launch per dispatch like the reference) */
+    RT_OPT_FRAMES_PER_LAUNCH = 5,/* max reference dispatches fused into one kernel launch (0 = default: 128, or 4096 with RT_OPT_ITEM_MODE = 2; 1 = one launch per dispatch like the reference) */
     RT_OPT_LEAF_SIZE = 6,        /* max primitives per BVH leaf (1..8, default 2); takes effect at the next rt_upload_scene */
     RT_OPT_SCHED = 7,            /* tuning: warp scheduler thresholds in lanes, node_loop_min | (shade_min << 16); results do not depend on it */
     RT_OPT_BUILDER = 8,          /* hierarchy over the Morton order: 0 = PLOC (default), 1 = radix tree (Karras 2012); takes effect at the next rt_upload_scene; results do not depend on it */
     RT_OPT_PLOC_RADIUS = 9,      /* PLOC search window, clusters to either side (1..16, default 3) */
     RT_OPT_KERNEL = 10,          /* 0 = persistent megakernel (default), 1 = wavefront kernels over a path-slot pool; results do not depend on it */
     RT_OPT_WAVE_SLOTS = 11,      /* path slots of the wavefront pool (128 B each; default 2^21) */
-    RT_OPT_STAGING_MIB = 12      /* budget of the staging planes (one W*H float4 plane per fused dispatch), MiB (default 8192); bounds the dispatches per launch together with RT_OPT_FRAMES_PER_LAUNCH */
+    RT_OPT_STAGING_MIB = 12,     /* budget of the staging planes (one W*H float4 plane per fused dispatch), MiB (default 4352: 128 dispatches per launch at 1080p, 32 at 4K); bounds the dispatches per launch together with RT_OPT_FRAMES_PER_LAUNCH; allocated at the first fused launch */
+    RT_OPT_ITEM_MODE = 13        /* work items of the trace kernel: 1 = one (pixel, dispatch) pair, frags staged and folded in dispatch order by a blend kernel; 2 = one pixel with all fused dispatches, the progressive store (wgsl:59-66) applied by the owning lane, no staging memory (coarse items: slower on fused launches); 0 = auto (default): 2 for single-dispatch launches, else 1; results do not depend on it */
 };
 
 typedef struct rt_ctx rt_ctx;
@@ -218,20 +221,46 @@ int rt_clear(rt_ctx* ctx);
 int rt_set_shard(rt_ctx* ctx, uint32_t tile_rank, uint32_t tile_world,
                  uint32_t frame_rank, uint32_t frame_world);
 
-/* In-process combine of the shards (one rt_ctx per device, one host thread driving them all, as a single-process
- * host like the reference's event loop would): folds the accumulation images of ctxs[0..n-1] into ctxs[0]'s image
- * with ONE kernel on ctxs[0]'s device that reads the other images out of their devices' memory through NVLink peer
- * loads (cudaDeviceEnablePeerAccess; contexts on the same device need none).  For every pixel only the contexts
- * whose tile shard owns it are read; each enters with weights[k], or with 1 / frame_world of its rt_set_shard when
- * weights == NULL (the count-weighted mean of equally long sample shards), summed in array order.  A pure tile
- * partition therefore reproduces the single-GPU image bit for bit.  Pixels no context owns keep ctxs[0]'s value.
- * Ordered after everything queued on every context's stream; later work on any of them waits for the combine.
- * All contexts must have the same size; 1 <= n <= 16.  (Multi-process hosts combine with NCCL on
- * rt_accum_device_ptr instead, as bench.py does.) */
+/* ---- image combine of the shards ------------------------------------------------------------------------------
+ * Every combine writes a SEPARATE image, the "combined image" of the context that owns the result (rt_read_combined,
+ * rt_combined_device_ptr); no accumulation image is modified, so rendering can go on after a combine and be combined
+ * again.  For every pixel the shards whose tile partition owns it enter in array / rank order, each with the weight
+ * (dispatches in its running mean) / (dispatches in all the owners' running means) — the count-weighted mean of the
+ * sample shards' running means, equal to the reference's sequential running mean up to f32 rounding; a pure tile
+ * partition reproduces the single-GPU image bit for bit.  Pixels no shard owns take the first context's own value.
+ *
+ * In ONE process (one rt_ctx per device, one host thread driving them all, as the reference's event loop would):
+ * rt_combine_peers runs ONE kernel on ctxs[0]'s device that reads the other images out of their devices' memory
+ * through NVLink peer loads (cudaDeviceEnablePeerAccess; contexts on the same device need none).  weights != NULL
+ * overrides the count weights.  Ordered after everything queued on every context's stream; later work on any of them
+ * waits for the combine.  All contexts must have the same size; 1 <= n <= 16. */
 int rt_combine_peers(rt_ctx* const* ctxs, uint32_t n, const float* weights);
 /* The same combine fused with the display transform of rt_read_rgba8 (clamp, sRGB OETF, 8 bit) and the copy to the
- * host: no context's accumulation image is modified.  Synchronous. */
+ * host.  Synchronous. */
 int rt_combine_peers_rgba8(rt_ctx* const* ctxs, uint32_t n, const float* weights, uint8_t* rgba, size_t n_bytes);
+
+/* With ONE PROCESS PER GPU (torchrun, MPI, or a host thread per device): the same combine over NCCL (NVLink 5 /
+ * NVSwitch), bound at run time (libnccl.so.2).  One rank obtains an id with rt_comm_unique_id and hands it to the
+ * others by whatever channel the host has (the reference has none: it is single-device); every rank then calls
+ * rt_comm_init (collective) with its context, whose device the communicator is bound to.
+ * rt_combine (collective, asynchronous on each context's stream, no host synchronisation): every rank packs the
+ * pixels of ITS tiles (W*H / tile_world of them) and sends them to `root` (grouped ncclSend / ncclRecv; the shard
+ * table travels by ncclAllGather), where one kernel applies the count weights, de-interleaves the tiles and writes the
+ * combined image — or, rt_combine_rgba8, the tone-mapped bytes, copied to `rgba` at the root (ignored elsewhere;
+ * synchronous at the root).  All ranks of a communicator must share one tile_world (rt_set_shard).  Results equal
+ * rt_combine_peers' on the same shards bit for bit. */
+#define RT_COMM_ID_BYTES 128
+int rt_comm_unique_id(void* id, size_t n_bytes);
+int rt_comm_init(rt_ctx* ctx, int n_ranks, int rank, const void* id, size_t n_bytes);
+int rt_comm_destroy(rt_ctx* ctx);
+int rt_combine(rt_ctx* ctx, int root);
+int rt_combine_rgba8(rt_ctx* ctx, int root, uint8_t* rgba, size_t n_bytes);
+
+/* The combined image of the last rt_combine_peers (on ctxs[0]) / rt_combine (at the root). Synchronous. */
+int rt_read_combined(rt_ctx* ctx, float* rgba, size_t n_floats);          /* W*H*4 */
+void* rt_combined_device_ptr(rt_ctx* ctx);                                /* float4[W*H], NULL before the first combine */
+/* Dispatches in the context's running mean (wgsl:59-66): the weight its image enters a combine with. */
+uint32_t rt_mean_count(const rt_ctx* ctx);
 
 int rt_set_option(rt_ctx* ctx, int option, int64_t value);
 int rt_get_option(const rt_ctx* ctx, int option, int64_t* value);

@@ -125,10 +125,17 @@ inline float smoothstep1(float e0, float e1, float x) {
     float t = fminf(fmaxf((x - e0) / (e1 - e0), 0.0f), 1.0f);
     return (t * t) * (3.0f - 2.0f * t);
 }
-/* f32 -> u32, truncating, saturating, NaN -> 0 (WGSL spec; SURVEY.md §3.4(3) "strict") */
+/* f32 -> u32, truncating, NaN -> 0.  Values >= 2^32 (the seed at 3840x2160, rows >= 518):
+ *   seed mode 0 "strict": saturate (WGSL spec);
+ *   seed mode 1 "wide"  : wrap modulo 2^32 (the float is an exact integer there) — what SPIR-V's OpConvertFToU,
+ *                         undefined out of range, may equally do; identical to strict below 2^32. */
+static int g_seed_mode = 0;
 inline uint32_t f2u_sat(float f) {
     if (!(f > 0.0f)) return 0u;
-    if (f >= 4294967296.0f) return 0xFFFFFFFFu;
+    if (f >= 4294967296.0f) {
+        if (g_seed_mode == 1) return (f >= 18446744073709551616.0f) ? 0u : (uint32_t)(uint64_t)f;
+        return 0xFFFFFFFFu;
+    }
     return (uint32_t)f;
 }
 
@@ -548,6 +555,8 @@ int rto_dispatch_tex(const rto_params* params, const rto_camera* camera,
 /* Optional extra totals for tests: when set, every dispatch ADDS {RNG draws (next_random_number calls),
  * camera paths (trace calls)} to stats[0..1].  Pass NULL to stop. */
 void rto_set_stats(uint64_t* stats) { g_stats = stats; }
+/* 0 = strict (default), 1 = wide: see f2u_sat.  Process-wide; returns the previous mode. */
+int rto_set_seed_mode(int mode) { int old = g_seed_mode; g_seed_mode = (mode == 1) ? 1 : 0; return old; }
 
 int rto_max_threads(void)
 {

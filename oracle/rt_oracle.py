@@ -82,6 +82,8 @@ def lib():
         L.rto_sample_texture.argtypes = [vp, f32, f32, vp]
         L.rto_max_threads.restype = C.c_int
         L.rto_set_stats.argtypes = [vp]
+        L.rto_set_seed_mode.argtypes = [C.c_int]
+        L.rto_set_seed_mode.restype = C.c_int
         L.rto_next_random_number.argtypes = [C.POINTER(u32)]
         L.rto_next_random_number.restype = u32
         L.rto_rand.argtypes = [C.POINTER(u32)]
@@ -124,6 +126,21 @@ class stats:
     def __exit__(self, *exc):
         lib().rto_set_stats(None)
         self.rng_draws, self.samples = int(self._buf[0]), int(self._buf[1])
+        return False
+
+
+class seed_mode:
+    """with seed_mode(1): ... -> the seed's out-of-range f32->u32 conversion wraps ("wide") instead of saturating."""
+
+    def __init__(self, mode):
+        self.mode = mode
+
+    def __enter__(self):
+        self.old = lib().rto_set_seed_mode(int(self.mode))
+        return self
+
+    def __exit__(self, *exc):
+        lib().rto_set_seed_mode(self.old)
         return False
 
 

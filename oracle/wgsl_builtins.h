@@ -50,8 +50,19 @@ typedef float f32;
 typedef uint32_t u32;
 typedef int32_t i32;
 
-/* ---- value conversions (WGSL 16.1) -------------------------------------------------- */
-inline u32 to_u32(f32 f) { if (!(f > 0.0f)) return 0u; if (f >= 4294967296.0f) return 0xFFFFFFFFu; return (u32)f; }
+/* ---- value conversions (WGSL 16.1) --------------------------------------------------
+ * u32(f32) of a value >= 2^32: saturates (the WGSL rule; default) or, with f2u_wrap set (the "wide" seed mode of
+ * the CUDA path, a labelled deviation), wraps modulo 2^32 as an out-of-range SPIR-V OpConvertFToU may. */
+static int f2u_wrap = 0;
+inline u32 to_u32(f32 f)
+{
+    if (!(f > 0.0f)) return 0u;
+    if (f >= 4294967296.0f) {
+        if (f2u_wrap) return (f >= 18446744073709551616.0f) ? 0u : (u32)(uint64_t)f;
+        return 0xFFFFFFFFu;
+    }
+    return (u32)f;
+}
 inline u32 to_u32(i32 i) { return (u32)i; }
 inline u32 to_u32(u32 u) { return u; }
 inline u32 to_u32(bool b) { return b ? 1u : 0u; }

@@ -61,6 +61,22 @@ def struct_layout(name, contract=True):
     return int(s.value), int(a.value)
 
 
+class seed_mode:
+    """with seed_mode(1): ... -> u32(f32) wraps modulo 2^32 out of range ("wide") in both builds."""
+
+    def __init__(self, mode):
+        self.mode = mode
+
+    def __enter__(self):
+        self.old = [lib(c).wgslref_set_f2u_wrap(int(self.mode)) for c in (True, False)]
+        return self
+
+    def __exit__(self, *exc):
+        for c, o in zip((True, False), self.old):
+            lib(c).wgslref_set_f2u_wrap(o)
+        return False
+
+
 class Aov:
     """Per-dispatch extras of the translated shader (hooks, oracle/wgsl_ref_hooks.h)."""
 

@@ -53,6 +53,7 @@ class Counters(C.Structure):
 RT_OPT_TRAVERSAL, RT_OPT_SEED_MODE, RT_OPT_PRIMARY_IDS, RT_OPT_DETAIL_COUNTERS = 1, 2, 3, 4
 RT_OPT_FRAMES_PER_LAUNCH, RT_OPT_LEAF_SIZE, RT_OPT_SCHED = 5, 6, 7
 RT_OPT_BUILDER, RT_OPT_PLOC_RADIUS, RT_OPT_KERNEL, RT_OPT_WAVE_SLOTS, RT_OPT_STAGING_MIB = 8, 9, 10, 11, 12
+RT_OPT_ITEM_MODE = 13
 RT_OK, RT_ERR_INVALID_ARGUMENT, RT_ERR_CUDA, RT_ERR_NO_SCENE = 0, -1, -2, -3
 RT_ERR_OUT_OF_MEMORY, RT_ERR_BAD_INDEX, RT_ERR_UNSUPPORTED = -4, -5, -6
 MISS = 0xFFFFFFFF
@@ -77,6 +78,14 @@ SYMBOLS = {
     "rt_set_shard": (C.c_int, [_vp, _u32, _u32, _u32, _u32]),
     "rt_combine_peers": (C.c_int, [C.POINTER(_vp), _u32, _vp]),
     "rt_combine_peers_rgba8": (C.c_int, [C.POINTER(_vp), _u32, _vp, _vp, _sz]),
+    "rt_comm_unique_id": (C.c_int, [_vp, _sz]),
+    "rt_comm_init": (C.c_int, [_vp, C.c_int, C.c_int, _vp, _sz]),
+    "rt_comm_destroy": (C.c_int, [_vp]),
+    "rt_combine": (C.c_int, [_vp, C.c_int]),
+    "rt_combine_rgba8": (C.c_int, [_vp, C.c_int, _vp, _sz]),
+    "rt_read_combined": (C.c_int, [_vp, _vp, _sz]),
+    "rt_combined_device_ptr": (_vp, [_vp]),
+    "rt_mean_count": (_u32, [_vp]),
     "rt_set_option": (C.c_int, [_vp, C.c_int, _i64]),
     "rt_get_option": (C.c_int, [_vp, C.c_int, C.POINTER(_i64)]),
     "rt_read_accum": (C.c_int, [_vp, _vp, _sz]),

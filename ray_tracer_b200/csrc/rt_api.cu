@@ -32,10 +32,16 @@ struct rt_ctx {
     uint32_t* primary_ids = nullptr;
     unsigned long long* d_counters = nullptr;     // rays, samples, node visits, tri/sphere tests, hit segments
     unsigned long long* d_queue = nullptr;        // work-queue head of the persistent trace kernel
+    float4* combined = nullptr;                   // result of rt_combine / rt_combine_peers (allocated at the first combine; accum is never overwritten by a combine)
+    uint8_t* d_rgba8 = nullptr;                   // tone-mapped image of rt_read_rgba8 / the fused combines (kept between calls)
+    uint32_t mean_count = 0;                      // dispatches in accum's running mean (the combine weight of a sample shard)
+    cudaMemPool_t mempool = nullptr;              // private pool of the stream-ordered scene allocations
+    rt::Comm* comm = nullptr;                     // NCCL communicator of the multi-process combine (rt_comm_init)
     float4* staging = nullptr;                    // per-dispatch frag planes awaiting the blend
     uint32_t staging_frames = 0;
     int n_sms = 148;
-    int64_t opt_staging_bytes = 8ll << 30;        // staging planes: 128 dispatches at 1080p, 61 at 4K (RT_OPT_STAGING_MIB)
+    int64_t opt_staging_bytes = 4352ll << 20;     // staging planes (RT_OPT_STAGING_MIB): 128 dispatches per launch at 1080p, 32 at 4K
+    int64_t opt_item_mode = 0;                    // 0: auto, 1: (pixel, dispatch) items + staging + blend kernel, 2: pixel items, running mean applied in the trace kernel
     int64_t opt_sched = 8 | (1 << 8) | (22 << 16);     // node loop runs while >= 8 lanes can step; shade once >= 22 lanes wait (swept on C3/C5)
     rt::SceneBuffers scene;
     std::vector<rt_mesh> mesh_ranges;             // the uploaded Mesh records (rt_update_records checks the index ranges against them)
@@ -43,10 +49,11 @@ struct rt_ctx {
     std::vector<Tex> textures;                    // texture extension: CUDA arrays + texture objects
     rt::TexDev* d_tex = nullptr;                  // device table of (object, width, height)
     bool has_scene = false, has_camera = false, has_params = false;
+    bool scene_too_deep = false;                  // BVH deeper than the traversal stack: launches use the exhaustive scan
     rt_params params{};
     rt_camera_uniform camera{};
     uint32_t tile_rank = 0, tile_world = 1, frame_rank = 0, frame_world = 1;
-    int64_t opt_traversal = 0, opt_seed_mode = 0, opt_primary_ids = 0, opt_detail = 0, opt_frames_per_launch = 128, opt_leaf_size = 2, opt_builder = 0, opt_ploc_radius = 3, opt_kernel = 0, opt_wave_slots = 1 << 21;
+    int64_t opt_traversal = 0, opt_seed_mode = 0, opt_primary_ids = 0, opt_detail = 0, opt_frames_per_launch = 0, opt_leaf_size = 2, opt_builder = 0, opt_ploc_radius = 3, opt_kernel = 0, opt_wave_slots = 1 << 21;
     rt::WavePool wave;                            // path-slot pool of the wavefront kernels (RT_OPT_KERNEL = 1)
     uint64_t dispatches = 0, launches = 0;
     double kernel_ms = 0.0;
@@ -72,18 +79,39 @@ struct DeviceGuard {
     ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
 };
 
+// New image buffers are allocated first and swapped in on success: a failed rt_resize leaves the context as it was.
 int alloc_image(rt_ctx* c, uint32_t w, uint32_t h)
 {
+    const size_t n = (size_t)w * h;
+    float4* accum = nullptr; uint32_t* ids = nullptr;
+    cudaError_t e = cudaMalloc((void**)&accum, n * sizeof(float4));
+    if (e == cudaSuccess) e = cudaMalloc((void**)&ids, n * sizeof(uint32_t));
+    if (e == cudaSuccess) e = cudaMemsetAsync(accum, 0, n * sizeof(float4), c->stream);          // wgpu zero-initialises textures
+    if (e == cudaSuccess) e = cudaMemsetAsync(ids, 0xFF, n * sizeof(uint32_t), c->stream);
+    if (e != cudaSuccess) { if (accum) cudaFree(accum); if (ids) cudaFree(ids); return cuda_fail(c, e, "image allocation"); }
     if (c->accum) cudaFree(c->accum);
     if (c->primary_ids) cudaFree(c->primary_ids);
     if (c->staging) cudaFree(c->staging);
-    c->accum = nullptr; c->primary_ids = nullptr; c->staging = nullptr; c->staging_frames = 0;
-    size_t n = (size_t)w * h;
-    CU(c, cudaMalloc((void**)&c->accum, n * sizeof(float4)));
-    CU(c, cudaMalloc((void**)&c->primary_ids, n * sizeof(uint32_t)));
-    CU(c, cudaMemsetAsync(c->accum, 0, n * sizeof(float4), c->stream));          // wgpu zero-initialises textures
-    CU(c, cudaMemsetAsync(c->primary_ids, 0xFF, n * sizeof(uint32_t), c->stream));
-    c->width = w; c->height = h;
+    if (c->combined) cudaFree(c->combined);
+    if (c->d_rgba8) cudaFree(c->d_rgba8);
+    c->accum = accum; c->primary_ids = ids; c->staging = nullptr; c->staging_frames = 0; c->combined = nullptr; c->d_rgba8 = nullptr;
+    c->width = w; c->height = h; c->mean_count = 0;
+    return RT_OK;
+}
+
+int ensure_combined(rt_ctx* c)
+{
+    if (c->combined) return RT_OK;
+    const size_t n = (size_t)c->width * c->height;
+    CU(c, cudaMalloc((void**)&c->combined, n * sizeof(float4)));
+    CU(c, cudaMemsetAsync(c->combined, 0, n * sizeof(float4), c->stream));
+    return RT_OK;
+}
+
+int ensure_rgba8(rt_ctx* c)
+{
+    if (c->d_rgba8) return RT_OK;
+    CU(c, cudaMalloc((void**)&c->d_rgba8, (size_t)c->width * c->height * 4));
     return RT_OK;
 }
 
@@ -110,11 +138,21 @@ rt::CameraDev to_dev(const rt_camera_uniform& u)
     return d;
 }
 
-// Dispatches fused per launch: bounded by the option and by the staging budget (one W*H float4 plane each).
+// Pixel items (one lane owns a pixel for every fused dispatch and applies wgsl:59-66 itself: no staging, no blend
+// kernel) whenever asked for, and in auto mode for single-dispatch launches, where the two item kinds coincide.
+// For fused launches auto mode keeps (pixel, dispatch) items: a 1080p teapot pixel of 128 dispatches is ~18 ms of one
+// lane's time and a lane gets only ~3 of them, so pixel items balance badly (measured: C3 3,985 vs 9,132 Mrays/s,
+// C4 / C5 / C2 -10 %); the running mean is order-dependent per pixel, so finer items need the staged frags.
+bool fold_mode(const rt_ctx* c, uint32_t n_frames) { return c->opt_kernel == 0 && (c->opt_item_mode == 2 || (c->opt_item_mode == 0 && n_frames == 1)); }
+
+// Dispatches fused per launch: 128 by default, bounded by the staging budget (one W*H float4 plane per dispatch);
+// forced pixel items need no staging: up to 4096 per launch unless the option says otherwise.
 uint32_t frames_per_launch(const rt_ctx* c)
 {
-    int64_t by_mem = c->opt_staging_bytes / (int64_t)((size_t)c->width * c->height * sizeof(float4));
     int64_t f = c->opt_frames_per_launch;
+    if (c->opt_kernel == 0 && c->opt_item_mode == 2) return (uint32_t)(f < 1 ? 4096 : f);
+    if (f < 1) f = 128;
+    int64_t by_mem = c->opt_staging_bytes / (int64_t)((size_t)c->width * c->height * sizeof(float4));
     if (f > by_mem) f = by_mem;
     return (uint32_t)(f < 1 ? 1 : f);
 }
@@ -142,6 +180,7 @@ int launch(rt_ctx* c, int32_t first_frame, uint32_t n_frames, bool want_ids)
     lp.width = c->width; lp.height = c->height;
     lp.bounces = c->params.number_of_bounces; lp.rpp = c->params.rays_per_pixel; lp.toggle = c->params.skybox;
     lp.first_frame = first_frame; lp.n_frames = n_frames;
+    lp.blend0 = first_frame >= 0 ? (int32_t)((uint32_t)first_frame / c->frame_world) : first_frame;
     lp.tile_rank = c->tile_rank; lp.tile_world = c->tile_world; lp.frame_world = c->frame_world;
     lp.tiles_x = (c->width + 7) / 8;
     const uint32_t tiles = lp.tiles_x * ((c->height + 7) / 8);
@@ -151,7 +190,8 @@ int launch(rt_ctx* c, int32_t first_frame, uint32_t n_frames, bool want_ids)
     lp.rpp_scale = (lp.rpp > 0 && (lp.rpp & (lp.rpp - 1)) == 0) ? 1.0f / (float)lp.rpp : 0.0f;
     lp.sched_n_stay = (int32_t)(c->opt_sched & 0xff); if (lp.sched_n_stay < 1) lp.sched_n_stay = 1; lp.sched_l_stay = (int32_t)((c->opt_sched >> 8) & 0xff); lp.sched_s_min = (int32_t)((c->opt_sched >> 16) & 0xff);
 
-    { int rc = ensure_staging(c, n_frames); if (rc != RT_OK) return rc; }
+    const bool fold = fold_mode(c, n_frames);
+    if (!fold) { int rc = ensure_staging(c, n_frames); if (rc != RT_OK) return rc; }
     std::pair<cudaEvent_t, cudaEvent_t> ev;
     if (!c->pool.empty()) { ev = c->pool.back(); c->pool.pop_back(); }
     else { CU(c, cudaEventCreate(&ev.first)); CU(c, cudaEventCreate(&ev.second)); }
@@ -160,11 +200,11 @@ int launch(rt_ctx* c, int32_t first_frame, uint32_t n_frames, bool want_ids)
     if (c->opt_kernel == 1) {
         if ((e = c->wave.ensure((uint32_t)c->opt_wave_slots)) != cudaSuccess) return cuda_fail(c, e, "wavefront pool");
         e = rt::launch_wave(sd, to_dev(c->camera), lp, c->wave, c->staging, want_ids ? c->primary_ids : nullptr, c->d_counters,
-                            c->opt_traversal == 1, c->opt_detail != 0, c->n_sms, c->stream);
+                            c->opt_traversal == 1 || c->scene_too_deep, c->opt_detail != 0, c->n_sms, c->stream);
         if (e == cudaSuccess) e = rt::launch_blend(lp, c->staging, c->accum, c->stream);
     } else {
         e = rt::launch_trace(sd, to_dev(c->camera), lp, c->staging, c->accum, want_ids ? c->primary_ids : nullptr,
-                             c->d_counters, c->d_queue, c->opt_traversal == 1, c->opt_detail != 0, c->n_sms, c->stream);
+                             c->d_counters, c->d_queue, c->opt_traversal == 1 || c->scene_too_deep, c->opt_detail != 0, fold, c->n_sms, c->stream);
     }
     if (e != cudaSuccess) return cuda_fail(c, e, "trace kernel launch");
     CU(c, cudaEventRecord(ev.second, c->stream));
@@ -172,6 +212,7 @@ int launch(rt_ctx* c, int32_t first_frame, uint32_t n_frames, bool want_ids)
     if (c->pending.size() > 4096) drain_events(c);
     c->launches++;
     c->dispatches += n_frames;
+    { const int64_t last = (int64_t)lp.blend0 + (int64_t)n_frames - 1; c->mean_count = last >= 0 ? (uint32_t)(last + 1) : 1u; }   // wgsl:59-66: blend index b = mean of b + 1 dispatches
     return RT_OK;
 }
 
@@ -215,9 +256,15 @@ int rt_create(rt_ctx** out, int device, uint32_t width, uint32_t height)
     int rc = RT_OK;
     do {
         if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) { rc = cuda_fail(nullptr, e, "cudaStreamCreate"); break; }
-        {   // scene uploads allocate stream-ordered from the default pool: keep freed blocks cached for the next upload
-            cudaMemPool_t pool; unsigned long long keep = ~0ull;
-            if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        {   // scene uploads allocate stream-ordered from a pool of this context that keeps freed blocks cached for the
+            // next upload; the device's default pool, which the host process may use itself, is not touched
+            cudaMemPoolProps props; memset(&props, 0, sizeof props);
+            props.allocType = cudaMemAllocationTypePinned; props.handleTypes = cudaMemHandleTypeNone;
+            props.location.type = cudaMemLocationTypeDevice; props.location.id = device;
+            unsigned long long keep = ~0ull;
+            if (cudaMemPoolCreate(&c->mempool, &props) == cudaSuccess) cudaMemPoolSetAttribute(c->mempool, cudaMemPoolAttrReleaseThreshold, &keep);
+            else { c->mempool = nullptr; cudaGetLastError(); }
+            c->scene.pool = c->mempool;
         }
         if ((e = cudaMalloc((void**)&c->d_counters, 6 * sizeof(unsigned long long))) != cudaSuccess) { rc = cuda_fail(nullptr, e, "cudaMalloc counters"); break; }
         if ((e = cudaMemsetAsync(c->d_counters, 0, 6 * sizeof(unsigned long long), c->stream)) != cudaSuccess) { rc = cuda_fail(nullptr, e, "memset counters"); break; }
@@ -241,13 +288,17 @@ void rt_destroy(rt_ctx* c)
     for (auto& p : c->pool) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
     c->scene.release();
     free_textures(c);
+    if (c->comm) { rt::comm_destroy(c->comm); c->comm = nullptr; }
+    if (c->combined) cudaFree(c->combined);
+    if (c->d_rgba8) cudaFree(c->d_rgba8);
     if (c->accum) cudaFree(c->accum);
     if (c->primary_ids) cudaFree(c->primary_ids);
     if (c->d_counters) cudaFree(c->d_counters);
     if (c->d_queue) cudaFree(c->d_queue);
     c->wave.release();
     if (c->staging) cudaFree(c->staging);
-    if (c->stream) cudaStreamDestroy(c->stream);
+    if (c->stream) { cudaStreamSynchronize(c->stream); cudaStreamDestroy(c->stream); }
+    if (c->mempool) cudaMemPoolDestroy(c->mempool);
     delete c;
 }
 
@@ -282,10 +333,9 @@ int rt_upload_scene(rt_ctx* c, const rt_sphere* spheres, uint32_t ns, const rt_v
     uint32_t leaf = (uint32_t)(c->opt_leaf_size < 1 ? 1 : (c->opt_leaf_size > 8 ? 8 : c->opt_leaf_size));
     cudaError_t e = rt::build_scene(c->scene, spheres, ns, vertices, nv, indices, ni, meshes, nm, leaf, (int)c->opt_builder, (int)c->opt_ploc_radius, c->stream);
     if (e != cudaSuccess) { c->has_scene = false; return cuda_fail(c, e, "scene build"); }
-    if (c->scene.max_depth > 62) {
-        c->has_scene = false; c->scene.release();
-        return fail(c, RT_ERR_UNSUPPORTED, "rt_upload_scene: BVH deeper than the traversal stack");
-    }
+    // A hierarchy deeper than the traversal stack (both builders; needs thousands of coincident primitives plus far
+    // outliers) is not an error: the reference renders any scene, so such a scene is traced with the exhaustive scan.
+    c->scene_too_deep = c->scene.max_depth > RT_STACK - 2;
     c->has_scene = true;
     c->mesh_ranges.assign(meshes, meshes + nm);
     return RT_OK;
@@ -436,6 +486,7 @@ int rt_clear(rt_ctx* c)
     if (!c) return RT_ERR_INVALID_ARGUMENT;
     DeviceGuard g(c->device);
     CU(c, cudaMemsetAsync(c->accum, 0, (size_t)c->width * c->height * sizeof(float4), c->stream));
+    c->mean_count = 0;
     return RT_OK;
 }
 
@@ -465,10 +516,19 @@ int combine_peers(rt_ctx* const* ctxs, uint32_t n, const float* weights, uint8_t
         if (p->width != c->width || p->height != c->height) return fail(c, RT_ERR_INVALID_ARGUMENT, std::string(who) + ": contexts differ in size");
         for (uint32_t j = 0; j < k; j++) if (ctxs[j] == p) return fail(c, RT_ERR_INVALID_ARGUMENT, std::string(who) + ": a context is listed twice");
         ps.p[k].accum = p->accum; ps.p[k].tile_rank = p->tile_rank; ps.p[k].tile_world = p->tile_world;
-        ps.p[k].weight = weights ? weights[k] : 1.0f / (float)p->frame_world;
+    }
+    for (uint32_t k = 0; k < n; k++) {
+        // default weight: this shard's share of the dispatches its pixels have seen (count-weighted mean of the running means);
+        // shards with the same tile partition own the same pixels
+        uint64_t total = 0;
+        for (uint32_t j = 0; j < n; j++)
+            if (ctxs[j]->tile_rank == ctxs[k]->tile_rank && ctxs[j]->tile_world == ctxs[k]->tile_world) total += ctxs[j]->mean_count;
+        ps.p[k].weight = weights ? weights[k] : (total == 0 || total == ctxs[k]->mean_count ? 1.0f : (float)ctxs[k]->mean_count / (float)total);
     }
     if (npx == 0) return RT_OK;
     DeviceGuard g(c->device);
+    { int rc = ensure_combined(c); if (rc != RT_OK) return rc; }
+    if (host_rgba8) { int rc = ensure_rgba8(c); if (rc != RT_OK) return rc; }
     // peer access + ordering: the combine waits for every shard's stream, and the shards wait for the combine
     std::vector<cudaEvent_t> events;
     auto drop = [&]() { for (cudaEvent_t e : events) cudaEventDestroy(e); };
@@ -488,16 +548,14 @@ int combine_peers(rt_ctx* const* ctxs, uint32_t n, const float* weights, uint8_t
         if (e == cudaSuccess) e = cudaStreamWaitEvent(c->stream, ev, 0);
         if (e != cudaSuccess) { drop(); return cuda_fail(c, e, "combine: ordering after a shard's stream"); }
     }
-    uint8_t* d8 = nullptr;
-    if (host_rgba8) { cudaError_t e = cudaMallocAsync((void**)&d8, npx * 4, c->stream); if (e != cudaSuccess) { drop(); return cuda_fail(c, e, "cudaMallocAsync rgba8"); } }
-    cudaError_t e = rt::launch_combine(ps, c->accum, d8, c->width, c->height, c->n_sms, c->stream);
+    uint8_t* d8 = host_rgba8 ? c->d_rgba8 : nullptr;
+    cudaError_t e = rt::launch_combine(ps, c->combined, d8, c->width, c->height, c->n_sms, c->stream);
     cudaEvent_t done = nullptr;
     if (e == cudaSuccess && n > 1) e = cudaEventCreateWithFlags(&done, cudaEventDisableTiming);
     if (done) events.push_back(done);
     if (e == cudaSuccess && done) e = cudaEventRecord(done, c->stream);
     for (uint32_t k = 1; k < n && e == cudaSuccess; k++) { DeviceGuard gp(ctxs[k]->device); e = cudaStreamWaitEvent(ctxs[k]->stream, done, 0); }
     if (e == cudaSuccess && host_rgba8) e = cudaMemcpyAsync(host_rgba8, d8, npx * 4, cudaMemcpyDeviceToHost, c->stream);
-    if (d8) cudaFreeAsync(d8, c->stream);
     if (e == cudaSuccess && host_rgba8) e = cudaStreamSynchronize(c->stream);
     drop();
     if (e != cudaSuccess) return cuda_fail(c, e, who);
@@ -516,15 +574,93 @@ int rt_combine_peers_rgba8(rt_ctx* const* ctxs, uint32_t n, const float* weights
     return combine_peers(ctxs, n, weights, rgba, n_bytes, "rt_combine_peers_rgba8");
 }
 
+// ---- multi-process combine over NCCL (rt_comm.cu) ---------------------------------------------------------------
+int rt_comm_unique_id(void* id, size_t n_bytes)
+{
+    if (!id || n_bytes != RT_COMM_ID_BYTES) return fail(nullptr, RT_ERR_INVALID_ARGUMENT, "rt_comm_unique_id: id must be RT_COMM_ID_BYTES bytes");
+    if (const char* e = rt::comm_unique_id(id)) return fail(nullptr, RT_ERR_UNSUPPORTED, e);
+    return RT_OK;
+}
+
+int rt_comm_init(rt_ctx* c, int n_ranks, int rank, const void* id, size_t n_bytes)
+{
+    if (!c) return RT_ERR_INVALID_ARGUMENT;
+    if (!id || n_bytes != RT_COMM_ID_BYTES) return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_comm_init: id must be RT_COMM_ID_BYTES bytes");
+    if (n_ranks < 1 || rank < 0 || rank >= n_ranks) return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_comm_init: rank must be in [0, n_ranks)");
+    if (c->comm) return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_comm_init: the context already has a communicator (rt_comm_destroy)");
+    DeviceGuard g(c->device);
+    if (const char* e = rt::comm_create(&c->comm, n_ranks, rank, id)) { c->comm = nullptr; return fail(c, RT_ERR_UNSUPPORTED, e); }
+    return RT_OK;
+}
+
+int rt_comm_destroy(rt_ctx* c)
+{
+    if (!c) return RT_ERR_INVALID_ARGUMENT;
+    DeviceGuard g(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    if (c->comm) { rt::comm_destroy(c->comm); c->comm = nullptr; }
+    return RT_OK;
+}
+
+namespace {
+int combine_comm(rt_ctx* c, int root, uint8_t* host_rgba8, size_t n_bytes, const char* who)
+{
+    if (!c) return RT_ERR_INVALID_ARGUMENT;
+    if (!c->comm) return fail(c, RT_ERR_INVALID_ARGUMENT, std::string(who) + ": no communicator (rt_comm_init)");
+    if (root < 0 || root >= rt::comm_size(c->comm)) return fail(c, RT_ERR_INVALID_ARGUMENT, std::string(who) + ": root out of range");
+    const bool is_root = rt::comm_rank(c->comm) == root;
+    const size_t npx = (size_t)c->width * c->height;
+    if (is_root && host_rgba8 && n_bytes != npx * 4) return fail(c, RT_ERR_INVALID_ARGUMENT, std::string(who) + ": size must be W*H*4");
+    DeviceGuard g(c->device);
+    const bool fused = host_rgba8 != nullptr || n_bytes == (size_t)-1;
+    if (is_root && !fused) { int rc = ensure_combined(c); if (rc != RT_OK) return rc; }
+    if (is_root && fused) { int rc = ensure_rgba8(c); if (rc != RT_OK) return rc; }
+    rt::ShardRec mine{c->tile_rank, c->tile_world, c->frame_rank, c->frame_world, c->mean_count, {0, 0, 0}};
+    if (const char* e = rt::comm_combine(c->comm, mine, root, c->accum, fused ? nullptr : c->combined, (is_root && fused) ? c->d_rgba8 : nullptr,
+                                         c->width, c->height, c->n_sms, c->stream))
+        return fail(c, RT_ERR_CUDA, e);
+    if (is_root && host_rgba8) {
+        CU(c, cudaMemcpyAsync(host_rgba8, c->d_rgba8, npx * 4, cudaMemcpyDeviceToHost, c->stream));
+        CU(c, cudaStreamSynchronize(c->stream));
+    }
+    return RT_OK;
+}
+} // namespace
+
+int rt_combine(rt_ctx* c, int root) { return combine_comm(c, root, nullptr, 0, "rt_combine"); }
+
+int rt_combine_rgba8(rt_ctx* c, int root, uint8_t* rgba, size_t n_bytes)
+{
+    if (!c) return RT_ERR_INVALID_ARGUMENT;
+    const bool is_root = c->comm && rt::comm_rank(c->comm) == root;
+    if (is_root && !rgba) return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_combine_rgba8: NULL at the root");
+    return combine_comm(c, root, is_root ? rgba : nullptr, is_root ? n_bytes : (size_t)-1, "rt_combine_rgba8");
+}
+
+int rt_read_combined(rt_ctx* c, float* rgba, size_t n_floats)
+{
+    if (!c || !rgba) return c ? fail(c, RT_ERR_INVALID_ARGUMENT, "rt_read_combined: NULL") : RT_ERR_INVALID_ARGUMENT;
+    if (n_floats != (size_t)c->width * c->height * 4) return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_read_combined: size must be W*H*4");
+    if (!c->combined) return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_read_combined: no combine has produced an image on this context");
+    DeviceGuard g(c->device);
+    CU(c, cudaMemcpyAsync(rgba, c->combined, n_floats * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    return RT_OK;
+}
+
+void* rt_combined_device_ptr(rt_ctx* c) { return c ? (void*)c->combined : nullptr; }
+uint32_t rt_mean_count(const rt_ctx* c) { return c ? c->mean_count : 0u; }
+
 int rt_set_option(rt_ctx* c, int option, int64_t value)
 {
     if (!c) return RT_ERR_INVALID_ARGUMENT;
     switch (option) {
     case RT_OPT_TRAVERSAL: if (value != 0 && value != 1) break; c->opt_traversal = value; return RT_OK;
-    case RT_OPT_SEED_MODE: if (value != 0) break; c->opt_seed_mode = value; return RT_OK;
+    case RT_OPT_SEED_MODE: if (value != 0 && value != 1) break; c->opt_seed_mode = value; return RT_OK;
     case RT_OPT_PRIMARY_IDS: c->opt_primary_ids = value != 0; return RT_OK;
     case RT_OPT_DETAIL_COUNTERS: c->opt_detail = value != 0; return RT_OK;
-    case RT_OPT_FRAMES_PER_LAUNCH: if (value < 1 || value > (1 << 20)) break; c->opt_frames_per_launch = value; return RT_OK;
+    case RT_OPT_FRAMES_PER_LAUNCH: if (value < 0 || value > (1 << 20)) break; c->opt_frames_per_launch = value; return RT_OK;
+    case RT_OPT_ITEM_MODE: if (value < 0 || value > 2) break; c->opt_item_mode = value; return RT_OK;
     case RT_OPT_LEAF_SIZE: if (value < 1 || value > 8) break; c->opt_leaf_size = value; return RT_OK;
     case RT_OPT_SCHED: c->opt_sched = value & 0xffffff; return RT_OK;
     case RT_OPT_BUILDER: if (value != 0 && value != 1) break; c->opt_builder = value; return RT_OK;
@@ -553,6 +689,7 @@ int rt_get_option(const rt_ctx* c, int option, int64_t* value)
     case RT_OPT_KERNEL: *value = c->opt_kernel; return RT_OK;
     case RT_OPT_WAVE_SLOTS: *value = c->opt_wave_slots; return RT_OK;
     case RT_OPT_STAGING_MIB: *value = c->opt_staging_bytes >> 20; return RT_OK;
+    case RT_OPT_ITEM_MODE: *value = c->opt_item_mode; return RT_OK;
     default: return RT_ERR_INVALID_ARGUMENT;
     }
 }
@@ -583,12 +720,10 @@ int rt_read_rgba8(rt_ctx* c, uint8_t* rgba, size_t n_bytes)
     size_t n = (size_t)c->width * c->height;
     if (n_bytes != n * 4) return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_read_rgba8: size must be W*H*4");
     DeviceGuard g(c->device);
-    uint8_t* d = nullptr;
-    CU(c, cudaMalloc((void**)&d, n * 4));
-    cudaError_t e = rt::launch_tonemap(c->accum, d, n, c->stream);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(rgba, d, n * 4, cudaMemcpyDeviceToHost, c->stream);
+    { int rc = ensure_rgba8(c); if (rc != RT_OK) return rc; }
+    cudaError_t e = rt::launch_tonemap(c->accum, c->d_rgba8, n, c->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(rgba, c->d_rgba8, n * 4, cudaMemcpyDeviceToHost, c->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
-    cudaFree(d);
     if (e != cudaSuccess) return cuda_fail(c, e, "tonemap");
     return RT_OK;
 }

@@ -424,9 +424,10 @@ __global__ void emit_nodes(int n_inner, const int2* children, const int2* ranges
     float4 blo = ch.y >= 0 ? imin[ch.y] : lmin[~ch.y], bhi = ch.y >= 0 ? imax[ch.y] : lmax[~ch.y];
     int el = encode_child(ch.x, ranges, new_slot, leaf_size), er = encode_child(ch.y, ranges, new_slot, leaf_size);
     const float3 ac = box_centre(alo, ahi), ah = box_half(alo, ahi, ac), bc = box_centre(blo, bhi), bh = box_half(blo, bhi, bc);
-    nodes[4 * (size_t)i + 0] = make_float4(ac.x, ac.y, ac.z, ah.x);
-    nodes[4 * (size_t)i + 1] = make_float4(ah.y, ah.z, bc.x, bc.y);
-    nodes[4 * (size_t)i + 2] = make_float4(bc.z, bh.x, bh.y, bh.z);
+    // pair order of node_test() (rt_device.cuh): (L.c.x,L.c.y | L.c.z,R.c.z) (R.c.x,R.c.y | L.h.x,L.h.y) (L.h.z,R.h.z | R.h.x,R.h.y)
+    nodes[4 * (size_t)i + 0] = make_float4(ac.x, ac.y, ac.z, bc.z);
+    nodes[4 * (size_t)i + 1] = make_float4(bc.x, bc.y, ah.x, ah.y);
+    nodes[4 * (size_t)i + 2] = make_float4(ah.z, bh.z, bh.x, bh.y);
     nodes[4 * (size_t)i + 3] = make_float4(__int_as_float(el), __int_as_float(er), 0.f, 0.f);
 }
 
@@ -434,17 +435,22 @@ __global__ void emit_single(const float4* lmin, const float4* lmax, float4* node
 {
     float4 lo = lmin[0], hi = lmax[0];
     const float3 c = box_centre(lo, hi), h = box_half(lo, hi, c);
-    nodes[0] = make_float4(c.x, c.y, c.z, h.x);
-    nodes[1] = make_float4(h.y, h.z, 0.f, 0.f);
-    nodes[2] = make_float4(0.f, -INFINITY, -INFINITY, -INFINITY);     // right child: empty box (never hit)
+    nodes[0] = make_float4(c.x, c.y, c.z, 0.f);
+    nodes[1] = make_float4(0.f, 0.f, h.x, h.y);
+    nodes[2] = make_float4(h.z, -INFINITY, -INFINITY, -INFINITY);     // right child: empty box (never hit)
     nodes[3] = make_float4(__int_as_float(~0), __int_as_float(~0), 0.f, 0.f);
 }
 
 // Stream-ordered allocation from the device's default pool (rt_create raises its release
 // threshold, so repeated uploads reuse the same blocks instead of paying cudaMalloc/cudaFree).
 static thread_local cudaStream_t g_alloc_stream = nullptr;
+static thread_local cudaMemPool_t g_alloc_pool = nullptr;     // the context's own pool (the device's default pool is left alone)
+cudaError_t pool_alloc(void** p, size_t bytes, cudaStream_t s)
+{
+    return g_alloc_pool ? cudaMallocFromPoolAsync(p, bytes ? bytes : 1, g_alloc_pool, s) : cudaMallocAsync(p, bytes ? bytes : 1, s);
+}
 template <typename T>
-cudaError_t dalloc(T** p, size_t n) { return cudaMallocAsync((void**)p, (n ? n : 1) * sizeof(T), g_alloc_stream); }
+cudaError_t dalloc(T** p, size_t n) { return pool_alloc((void**)p, (n ? n : 1) * sizeof(T), g_alloc_stream); }
 
 } // namespace
 
@@ -469,7 +475,7 @@ cudaError_t build_scene(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns
 {
     out.release();
     out.stream = stream;
-    g_alloc_stream = stream;
+    g_alloc_stream = stream; g_alloc_pool = out.pool;
     cudaError_t err = cudaSuccess;
     std::vector<uint32_t> tri_start(nm + 1, 0);
     for (uint32_t m = 0; m < nm; m++) tri_start[m + 1] = tri_start[m] + meshes[m].triangles;
@@ -520,7 +526,7 @@ cudaError_t build_scene(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns
         setup_prims<<<nb, T, 0, stream>>>(rs, hot, out.c0, out.c1, out.c2, out.c3, out.c4, out.c5, bmin, bmax, d_bounds);
         morton_keys<<<nb, T, 0, stream>>>(n, bmin, bmax, d_bounds, keys, ids);
         RT_TRY(cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, keys, keys2, ids, ids2, (int)n, 0, 63, stream));
-        RT_TRY(cudaMallocAsync(&cub_tmp, cub_bytes ? cub_bytes : 1, stream));
+        RT_TRY(pool_alloc(&cub_tmp, cub_bytes, stream));
         RT_TRY(cub::DeviceRadixSort::SortPairs(cub_tmp, cub_bytes, keys, keys2, ids, ids2, (int)n, 0, 63, stream));
         gather_boxes<<<nb, T, 0, stream>>>(n, ids2, bmin, bmax, lmin, lmax);
         if (n == 1) {
@@ -537,7 +543,7 @@ cudaError_t build_scene(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns
                 RT_TRY(dalloc(&cloA, n)); RT_TRY(dalloc(&chiA, n)); RT_TRY(dalloc(&cloB, n)); RT_TRY(dalloc(&chiB, n));
                 RT_TRY(dalloc(&pflags, n)); RT_TRY(dalloc(&ppos, n)); RT_TRY(dalloc(&d_tot, 2));
                 RT_TRY(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, pflags, ppos, (int)n, stream));
-                RT_TRY(cudaMallocAsync(&scan_tmp, scan_bytes ? scan_bytes : 1, stream));
+                RT_TRY(pool_alloc(&scan_tmp, scan_bytes, stream));
                 ploc_init<<<nb, T, 0, stream>>>((int)n, lmin, lmax, cidA, cloA, chiA);
                 RT_TRY(dalloc(&d_state, 4));
                 int h_state[4] = {(int)n, 0, 0, 0};              // clusters left, nodes created, force flag, rounds done

@@ -44,7 +44,7 @@ combine_kernel(PeerSet ps, float4* __restrict__ out, uchar4* __restrict__ out8, 
             acc = any ? make_float4(acc.x + w.x, acc.y + w.y, acc.z + w.z, acc.w + w.w) : w;
             any = true;
         }
-        if (!any) { if (!TONEMAP) continue; acc = out[i]; }               // no shard owns this pixel: keep what the result image holds
+        if (!any) acc = ps.p[0].accum[i];                                  // no shard owns this pixel: the first context's own value
         if (TONEMAP) {
             const float a = fminf(fmaxf(acc.w, 0.0f), 1.0f);
             out8[i] = make_uchar4((unsigned char)srgb8_of(acc.x), (unsigned char)srgb8_of(acc.y), (unsigned char)srgb8_of(acc.z),

@@ -25,9 +25,11 @@
 //    point sampling through the texture path, bilinear weights applied in the kernel so the
 //    result is reproducible bit for bit (rt_shade.cuh).
 //  BVH nodes, 64 B each (both children's boxes live in the parent, one fetch = two tests):
-//    boxes as centre c / half extent h (rounded outward), which makes the slab test select-free:
-//    n[4*i+0] = (L.c.xyz, L.h.x)  n[4*i+1] = (L.h.yz, R.c.xy)
-//    n[4*i+2] = (R.c.z, R.h.xyz)  n[4*i+3] = (left, right, 0, 0) as int bits
+//    boxes as centre c / half extent h (rounded outward), which makes the slab test select-free;
+//    the twelve numbers are ordered in the 64-bit pairs the packed FP32 instructions of sm_100
+//    (FFMA2 / FADD2: two independent IEEE operations per issue slot) consume, see node_test():
+//    n[4*i+0] = (L.c.x, L.c.y | L.c.z, R.c.z)  n[4*i+1] = (R.c.x, R.c.y | L.h.x, L.h.y)
+//    n[4*i+2] = (L.h.z, R.h.z | R.h.x, R.h.y)  n[4*i+3] = (left, right, 0, 0) as int bits
 //    child >= 0: inner node index; child < 0: leaf, ~child = (first_slot << 3) | (count - 1)
 #pragma once
 #include <cuda_runtime.h>
@@ -81,6 +83,7 @@ struct LaunchParams {
     uint32_t width, height;
     int32_t bounces, rpp, toggle;
     int32_t first_frame;       // params.frames of the first fused dispatch
+    int32_t blend0;            // running-mean index of the first fused dispatch (this rank's own count): dispatch fi blends with weight 1/(blend0 + fi + 1) when blend0 + fi >= 1
     uint32_t n_frames;         // fused dispatches (frame stride = frame_world)
     uint32_t tile_rank, tile_world;
     uint32_t frame_world;      // stride between frames rendered by this rank
@@ -97,6 +100,76 @@ __device__ __forceinline__ void ldg256(const float4* p, float4& a, float4& b)
 {
     asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                  : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w) : "l"(p));
+}
+
+// ---- packed binary32 pairs (sm_100a FFMA2 / FADD2): two independent, correctly rounded operations
+// per instruction on an aligned 64-bit register pair; a scalar operand is broadcast by the hardware.
+typedef unsigned long long f2_t;
+__device__ __forceinline__ f2_t f2_pack(float lo, float hi) { return (f2_t)__float_as_uint(lo) | ((f2_t)__float_as_uint(hi) << 32); }
+__device__ __forceinline__ float f2_lo(f2_t v) { return __uint_as_float((unsigned)(v & 0xffffffffull)); }
+__device__ __forceinline__ float f2_hi(f2_t v) { return __uint_as_float((unsigned)(v >> 32)); }
+__device__ __forceinline__ f2_t f2_fma(f2_t a, f2_t b, f2_t c) { f2_t r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+__device__ __forceinline__ f2_t f2_add(f2_t a, f2_t b) { f2_t r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f2_t f2_sub(f2_t a, f2_t b) { f2_t r; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+// the same 256-bit read-only load as ldg256, delivered as four 64-bit pairs
+__device__ __forceinline__ void ldg256_f2(const float4* p, f2_t& a, f2_t& b, f2_t& c, f2_t& d)
+{
+    asm volatile("ld.global.nc.v4.b64 {%0,%1,%2,%3}, [%4];" : "=l"(a), "=l"(b), "=l"(c), "=l"(d) : "l"(p));
+}
+
+// Per-ray constants of the slab test against boxes stored as centre c / half extent h: along an axis the ray is
+// inside the padded slab for t in [a - b, a + b], a = c * (1/d) - o/d, b = (h + pad) * |1/d|.  Not parity-relevant
+// (conservative culling only; DESIGN.md "Conservative culling").
+struct RaySlab {
+    f2_t inv_xy, noi_xy, ainv_xy, pi_xy;      // (1/d, -o/d, |1/d|, pad*|1/d|) for x and y
+    float inv_z, noi_z, ainv_z, pi_z;         // ... and z (broadcast into both halves of a pair by the instruction)
+};
+__device__ __forceinline__ void slab_setup(RaySlab& s, float3 ro, float3 rd, float max_abs, float pad_scale)
+{
+    const float ix = __fdividef(1.0f, rd.x), iy = __fdividef(1.0f, rd.y), iz = __fdividef(1.0f, rd.z);
+    const float pad = pad_scale * fmaxf(fmaxf(max_abs, fabsf(ro.x)), fmaxf(fabsf(ro.y), fabsf(ro.z)));
+    const float ax = fabsf(ix), ay = fabsf(iy), az = fabsf(iz);
+    s.inv_xy = f2_pack(ix, iy); s.inv_z = iz;
+    s.noi_xy = f2_pack(-(ro.x * ix), -(ro.y * iy)); s.noi_z = -(ro.z * iz);
+    s.ainv_xy = f2_pack(ax, ay); s.ainv_z = az;
+    s.pi_xy = f2_pack(pad * ax, pad * ay); s.pi_z = pad * az;
+}
+// One node visit = both children's slab tests: 2 x LDG.256, 6 FFMA2 + 6 FADD2 (instead of 12 FFMA + 12 FADD),
+// 4 two-input + 4 three-input min/max.  Entry / exit distances clamped to [0, cull]; a child is hit when tn <= tf.
+__device__ __forceinline__ void node_test(const float4* np, const RaySlab& s, float cull,
+                                          float& ltn, float& ltf, float& rtn, float& rtf, int& cl, int& cr)
+{
+    f2_t a0, a1, a2, a3, b0, b1, b2, b3;
+    ldg256_f2(np, a0, a1, a2, a3); ldg256_f2(np + 2, b0, b1, b2, b3);
+    cl = (int)(unsigned)(b2 & 0xffffffffull); cr = (int)(unsigned)(b2 >> 32);
+#ifdef RT_SCALAR_SLABS                               // A/B build: the same test with scalar FFMA / FADD
+    {
+        const float ix = f2_lo(s.inv_xy), iy = f2_hi(s.inv_xy), nx = f2_lo(s.noi_xy), ny = f2_hi(s.noi_xy);
+        const float ax = f2_lo(s.ainv_xy), ay = f2_hi(s.ainv_xy), px = f2_lo(s.pi_xy), py = f2_hi(s.pi_xy);
+        const float lax = __fmaf_rn(f2_lo(a0), ix, nx), lay = __fmaf_rn(f2_hi(a0), iy, ny), laz = __fmaf_rn(f2_lo(a1), s.inv_z, s.noi_z);
+        const float rax = __fmaf_rn(f2_lo(a2), ix, nx), ray_ = __fmaf_rn(f2_hi(a2), iy, ny), raz = __fmaf_rn(f2_hi(a1), s.inv_z, s.noi_z);
+        const float lbx = __fmaf_rn(f2_lo(a3), ax, px), lby = __fmaf_rn(f2_hi(a3), ay, py), lbz = __fmaf_rn(f2_lo(b0), s.ainv_z, s.pi_z);
+        const float rbx = __fmaf_rn(f2_lo(b1), ax, px), rby = __fmaf_rn(f2_hi(b1), ay, py), rbz = __fmaf_rn(f2_hi(b0), s.ainv_z, s.pi_z);
+        ltn = fmaxf(fmaxf(lax - lbx, lay - lby), fmaxf(laz - lbz, 0.0f));
+        ltf = fminf(fminf(lax + lbx, lay + lby), fminf(laz + lbz, cull));
+        rtn = fmaxf(fmaxf(rax - rbx, ray_ - rby), fmaxf(raz - rbz, 0.0f));
+        rtf = fminf(fminf(rax + rbx, ray_ + rby), fminf(raz + rbz, cull));
+        return;
+    }
+#endif
+    const f2_t inv_zz = f2_pack(s.inv_z, s.inv_z), noi_zz = f2_pack(s.noi_z, s.noi_z);
+    const f2_t ainv_zz = f2_pack(s.ainv_z, s.ainv_z), pi_zz = f2_pack(s.pi_z, s.pi_z);
+    const f2_t P0 = f2_fma(a0, s.inv_xy, s.noi_xy);      // (L.a.x, L.a.y)
+    const f2_t P1 = f2_fma(a1, inv_zz, noi_zz);          // (L.a.z, R.a.z)
+    const f2_t P2 = f2_fma(a2, s.inv_xy, s.noi_xy);      // (R.a.x, R.a.y)
+    const f2_t Q0 = f2_fma(a3, s.ainv_xy, s.pi_xy);      // (L.b.x, L.b.y)
+    const f2_t Q1 = f2_fma(b0, ainv_zz, pi_zz);          // (L.b.z, R.b.z)
+    const f2_t Q2 = f2_fma(b1, s.ainv_xy, s.pi_xy);      // (R.b.x, R.b.y)
+    const f2_t N0 = f2_sub(P0, Q0), F0 = f2_add(P0, Q0), N1 = f2_sub(P1, Q1), F1 = f2_add(P1, Q1), N2 = f2_sub(P2, Q2), F2 = f2_add(P2, Q2);
+    ltn = fmaxf(fmaxf(f2_lo(N0), f2_hi(N0)), fmaxf(f2_lo(N1), 0.0f));
+    ltf = fminf(fminf(f2_lo(F0), f2_hi(F0)), fminf(f2_lo(F1), cull));
+    rtn = fmaxf(fmaxf(f2_lo(N2), f2_hi(N2)), fmaxf(f2_hi(N1), 0.0f));
+    rtf = fminf(fminf(f2_lo(F2), f2_hi(F2)), fminf(f2_hi(F1), cull));
 }
 
 // ---- vector helpers (the fused forms are the arithmetic contract's) -----

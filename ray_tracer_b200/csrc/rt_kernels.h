@@ -35,11 +35,12 @@ namespace rt {
 #define RT_QUEUE_GUIDE 20ull      // grab size = remaining items / (warps x this), clamped to [32, RT_QUEUE_CHUNK]
 #endif
 
-// trace (persistent warps over the (pixel, dispatch) item queue) + blend (running mean of the
-// staged dispatches into `accum`). `staging` holds lp.n_frames planes of W*H float4.
+// trace (persistent warps over the item queue).  fold = true: items are pixels, the kernel applies the running mean
+// to `accum` itself (staging unused, may be null); fold = false: items are (pixel, dispatch) pairs written to
+// `staging` (lp.n_frames planes of W*H float4) and blend_kernel folds them into `accum`.
 cudaError_t launch_trace(const SceneDev& sc, const CameraDev& cam, const LaunchParams& lp, float4* staging, float4* accum,
                          uint32_t* primary_ids, unsigned long long* counters, unsigned long long* queue,
-                         bool brute, bool detail, int n_sms, cudaStream_t stream);
+                         bool brute, bool detail, bool fold, int n_sms, cudaStream_t stream);
 
 // Device-resident scene: SoA primitive arrays + LBVH, built on the GPU from the AoS records.
 struct SceneBuffers {
@@ -48,6 +49,7 @@ struct SceneBuffers {
     float4 *c3 = nullptr, *c4 = nullptr, *c5 = nullptr;   // texture extension (uvs + edges), only when has_tex
     bool has_tex = false;
     cudaStream_t stream = nullptr;  // the arrays are stream-ordered allocations on this stream
+    cudaMemPool_t pool = nullptr;   // ... out of the context's private pool (nullptr: the device's default pool)
     // Build state kept for refit_scene (rt_update_records): the device copies of the caller's records,
     // the id-order hot records and bounds, the Morton-order permutation and the hierarchy's topology.
     struct Keep {
@@ -112,5 +114,16 @@ struct PeerSet { PeerSrc p[RT_MAX_PEERS]; uint32_t n; };
 // out (RGBA32F, may alias p[0].accum) or, when rgba8 != nullptr, the tone-mapped image (out is then only read
 // for pixels no shard owns); runs on `stream` of the device that owns out / rgba8.
 cudaError_t launch_combine(const PeerSet& ps, float4* out, uint8_t* rgba8, uint32_t width, uint32_t height, int n_sms, cudaStream_t stream);
+
+// ---- multi-process image combine over NCCL (rt_comm.cu) ------------------------------------------
+struct ShardRec { uint32_t tile_rank, tile_world, frame_rank, frame_world, count, pad[3]; };   // count: frames in the rank's running mean
+struct Comm;
+const char* comm_unique_id(void* id128);                                   // nullptr on success, else the error text
+const char* comm_create(Comm** out, int n_ranks, int rank, const void* id128);
+void comm_destroy(Comm* c);
+int comm_rank(const Comm* c);
+int comm_size(const Comm* c);
+const char* comm_combine(Comm* c, const ShardRec& mine, int root, const float4* accum, float4* out, uint8_t* out8,
+                         uint32_t width, uint32_t height, int n_sms, cudaStream_t stream);
 
 } // namespace rt

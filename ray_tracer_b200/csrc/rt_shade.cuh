@@ -104,14 +104,18 @@ __device__ __forceinline__ float4 environment_light(float3 d)
     return make_float4(mix1(0.35f, sky.x, g2s) + s, mix1(0.3f, sky.y, g2s) + s, mix1(0.35f, sky.z, g2s) + s, mix1(0.0f, sky.w, g2s) + s);
 }
 
-// wgsl:307-308; strict mode saturates the f32->u32 conversion (WGSL rule)
-__device__ __forceinline__ uint32_t pixel_seed(uint32_t x, uint32_t y, uint32_t w, uint32_t h, int32_t frames)
+// wgsl:307-308.  The f32 -> u32 conversion of a value >= 2^32 (3840x2160: every row from 518 on):
+//   seed_mode 0 "strict": saturates to 0xFFFFFFFF — the WGSL rule; those pixels then share one RNG stream per dispatch;
+//   seed_mode 1 "wide"  : wraps modulo 2^32 (the float is an exact integer there) — what a SPIR-V OpConvertFToU, which is
+//                         undefined out of range, may equally do; identical to strict wherever the value is below 2^32.
+__device__ __forceinline__ uint32_t pixel_seed(uint32_t x, uint32_t y, uint32_t w, uint32_t h, int32_t frames, int32_t seed_mode)
 {
     float px = (float)x * (float)w;
     float py = (float)y * (float)h;
     float lin = py * (float)w + px;
     uint32_t af = (frames < 0) ? (0u - (uint32_t)frames) : (uint32_t)frames;
-    return __float2uint_rz(lin) + af * 71939u;
+    const uint32_t base = (seed_mode == 1) ? (uint32_t)__float2ull_rz(lin) : __float2uint_rz(lin);
+    return base + af * 71939u;
 }
 
 // Work item g -> (pixel, dispatch): items are numbered tile-major, dispatch-minor, 32 pixels (an 8x4
@@ -124,6 +128,17 @@ __device__ __forceinline__ bool decode_item(const LaunchParams& lp, uint64_t g, 
     uint32_t wt;
     if ((tf >> 32) == 0ull) { wt = lp.div_frames.div((uint32_t)tf); fi = (uint32_t)tf - wt * lp.n_frames; }
     else { fi = (uint32_t)(tf % lp.n_frames); wt = (uint32_t)(tf / lp.n_frames); }
+    const uint32_t t = (wt >> 1) * lp.tile_world + lp.tile_rank;
+    const uint32_t ty = lp.div_tiles_x.div(t), tx = t - ty * lp.tiles_x;
+    px = tx * 8u + (pos & 7u);
+    py = ty * 8u + (wt & 1u) * 4u + (pos >> 3);
+    return px < lp.width && py < lp.height;
+}
+// FOLD items: work item g -> pixel (one item per pixel of this rank's tiles, all fused dispatches), same tile numbering.
+__device__ __forceinline__ bool decode_pixel(const LaunchParams& lp, uint64_t g, uint32_t& px, uint32_t& py)
+{
+    const uint32_t pos = (uint32_t)(g & 31ull);
+    const uint32_t wt = (uint32_t)(g >> 5);
     const uint32_t t = (wt >> 1) * lp.tile_world + lp.tile_rank;
     const uint32_t ty = lp.div_tiles_x.div(t), tx = t - ty * lp.tiles_x;
     px = tx * 8u + (pos & 7u);

@@ -26,14 +26,27 @@
 
 namespace rt {
 
+#ifdef RT_LANE_STATS
+// tuning builds only (scripts/build_variant.sh stats "-DRT_LANE_STATS"): where the lanes of a warp are while it runs
+// the node loop / leaf loop / SHADE, summed over the launch; read with rt_debug_lane_stats (not part of the ABI).
+__device__ unsigned long long g_lane_stats[16];
+#define LANE_STAT(k, pred) do { const unsigned b_ = __ballot_sync(0xffffffffu, (pred)); if ((threadIdx.x & 31u) == 0) ls[k] += __popc(b_); } while (0)
+#else
+#define LANE_STAT(k, pred) do { } while (0)
+#endif
+
 // ---- the trace kernel ---------------------------------------------------------------------
-// Work item = one (pixel, dispatch) pair: the rpp+1 camera paths of one pixel in one
-// reference dispatch, whose sum/rpp ("frag", wgsl:326) goes to that dispatch's staging plane.
-// Items are numbered tile-major, dispatch-minor, 32 pixels (an 8x4 tile) at a time.
-// ---- the trace kernel ---------------------------------------------------------------------
-// Work item = one (pixel, dispatch) pair: the rpp+1 camera paths of one pixel in one
-// reference dispatch, whose sum/rpp ("frag", wgsl:326) goes to that dispatch's staging plane.
-// Items are numbered tile-major, dispatch-minor, 32 pixels (an 8x4 tile) at a time.
+// Work item, FOLD = true (default): one PIXEL with all the dispatches fused into the launch.  The lane
+// that owns the pixel runs its dispatches in order and applies the reference's progressive store
+// (wgsl:59-66: running mean with weight 1/(frames+1)) to the accumulation image itself, one
+// read-modify-write of 16 bytes per dispatch that stays in L1/L2 — no staging planes, no blend
+// kernel, the only DRAM traffic of a launch is the image read once and written once.  The store is
+// order-dependent per pixel, which is why one lane owns the pixel.
+// Work item, FOLD = false (RT_OPT_ITEM_MODE = 1, and the wavefront kernels): one (pixel, dispatch)
+// pair whose sum/rpp ("frag", wgsl:326) goes to that dispatch's staging plane; blend_kernel folds the
+// planes in dispatch order afterwards.  Finer items (a better tail on very short launches) for
+// 32 B per pixel per dispatch of DRAM traffic.
+// Items are numbered tile-major, 32 pixels (an 8x4 tile) at a time.
 //
 // Each warp alternates between two sections:
 //   SHADE    — lanes whose traversal has ended shade the hit (or the sky), finish / fetch
@@ -44,6 +57,9 @@ namespace rt {
 //              primitives are tested with most lanes busy.
 // The warp goes back to SHADE when enough lanes have finished their ray (sched_s_min), the
 // others keep their traversal state (node, stack, closest hit) across the switch.
+#ifndef RT_PARK2
+#define RT_PARK2 0                   // 1: a lane may park two leaves before it stops descending (A/B)
+#endif
 #ifndef RT_NODE_U2
 #define RT_NODE_U2 1                 // lanes able to step for a second / third node step on the same warp vote
 #endif
@@ -55,9 +71,25 @@ namespace rt {
 #endif
 #define RT_EMPTY 0x7fffffff                        // "no current node": traversal stack exhausted
 
-template <bool BRUTE, bool DETAIL, bool TEX, bool PF>
+// wgsl:59-66 for one dispatch of one pixel: `frames >= 1` blends with weight 1/(frames+1), else overwrites.
+// (frames of the fi-th fused dispatch = first_frame + fi * frame_world; its weight index counts this rank's own
+// dispatches: blend0 + fi, see LaunchParams.)
+__device__ __forceinline__ void fold_store(const LaunchParams& lp, float4* accum, uint32_t pix, uint32_t fi, float4 fr)
+{
+    const int32_t blend = lp.blend0 + (int32_t)fi;
+    if (blend >= 1) {
+        const float4 acc = accum[pix];
+        const float weight = 1.0f / (float)(blend + 1);
+        const float om = 1.0f - weight;
+        accum[pix] = make_float4(acc.x * om + fr.x * weight, acc.y * om + fr.y * weight, acc.z * om + fr.z * weight, acc.w * om + fr.w * weight);
+    } else {
+        accum[pix] = fr;
+    }
+}
+
+template <bool BRUTE, bool DETAIL, bool TEX, bool PF, bool FOLD>
 __global__ void __launch_bounds__(RT_BLOCK_THREADS, RT_MIN_BLOCKS)
-trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ staging,
+trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ staging, float4* accum,
              uint32_t* __restrict__ primary_ids, unsigned long long* __restrict__ counters,
              unsigned long long* __restrict__ queue)
 {
@@ -65,11 +97,14 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
     int stack[RT_STACK];                           // local memory: lane-interleaved by the hardware, only touched levels occupy L1
     stack[0] = RT_EMPTY;                           // sentinel under every traversal (sp starts at 1): a pop needs no emptiness test
 
-    const uint64_t n_items = (uint64_t)lp.n_warp_tiles * lp.n_frames * 32ull;
+    const uint64_t n_items = (uint64_t)lp.n_warp_tiles * (FOLD ? 1u : lp.n_frames) * 32ull;
     const unsigned long long guide = (unsigned long long)gridDim.x * (RT_BLOCK_THREADS / 32) * RT_QUEUE_GUIDE;   // warps x K
     const size_t plane = (size_t)lp.width * lp.height;
     const float sw = (float)lp.width, sh = (float)lp.height, rppf = (float)lp.rpp;
     uint32_t n_rays = 0, n_samples = 0, n_nodes = 0, n_tri = 0, n_sph = 0, n_hits = 0;
+#ifdef RT_LANE_STATS
+    unsigned long long ls[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, ls8 = 0;
+#endif
 
     uint64_t pool_next = 0, pool_end = 0;          // warp-uniform: items granted to this warp
     bool exhausted = false;                        // warp-uniform: the global queue is empty
@@ -82,7 +117,8 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
     int32_t j = 0, seg = 0;
     float4 incoming = make_float4(0.f, 0.f, 0.f, 0.f), color = incoming;
     float3 ro = f3(0.f, 0.f, 0.f), rd = ro;        // current ray
-    float3 inv = ro, noi = ro, ainv = ro, pi = ro; // slab setup of the current ray: 1/d, -o/d, |1/d|, pad*|1/d|
+    RaySlab slab;                                  // slab-test constants of the current ray: 1/d, -o/d, |1/d|, pad*|1/d|
+    slab.inv_xy = slab.noi_xy = slab.ainv_xy = slab.pi_xy = 0ull; slab.inv_z = slab.noi_z = slab.ainv_z = slab.pi_z = 0.f;
     // item state touched once per camera path lives in shared memory (keeps the traversal loops at 64 registers)
     __shared__ float4 s_total[RT_BLOCK_THREADS];   // sum of the item's finished paths (wgsl:323)
     __shared__ uint2 s_item[RT_BLOCK_THREADS];     // (pixel index, dispatch index within the launch)
@@ -94,10 +130,15 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
     float cull = RT_FLT_MAX;                       // best.dst with slack: the distance beyond which a subtree is skipped (see RT_CULL_SLACK)
     int node = RT_EMPTY, sp = 0;                   // current node (inner >= 0, leaf < 0, or RT_EMPTY) / stack height
     uint32_t leaf_first = 0, leaf_count = 0;       // parked leaf primitives
+#if RT_PARK2
+    int leaf2 = 0;                                 // a second parked leaf (encoded child word, < 0), 0 = none
+#endif
 
     for (;;) {
         // ======================= SHADE section =======================
         {
+            LANE_STAT(9, lane == 0); LANE_STAT(10, shading && has_item && traced); LANE_STAT(11, shading && has_item && traced && best.id != RT_MISS);
+            LANE_STAT(12, !shading);
             bool need_path = false;
             if (shading && has_item) {
                 if (traced) {
@@ -118,9 +159,20 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
                 } else {
                     need_path = true;                                                              // fresh item
                 }
-                if (need_path && j > lp.rpp) {
-                    staging[(size_t)fi * plane + pix] = frag_of_total(lp, total);                       // wgsl:326
-                    has_item = false; need_path = false;
+                if (need_path && j > lp.rpp) {                                                     // the dispatch's frag is complete, wgsl:326
+                    const float4 fr = frag_of_total(lp, total);
+                    if (FOLD) {
+                        fold_store(lp, accum, pix, fi, fr);                                        // wgsl:59-66
+                        fi++;
+                        if (fi < lp.n_frames) {                                                    // next dispatch of this pixel
+                            const uint32_t py = lp.div_width.div(pix), px = pix - py * lp.width;
+                            rng = pixel_seed(px, py, lp.width, lp.height, lp.first_frame + (int32_t)(fi * lp.frame_world), lp.seed_mode);
+                            j = 0; total = make_float4(0.f, 0.f, 0.f, 0.f);
+                        } else { has_item = false; need_path = false; }
+                    } else {
+                        staging[(size_t)fi * plane + pix] = fr;
+                        has_item = false; need_path = false;
+                    }
                 }
             }
             // ---- take the next item (warp-uniform control flow) ----
@@ -131,12 +183,14 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
                     // 8x4 tile of one dispatch (32 items) near the end, so that no warp is left holding a
                     // large pool of heavy pixels when the queue runs dry (a heavy 128-item pool takes one
                     // warp milliseconds: the launch's fixed cost went from 3.3 ms to under 1 ms on C3)
-                    unsigned long long g = 0, chunk = 0;
+                    unsigned long long g = 0, chunk = 32ull;                    // FOLD: one 8x4 tile (32 pixels x all dispatches) per grab
                     if (lane == 0) {
-                        const unsigned long long cur = *(volatile unsigned long long*)queue;
-                        const unsigned long long rem = cur < n_items ? n_items - cur : 0ull;
-                        chunk = (rem / guide) & ~31ull;
-                        chunk = chunk < 32ull ? 32ull : (chunk > RT_QUEUE_CHUNK ? RT_QUEUE_CHUNK : chunk);
+                        if (!FOLD) {
+                            const unsigned long long cur = *(volatile unsigned long long*)queue;
+                            const unsigned long long rem = cur < n_items ? n_items - cur : 0ull;
+                            chunk = (rem / guide) & ~31ull;
+                            chunk = chunk < 32ull ? 32ull : (chunk > RT_QUEUE_CHUNK ? RT_QUEUE_CHUNK : chunk);
+                        }
                         g = atomicAdd(queue, chunk);
                     }
                     g = __shfl_sync(0xffffffffu, g, 0); chunk = __shfl_sync(0xffffffffu, chunk, 0);
@@ -148,13 +202,18 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
                 const uint64_t avail = pool_end - pool_next;
                 if (mine && rank < avail) {
                     uint32_t px, py;
-                    if (decode_item(lp, pool_next + rank, px, py, fi)) {         // else: outside the image, ask again
+                    bool inside;
+                    if (FOLD) { inside = decode_pixel(lp, pool_next + rank, px, py); fi = 0; }
+                    else inside = decode_item(lp, pool_next + rank, px, py, fi);
+                    if (inside) {                                                // else: outside the image, ask again
                         pix = py * lp.width + px;
-                        rng = pixel_seed(px, py, lp.width, lp.height, lp.first_frame + (int32_t)(fi * lp.frame_world));
+                        rng = pixel_seed(px, py, lp.width, lp.height, lp.first_frame + (int32_t)(fi * lp.frame_world), lp.seed_mode);
                         j = 0; has_item = true; need_path = true;
                         total = make_float4(0.f, 0.f, 0.f, 0.f);
                         if (lp.rpp < 0) {                                        // wgsl:312 loop never runs
-                            staging[(size_t)fi * plane + pix] = make_float4(0.0f / rppf, 0.0f / rppf, 0.0f / rppf, 0.0f / rppf);
+                            const float4 z = make_float4(0.0f / rppf, 0.0f / rppf, 0.0f / rppf, 0.0f / rppf);
+                            if (FOLD) { for (uint32_t f = 0; f < lp.n_frames; f++) fold_store(lp, accum, pix, f, z); }
+                            else staging[(size_t)fi * plane + pix] = z;
                             has_item = false; need_path = false;
                         }
                     }
@@ -192,6 +251,9 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
                 // ---- start the traversal of (ro, rd): wgsl:234 ----
                 best.dst = RT_FLT_MAX; best.u = 0.0f; best.v = 0.0f; best.id = RT_MISS; cull = RT_FLT_MAX;
                 sp = 1; node = RT_EMPTY; leaf_count = 0;
+#if RT_PARK2
+                leaf2 = 0;
+#endif
                 if (lp.bounces < 0) {
                     total = total + incoming; j++;                // wgsl:233 loop never runs: the path ends untraced
                     traced = false;                               // stays "shading" as a fresh lane needing a path
@@ -201,14 +263,7 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
                 } else if (sc.root < 0) {
                     traced = true;                                // empty scene: immediate miss
                 } else {
-                    // slab setup for boxes stored as centre c / half extent h: along each axis the ray is
-                    // inside the padded slab for t in [a - b, a + b], a = (c - o)/d, b = (h + pad)/|d|.
-                    // Not parity-relevant (conservative culling only).
-                    inv = f3(__fdividef(1.0f, rd.x), __fdividef(1.0f, rd.y), __fdividef(1.0f, rd.z));
-                    const float pad = sc.pad_scale * fmaxf(fmaxf(sc.max_abs, fabsf(ro.x)), fmaxf(fabsf(ro.y), fabsf(ro.z)));
-                    ainv = f3(fabsf(inv.x), fabsf(inv.y), fabsf(inv.z));
-                    noi = f3(-(ro.x * inv.x), -(ro.y * inv.y), -(ro.z * inv.z));
-                    pi = f3(pad * ainv.x, pad * ainv.y, pad * ainv.z);
+                    slab_setup(slab, ro, rd, sc.max_abs, sc.pad_scale);
                     node = sc.root;
                     traced = true; shading = false;
                 }
@@ -223,25 +278,13 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
             const int cnt0 = __popc(__ballot_sync(0xffffffffu, !shading && node >= 0 && node != RT_EMPTY));
             const int thr = max(1, min(lp.sched_n_stay, (cnt0 + 1) >> 1));
             auto node_step = [&]() {
+                LANE_STAT(0, lane == 0); LANE_STAT(1, !shading && node >= 0 && node != RT_EMPTY); LANE_STAT(2, shading && !idle); LANE_STAT(3, !shading && node < 0);
+                LANE_STAT(4, !shading && node == RT_EMPTY && leaf_count != 0u); LANE_STAT(5, idle);
                 if (!shading && node >= 0 && node != RT_EMPTY) {
-                    const float4* np = sc.nodes + 4 * (size_t)node;
-                    float4 n0, n1, n2, n3;
-                    ldg256(np, n0, n1); ldg256(np + 2, n2, n3);
                     if (DETAIL) n_nodes++;
-                    // left: centre (n0.x,n0.y,n0.z) half (n0.w,n1.x,n1.y); right: centre (n1.z,n1.w,n2.x) half (n2.y,n2.z,n2.w).
-                    // 12 FFMA + 12 FADD on the fma pipe, 4 three-input min/max on the alu pipe (no sign selects).
-                    const float lax = __fmaf_rn(n0.x, inv.x, noi.x), lbx = __fmaf_rn(n0.w, ainv.x, pi.x);
-                    const float lay = __fmaf_rn(n0.y, inv.y, noi.y), lby = __fmaf_rn(n1.x, ainv.y, pi.y);
-                    const float laz = __fmaf_rn(n0.z, inv.z, noi.z), lbz = __fmaf_rn(n1.y, ainv.z, pi.z);
-                    const float rax = __fmaf_rn(n1.z, inv.x, noi.x), rbx = __fmaf_rn(n2.y, ainv.x, pi.x);
-                    const float ray_ = __fmaf_rn(n1.w, inv.y, noi.y), rby = __fmaf_rn(n2.z, ainv.y, pi.y);
-                    const float raz = __fmaf_rn(n2.x, inv.z, noi.z), rbz = __fmaf_rn(n2.w, ainv.z, pi.z);
-                    const float ltn = fmaxf(fmaxf(lax - lbx, lay - lby), fmaxf(laz - lbz, 0.0f));
-                    const float ltf = fminf(fminf(lax + lbx, lay + lby), fminf(laz + lbz, cull));
-                    const float rtn = fmaxf(fmaxf(rax - rbx, ray_ - rby), fmaxf(raz - rbz, 0.0f));
-                    const float rtf = fminf(fminf(rax + rbx, ray_ + rby), fminf(raz + rbz, cull));
+                    float ltn, ltf, rtn, rtf; int cl, cr;
+                    node_test(sc.nodes + 4 * (size_t)node, slab, cull, ltn, ltf, rtn, rtf, cl, cr);
                     const bool hl = ltn <= ltf, hr = rtn <= rtf;
-                    const int cl = __float_as_int(n3.x), cr = __float_as_int(n3.y);
                     if (hl && hr) {
                         const bool left_first = ltn <= rtn;
                         stack[sp++] = left_first ? cr : cl;
@@ -253,11 +296,24 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
                     } else if (hl) node = cl;
                     else if (hr) node = cr;
                     else node = stack[--sp];
+#if RT_PARK2
+                    if (node < 0) {                              // park the leaf (two slots), keep descending
+                        if (leaf_count == 0u) {
+                            const uint32_t leaf = (uint32_t)(~node);
+                            leaf_first = leaf >> 3; leaf_count = (leaf & 7u) + 1u;
+                            node = stack[--sp];
+                        } else if (leaf2 == 0) {
+                            leaf2 = node;
+                            node = stack[--sp];
+                        }
+                    }
+#else
                     if (node < 0 && leaf_count == 0u) {          // park the leaf, keep descending
                         const uint32_t leaf = (uint32_t)(~node);
                         leaf_first = leaf >> 3; leaf_count = (leaf & 7u) + 1u;
                         node = stack[--sp];
                     }
+#endif
                 }
             };
             for (;;) {
@@ -271,6 +327,7 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
             }
             // ---- leaf loop: test parked primitives, one per lane per step ----
             while (__ballot_sync(0xffffffffu, !shading && leaf_count != 0u)) {
+                LANE_STAT(6, lane == 0); LANE_STAT(7, !shading && leaf_count != 0u);
                 if (!shading && leaf_count != 0u) {
                     const float4* pr = sc.prims + 4 * (size_t)leaf_first;
                     float4 q0, q1;
@@ -282,6 +339,9 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
                     } else {
                         if (DETAIL) n_tri++;
                         float det;
+#ifdef RT_LANE_STATS
+                        ls8++;
+#endif
                         if (triangle_faces_ray(rd, xyz(q0), det)) {
                             float4 q2, q3;
                             ldg256(pr + 2, q2, q3);
@@ -290,11 +350,26 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
                     }
                     cull = best.dst * RT_CULL_SLACK;
                     leaf_first++;
+#if RT_PARK2
+                    if (--leaf_count == 0u) {
+                        if (leaf2 != 0) {                        // the second parked leaf moves up
+                            const uint32_t leaf = (uint32_t)(~leaf2);
+                            leaf_first = leaf >> 3; leaf_count = (leaf & 7u) + 1u;
+                            leaf2 = 0;
+                            if (node < 0) { leaf2 = node; node = stack[--sp]; }
+                        } else if (node < 0) {                   // a leaf was waiting in `node`
+                            const uint32_t leaf = (uint32_t)(~node);
+                            leaf_first = leaf >> 3; leaf_count = (leaf & 7u) + 1u;
+                            node = stack[--sp];
+                        }
+                    }
+#else
                     if (--leaf_count == 0u && node < 0) {        // a second leaf was waiting in `node`
                         const uint32_t leaf = (uint32_t)(~node);
                         leaf_first = leaf >> 3; leaf_count = (leaf & 7u) + 1u;
                         node = stack[--sp];
                     }
+#endif
                 }
             }
             // lanes with nothing left have their closest hit
@@ -315,6 +390,11 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
             ns += __shfl_xor_sync(0xffffffffu, ns, o); nh += __shfl_xor_sync(0xffffffffu, nh, o);
         }
     }
+#ifdef RT_LANE_STATS
+    for (int o = 16; o > 0; o >>= 1) ls8 += __shfl_xor_sync(0xffffffffu, ls8, o);
+    ls[8] = ls8;
+    if (lane == 0) for (int k = 0; k < 16; k++) atomicAdd(&g_lane_stats[k], ls[k]);
+#endif
     if (lane == 0) {
         atomicAdd(counters + 0, r);
         atomicAdd(counters + 1, s);
@@ -357,46 +437,66 @@ __global__ void blend_kernel(LaunchParams lp, const float4* __restrict__ staging
 }
 
 namespace {
-typedef void (*TraceFn)(SceneDev, CameraDev, LaunchParams, float4*, uint32_t*, unsigned long long*, unsigned long long*);
+typedef void (*TraceFn)(SceneDev, CameraDev, LaunchParams, float4*, float4*, uint32_t*, unsigned long long*, unsigned long long*);
 // PF: prefetch the postponed child of a two-hit node step into L1.  Pays while the hierarchy and the records fit the
 // caches (C3 +0.8 %, C4 +1.8 %, C2 +0.4 %); on C5 (1.1 M primitives, 140 MB of nodes + records, L1 data pipe at 85 %)
 // the extra requests cost 1.5 %, so the launcher picks the variant by scene size.
 #define RT_PF_MAX_PRIMS 262144u
-TraceFn trace_variant(bool brute, bool detail, bool tex, bool pf)
+template <bool FOLD>
+TraceFn trace_variant_t(bool brute, bool detail, bool tex, bool pf)
 {
     static const TraceFn table[12] = {
-        trace_kernel<false, false, false, false>, trace_kernel<false, false, true, false>, trace_kernel<false, true, false, false>, trace_kernel<false, true, true, false>,
-        trace_kernel<false, false, false, true>,  trace_kernel<false, false, true, true>,  trace_kernel<false, true, false, true>,  trace_kernel<false, true, true, true>,
-        trace_kernel<true, false, false, false>,  trace_kernel<true, false, true, false>,  trace_kernel<true, true, false, false>,  trace_kernel<true, true, true, false>};
+        trace_kernel<false, false, false, false, FOLD>, trace_kernel<false, false, true, false, FOLD>, trace_kernel<false, true, false, false, FOLD>, trace_kernel<false, true, true, false, FOLD>,
+        trace_kernel<false, false, false, true, FOLD>,  trace_kernel<false, false, true, true, FOLD>,  trace_kernel<false, true, false, true, FOLD>,  trace_kernel<false, true, true, true, FOLD>,
+        trace_kernel<true, false, false, false, FOLD>,  trace_kernel<true, false, true, false, FOLD>,  trace_kernel<true, true, false, false, FOLD>,  trace_kernel<true, true, true, false, FOLD>};
     return table[(brute ? 8 : (pf ? 4 : 0)) | (detail ? 2 : 0) | (tex ? 1 : 0)];
+}
+TraceFn trace_variant(bool brute, bool detail, bool tex, bool pf, bool fold)
+{
+    return fold ? trace_variant_t<true>(brute, detail, tex, pf) : trace_variant_t<false>(brute, detail, tex, pf);
 }
 } // namespace
 
-int trace_blocks_per_sm(bool brute, bool detail, bool tex, bool pf)
+int trace_blocks_per_sm(bool brute, bool detail, bool tex, bool pf, bool fold)
 {
     int n = 0;
-    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, trace_variant(brute, detail, tex, pf), RT_BLOCK_THREADS, 0);
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, trace_variant(brute, detail, tex, pf, fold), RT_BLOCK_THREADS, 0);
     return (e == cudaSuccess && n > 0) ? n : 1;
 }
 
+// fold = true: `accum` is updated in place by the kernel (staging unused); fold = false: the kernel fills the staging
+// planes and blend_kernel folds them into `accum`.
 cudaError_t launch_trace(const SceneDev& sc, const CameraDev& cam, const LaunchParams& lp, float4* staging, float4* accum,
                          uint32_t* primary_ids, unsigned long long* counters, unsigned long long* queue,
-                         bool brute, bool detail, int n_sms, cudaStream_t stream)
+                         bool brute, bool detail, bool fold, int n_sms, cudaStream_t stream)
 {
     if (lp.n_warp_tiles == 0 || lp.n_frames == 0) return cudaSuccess;
     cudaError_t e = cudaMemsetAsync(queue, 0, sizeof(unsigned long long), stream);
     if (e != cudaSuccess) return e;
     const bool tex = sc.c3 != nullptr && sc.n_tex != 0u;       // texture code only when the scene carries handles and a table is bound
-    const uint64_t warps_needed = ((uint64_t)lp.n_warp_tiles * lp.n_frames * 32ull + RT_QUEUE_CHUNK - 1) / RT_QUEUE_CHUNK;
+    const uint64_t n_items = (uint64_t)lp.n_warp_tiles * (fold ? 1u : lp.n_frames) * 32ull;
+    const uint64_t per_grab = fold ? 32ull : RT_QUEUE_CHUNK;
+    const uint64_t warps_needed = (n_items + per_grab - 1) / per_grab;
     const bool pf = !brute && sc.n_prims <= RT_PF_MAX_PRIMS;
-    uint64_t blocks = (uint64_t)n_sms * trace_blocks_per_sm(brute, detail, tex, pf);
+    uint64_t blocks = (uint64_t)n_sms * trace_blocks_per_sm(brute, detail, tex, pf, fold);
     const uint64_t cap = (warps_needed + RT_BLOCK_THREADS / 32 - 1) / (RT_BLOCK_THREADS / 32);
     if (blocks > cap) blocks = cap;
     dim3 grid((unsigned)blocks), block(RT_BLOCK_THREADS);
-    trace_variant(brute, detail, tex, pf)<<<grid, block, 0, stream>>>(sc, cam, lp, staging, primary_ids, counters, queue);
+    trace_variant(brute, detail, tex, pf, fold)<<<grid, block, 0, stream>>>(sc, cam, lp, staging, accum, primary_ids, counters, queue);
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
-    return launch_blend(lp, staging, accum, stream);
+    return fold ? cudaSuccess : launch_blend(lp, staging, accum, stream);
 }
+
+#ifdef RT_LANE_STATS
+extern "C" int rt_debug_lane_stats(unsigned long long* out16, int reset)
+{
+    unsigned long long z[16] = {0};
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e == cudaSuccess && out16) e = cudaMemcpyFromSymbol(out16, g_lane_stats, sizeof z);
+    if (e == cudaSuccess && reset) e = cudaMemcpyToSymbol(g_lane_stats, z, sizeof z);
+    return e == cudaSuccess ? 0 : -1;
+}
+#endif
 
 cudaError_t launch_blend(const LaunchParams& lp, const float4* staging, float4* accum, cudaStream_t stream)
 {

@@ -115,7 +115,9 @@ wave_trace(SceneDev sc, WaveDev wv, int n_stay, int refill_min)
     unsigned long long in_next = 0, in_end = 0;      // warp-uniform: the warp's current input chunk
     unsigned long long hit_pos = 0, hit_end = 0, miss_pos = 0, miss_end = 0;   // ... and its output chunks
     uint32_t slot = 0;
-    float3 ro = f3(0.f, 0.f, 0.f), rd = ro, inv = ro, noi = ro, ainv = ro, pi = ro;
+    float3 ro = f3(0.f, 0.f, 0.f), rd = ro;
+    RaySlab slab;
+    slab.inv_xy = slab.noi_xy = slab.ainv_xy = slab.pi_xy = 0ull; slab.inv_z = slab.noi_z = slab.ainv_z = slab.pi_z = 0.f;
     HitRec best; best.dst = RT_FLT_MAX; best.u = best.v = 0.f; best.id = RT_MISS;
     float cull = RT_FLT_MAX;                         // best.dst with slack (RT_CULL_SLACK, rt_kernels.h)
     int node = WV_EMPTY, sp = 1;
@@ -144,11 +146,7 @@ wave_trace(SceneDev sc, WaveDev wv, int n_stay, int refill_min)
                 if (BRUTE) leaf_count = sc.n_prims;
                 else if (sc.root >= 0) {
                     node = sc.root;
-                    inv = f3(__fdividef(1.0f, rd.x), __fdividef(1.0f, rd.y), __fdividef(1.0f, rd.z));
-                    const float pad = sc.pad_scale * fmaxf(fmaxf(sc.max_abs, fabsf(ro.x)), fmaxf(fabsf(ro.y), fabsf(ro.z)));
-                    ainv = f3(fabsf(inv.x), fabsf(inv.y), fabsf(inv.z));
-                    noi = f3(-(ro.x * inv.x), -(ro.y * inv.y), -(ro.z * inv.z));
-                    pi = f3(pad * ainv.x, pad * ainv.y, pad * ainv.z);
+                    slab_setup(slab, ro, rd, sc.max_abs, sc.pad_scale);
                 }
                 active = true;
                 n_rays++;
@@ -165,22 +163,10 @@ wave_trace(SceneDev sc, WaveDev wv, int n_stay, int refill_min)
             const int thr = max(1, min(n_stay, (cnt0 + 1) >> 1));
             while (__popc(__ballot_sync(0xffffffffu, active && node >= 0 && node != WV_EMPTY)) >= thr) {
                 if (active && node >= 0 && node != WV_EMPTY) {
-                    const float4* np = sc.nodes + 4 * (size_t)node;
-                    float4 n0, n1, n2, n3;
-                    ldg256(np, n0, n1); ldg256(np + 2, n2, n3);
                     if (DETAIL) n_nodes++;
-                    const float lax = __fmaf_rn(n0.x, inv.x, noi.x), lbx = __fmaf_rn(n0.w, ainv.x, pi.x);
-                    const float lay = __fmaf_rn(n0.y, inv.y, noi.y), lby = __fmaf_rn(n1.x, ainv.y, pi.y);
-                    const float laz = __fmaf_rn(n0.z, inv.z, noi.z), lbz = __fmaf_rn(n1.y, ainv.z, pi.z);
-                    const float rax = __fmaf_rn(n1.z, inv.x, noi.x), rbx = __fmaf_rn(n2.y, ainv.x, pi.x);
-                    const float ray_ = __fmaf_rn(n1.w, inv.y, noi.y), rby = __fmaf_rn(n2.z, ainv.y, pi.y);
-                    const float raz = __fmaf_rn(n2.x, inv.z, noi.z), rbz = __fmaf_rn(n2.w, ainv.z, pi.z);
-                    const float ltn = fmaxf(fmaxf(lax - lbx, lay - lby), fmaxf(laz - lbz, 0.0f));
-                    const float ltf = fminf(fminf(lax + lbx, lay + lby), fminf(laz + lbz, cull));
-                    const float rtn = fmaxf(fmaxf(rax - rbx, ray_ - rby), fmaxf(raz - rbz, 0.0f));
-                    const float rtf = fminf(fminf(rax + rbx, ray_ + rby), fminf(raz + rbz, cull));
+                    float ltn, ltf, rtn, rtf; int cl, cr;
+                    node_test(sc.nodes + 4 * (size_t)node, slab, cull, ltn, ltf, rtn, rtf, cl, cr);
                     const bool hl = ltn <= ltf, hr = rtn <= rtf;
-                    const int cl = __float_as_int(n3.x), cr = __float_as_int(n3.y);
                     if (hl && hr) {
                         const bool left_first = ltn <= rtn;
                         stack[sp++] = left_first ? cr : cl;
@@ -340,7 +326,7 @@ wave_miss(CameraDev cam, WaveDev wv, LaunchParams lp, float4* __restrict__ stagi
                     uint32_t px, py;
                     if (decode_item(lp, g, px, py, fi)) {                                  // else: outside the image, ask again
                         pix = py * lp.width + px;
-                        rng = pixel_seed(px, py, lp.width, lp.height, lp.first_frame + (int32_t)(fi * lp.frame_world));
+                        rng = pixel_seed(px, py, lp.width, lp.height, lp.first_frame + (int32_t)(fi * lp.frame_world), lp.seed_mode);
                         j = 0; has_item = true;
                         tot = make_float4(0.f, 0.f, 0.f, 0.f);
                         if (lp.rpp < 0) {                                                  // wgsl:312 loop never runs

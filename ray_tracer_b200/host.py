@@ -410,7 +410,8 @@ class Context:
 
     @staticmethod
     def combine(shards):
-        """Fold the shard contexts' images into shards[0]'s with one kernel over peer memory (rt_combine_peers)."""
+        """Fold the shard contexts' images into shards[0]'s combined image with one kernel over peer memory (rt_combine_peers);
+        shards[0].read_texture() / save_png() show it until that context renders again."""
         shards = list(shards)
         arr = (C.c_void_p * len(shards))(*[s._h for s in shards])
         shards[0]._ck(shards[0]._L.rth_context_combine(arr, len(shards)))

@@ -38,6 +38,7 @@ void Context::resize(uint32_t width, uint32_t height)
     if (width == 0 || height == 0) return;                     // context.rs:127
     scene.camera.aspect = (float)width / (float)height;        // :130
     check(rt_resize(ctx_, width, height), "rt_resize");        // :132 new texture
+    combined_from_.clear();
     params.width = width; params.height = height;
     params.frames = -1;                                        // :136
     check(rt_set_params(ctx_, &params), "rt_set_params");      // :138
@@ -74,7 +75,8 @@ void Context::save_png(const std::string& path, bool mirror_x)
 {
     const uint32_t W = params.width, H = params.height;
     std::vector<uint8_t> px((size_t)W * H * 4), out((size_t)W * H * 4);
-    check(rt_read_rgba8(ctx_, px.data(), px.size()), "rt_read_rgba8");
+    if (!combined_from_.empty()) check(rt_combine_peers_rgba8(combined_from_.data(), (uint32_t)combined_from_.size(), nullptr, px.data(), px.size()), "rt_combine_peers_rgba8");
+    else check(rt_read_rgba8(ctx_, px.data(), px.size()), "rt_read_rgba8");
     for (uint32_t y = 0; y < H; y++)                           // texture row 0 is the bottom image row
         for (uint32_t x = 0; x < W; x++)
             memcpy(&out[((size_t)(H - 1 - y) * W + (mirror_x ? W - 1 - x : x)) * 4], &px[((size_t)y * W + x) * 4], 4);
@@ -83,6 +85,7 @@ void Context::save_png(const std::string& path, bool mirror_x)
 
 void Context::render()
 {
+    combined_from_.clear();
     check(rt_dispatch(ctx_), "rt_dispatch");                   // context.rs:196-208
 }
 
@@ -99,6 +102,7 @@ void Context::run_frames(uint32_t n)
     params.frames += (int32_t)n;
     check(rt_set_camera(ctx_, &u), "rt_set_camera");
     check(rt_set_params(ctx_, &params), "rt_set_params");
+    combined_from_.clear();
     check(rt_render_frames(ctx_, first, n), "rt_render_frames");
 }
 
@@ -113,6 +117,7 @@ void Context::combine(const std::vector<Context*>& shards)
     std::vector<rt_ctx*> h;
     for (Context* c : shards) { if (!c) throw std::runtime_error("Context::combine: null shard"); h.push_back(c->ctx_); }
     shards[0]->check(rt_combine_peers(h.data(), (uint32_t)h.size(), nullptr), "rt_combine_peers");
+    shards[0]->combined_from_ = h;
 }
 
 void Context::set_scene(int id)
@@ -134,7 +139,8 @@ void Context::sync() { check(rt_sync(ctx_), "rt_sync"); }
 std::vector<float> Context::read_texture()
 {
     std::vector<float> out((size_t)params.width * params.height * 4);
-    check(rt_read_accum(ctx_, out.data(), out.size()), "rt_read_accum");
+    if (!combined_from_.empty()) check(rt_read_combined(ctx_, out.data(), out.size()), "rt_read_combined");
+    else check(rt_read_accum(ctx_, out.data(), out.size()), "rt_read_accum");
     return out;
 }
 
@@ -306,7 +312,9 @@ int rth_context_read_texture(void* c, float* out, size_t n)
 {
     RTH_TRY({
         rtb::Context* x = (rtb::Context*)c;
-        if (rt_read_accum(x->handle(), out, n) != RT_OK) throw std::runtime_error(rt_last_error(x->handle()));
+        std::vector<float> v = x->read_texture();
+        if (v.size() != n) throw std::runtime_error("rth_context_read_texture: size must be W*H*4");
+        memcpy(out, v.data(), n * sizeof(float));
     });
 }
 void* rth_context_handle(void* c) { return ((rtb::Context*)c)->handle(); }

@@ -156,7 +156,9 @@ public:
     void sync();
     // Several GPUs from one process (no reference counterpart): every shard context gets the same scene,
     // inputs and update()/run_frames() calls and renders only its share of the tiles / frames (rt_set_shard);
-    // combine() folds the shards' images into shards[0]'s with one kernel over NVLink peer memory (rt_combine_peers).
+    // combine() folds the shards' images into shards[0]'s combined image with one kernel over NVLink peer memory
+    // (rt_combine_peers); until shards[0] renders again, its read_texture() / save_png() show that image.  The shards'
+    // own accumulation images are untouched, so the same shards can go on rendering and be combined again.
     void set_shard(uint32_t tile_rank, uint32_t tile_world, uint32_t frame_rank, uint32_t frame_world);
     static void combine(const std::vector<Context*>& shards);
     std::vector<float> read_texture();              // RGBA32F, row 0 = bottom
@@ -164,6 +166,7 @@ public:
 
 private:
     rt_ctx* ctx_ = nullptr;
+    std::vector<rt_ctx*> combined_from_;            // non-empty: the last combine's shard set, still current
     void check(int rc, const char* what);
     void upload();
 };

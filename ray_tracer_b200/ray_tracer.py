@@ -129,6 +129,39 @@ class RayTracer:
     def set_shard(self, tile_rank=0, tile_world=1, frame_rank=0, frame_world=1):
         self._ck(self._L.rt_set_shard(self._h, tile_rank, tile_world, frame_rank, frame_world))
 
+    # -- multi-process combine over NCCL (rt_comm_init / rt_combine) ------------------------
+    def comm_init(self, n_ranks, rank, unique_id):
+        """Collective. unique_id: the 128 bytes of comm_unique_id() of one rank, handed round by the host."""
+        b = bytes(unique_id)
+        self._ck(self._L.rt_comm_init(self._h, int(n_ranks), int(rank), b, len(b)))
+
+    def comm_destroy(self):
+        self._ck(self._L.rt_comm_destroy(self._h))
+
+    def combine(self, root=0):
+        """Collective, asynchronous: the shards' images -> the combined image at `root` (read_combined)."""
+        self._ck(self._L.rt_combine(self._h, int(root)))
+
+    def combine_rgba8(self, root=0, is_root=True):
+        """Collective: the combine fused with the display transform; returns (H, W, 4) uint8 at the root, None elsewhere."""
+        out = np.empty((self.height, self.width, 4), np.uint8) if is_root else None
+        self._ck(self._L.rt_combine_rgba8(self._h, int(root), _ptr(out) if out is not None else None, out.size if out is not None else 0))
+        return out
+
+    def read_combined(self, out=None):
+        if out is None:
+            out = np.empty((self.height, self.width, 4), np.float32)
+        self._ck(self._L.rt_read_combined(self._h, _ptr(out), out.size))
+        return out
+
+    @property
+    def combined_device_ptr(self):
+        return self._L.rt_combined_device_ptr(self._h)
+
+    @property
+    def mean_count(self):
+        return int(self._L.rt_mean_count(self._h))
+
     def set_option(self, option, value):
         self._ck(self._L.rt_set_option(self._h, int(option), int(value)))
 
@@ -188,8 +221,18 @@ def _peer_args(tracers, weights):
     return tracers, arr, w
 
 
+def comm_unique_id():
+    """rt_comm_unique_id: 128 bytes for rt_comm_init, to be handed to every rank by the host."""
+    buf = C.create_string_buffer(128)
+    L = _lib.lib()
+    rc = L.rt_comm_unique_id(buf, 128)
+    if rc != 0:
+        raise RtError(rc, L.rt_last_error(None).decode())
+    return buf.raw
+
+
 def combine_peers(tracers, weights=None):
-    """rt_combine_peers: fold the shards' images into tracers[0]'s with one kernel over NVLink peer memory."""
+    """rt_combine_peers: the shards' images -> tracers[0]'s combined image (read_combined) with one kernel over NVLink peer memory."""
     tracers, arr, w = _peer_args(tracers, weights)
     tracers[0]._ck(tracers[0]._L.rt_combine_peers(arr, len(tracers), _ptr(w) if w is not None else None))
 

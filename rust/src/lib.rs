@@ -40,7 +40,7 @@ const _: () = {
 };
 
 pub mod opt { pub const TRAVERSAL: i32 = 1; pub const SEED_MODE: i32 = 2; pub const PRIMARY_IDS: i32 = 3; pub const DETAIL_COUNTERS: i32 = 4;
-              pub const FRAMES_PER_LAUNCH: i32 = 5; pub const LEAF_SIZE: i32 = 6; pub const SCHED: i32 = 7; pub const BUILDER: i32 = 8; pub const PLOC_RADIUS: i32 = 9; pub const KERNEL: i32 = 10; pub const WAVE_SLOTS: i32 = 11; pub const STAGING_MIB: i32 = 12; }
+              pub const FRAMES_PER_LAUNCH: i32 = 5; pub const LEAF_SIZE: i32 = 6; pub const SCHED: i32 = 7; pub const BUILDER: i32 = 8; pub const PLOC_RADIUS: i32 = 9; pub const KERNEL: i32 = 10; pub const WAVE_SLOTS: i32 = 11; pub const STAGING_MIB: i32 = 12; pub const ITEM_MODE: i32 = 13; }
 
 #[repr(C)] pub struct RtCtx { _private: [u8; 0] }
 
@@ -63,6 +63,14 @@ extern "C" {
     pub fn rt_set_shard(ctx: *mut RtCtx, tile_rank: u32, tile_world: u32, frame_rank: u32, frame_world: u32) -> c_int;
     pub fn rt_combine_peers(ctxs: *const *mut RtCtx, n: u32, weights: *const f32) -> c_int;
     pub fn rt_combine_peers_rgba8(ctxs: *const *mut RtCtx, n: u32, weights: *const f32, rgba: *mut u8, n_bytes: usize) -> c_int;
+    pub fn rt_comm_unique_id(id: *mut c_void, n_bytes: usize) -> c_int;
+    pub fn rt_comm_init(ctx: *mut RtCtx, n_ranks: c_int, rank: c_int, id: *const c_void, n_bytes: usize) -> c_int;
+    pub fn rt_comm_destroy(ctx: *mut RtCtx) -> c_int;
+    pub fn rt_combine(ctx: *mut RtCtx, root: c_int) -> c_int;
+    pub fn rt_combine_rgba8(ctx: *mut RtCtx, root: c_int, rgba: *mut u8, n_bytes: usize) -> c_int;
+    pub fn rt_read_combined(ctx: *mut RtCtx, rgba: *mut f32, n_floats: usize) -> c_int;
+    pub fn rt_combined_device_ptr(ctx: *mut RtCtx) -> *mut c_void;
+    pub fn rt_mean_count(ctx: *const RtCtx) -> u32;
     pub fn rt_set_option(ctx: *mut RtCtx, option: c_int, value: i64) -> c_int;
     pub fn rt_get_option(ctx: *const RtCtx, option: c_int, value: *mut i64) -> c_int;
     pub fn rt_read_accum(ctx: *mut RtCtx, rgba: *mut f32, n_floats: usize) -> c_int;
@@ -139,12 +147,35 @@ impl RayTracer {
         let mut v = vec![0u8; self.width as usize * self.height as usize * 4];
         self.check(unsafe { rt_read_rgba8(self.ctx, v.as_mut_ptr(), v.len()) })?; Ok(v)
     }
+    /// One process (or host thread) per GPU: join the NCCL communicator of the job. `id` = `comm_unique_id()` of one rank,
+    /// handed to the others by the host (upstream is single-device, context.rs:196-208 is the one dispatch site this serves).
+    pub fn comm_init(&self, n_ranks: i32, rank: i32, id: &[u8; 128]) -> Result<()> {
+        self.check(unsafe { rt_comm_init(self.ctx, n_ranks, rank, id.as_ptr() as *const c_void, id.len()) })
+    }
+    /// Collective, asynchronous: every rank's tiles -> `root`, count-weighted, de-interleaved there (`read_combined`).
+    pub fn combine(&self, root: i32) -> Result<()> { self.check(unsafe { rt_combine(self.ctx, root) }) }
+    /// The combined image of the last `combine` (at the root) / `combine_peers` (on shards[0]); accum is never overwritten.
+    pub fn read_combined(&self) -> Result<Vec<f32>> {
+        let mut v = vec![0f32; self.width as usize * self.height as usize * 4];
+        self.check(unsafe { rt_read_combined(self.ctx, v.as_mut_ptr(), v.len()) })?; Ok(v)
+    }
     pub fn counters(&self) -> Result<Counters> { let mut c = Counters::default(); self.check(unsafe { rt_get_counters(self.ctx, &mut c) })?; Ok(c) }
 }
 impl Drop for RayTracer { fn drop(&mut self) { unsafe { rt_destroy(self.ctx) } } }
 
-/// Several GPUs from one process (one `RayTracer` per device, sharded with `set_shard`): folds every shard's image
-/// into `shards[0]`'s with one kernel over NVLink peer memory. `weights = None`: 1 / frame_world of each shard.
+/// 128 bytes identifying a new NCCL communicator (`ncclGetUniqueId`); one rank makes it, all pass it to `comm_init`.
+pub fn comm_unique_id() -> Result<[u8; 128]> {
+    let mut id = [0u8; 128];
+    let rc = unsafe { rt_comm_unique_id(id.as_mut_ptr() as *mut c_void, id.len()) };
+    if rc != 0 {
+        let message = unsafe { CStr::from_ptr(rt_last_error(std::ptr::null())) }.to_string_lossy().into_owned();
+        return Err(Error { code: rc, message });
+    }
+    Ok(id)
+}
+/// Several GPUs from one process (one `RayTracer` per device, sharded with `set_shard`): combines every shard's image
+/// into `shards[0]`'s combined image (`read_combined`) with one kernel over NVLink peer memory. `weights = None`: each
+/// shard's share of the dispatches its pixels have seen.
 pub fn combine_peers(shards: &[&RayTracer], weights: Option<&[f32]>) -> Result<()> {
     let ptrs: Vec<*mut RtCtx> = shards.iter().map(|s| s.ctx).collect();
     let w = weights.map_or(std::ptr::null(), |w| w.as_ptr());

@@ -66,7 +66,7 @@ if a.check:
     one = rt.RayTracer(0, p["width"], p["height"])
     one.upload_scene(*scene.arrays()); one.upload_textures(scene.textures); one.set_camera(scene.camera_uniform()); one.set_params(**p)
     one.render_frames(0, D * N); ref = one.read_accum(); one.close()
-    got = trs[0].read_accum()
+    got = trs[0].read_combined()
     same = got.view(np.uint32) == ref.view(np.uint32)
     line["max_abs_diff_vs_one_gpu"] = float(np.max(np.abs(np.where(same, 0.0, got.astype(np.float64) - ref))))
     line["bit_identical_to_one_gpu"] = bool(np.array_equal(got.view(np.uint32), ref.view(np.uint32)))

@@ -47,9 +47,14 @@ def test_tile_shards_combine_to_the_single_context_image_bit_for_bit(rtlib):
         part0 = trs[0].read_accum()
         assert not np.array_equal(part0, full)
         rtlib.combine_peers(trs)
-        assert_bits_equal(trs[0].read_accum(), full, "tile shards, world %d" % world)
-        # the other contexts keep their own tiles and can go on rendering
-        trs[1].render_frames(frames, 1); trs[1].sync()
+        assert_bits_equal(trs[0].read_combined(), full, "tile shards, world %d" % world)
+        assert_bits_equal(trs[0].read_accum(), part0, "a combine leaves the accumulation image alone")
+        # every context keeps its own tiles and can go on rendering; a second combine follows the single context
+        for t in trs:
+            t.render_frames(frames, 2)
+        rtlib.combine_peers(trs)
+        one = _tracer(rtlib, 0, scene); one.render_frames(0, frames + 2); full2 = one.read_accum(); one.close()
+        assert_bits_equal(trs[0].read_combined(), full2, "tile shards after more frames, world %d" % world)
         for t in trs:
             t.close()
 
@@ -73,7 +78,8 @@ def test_tile_and_sample_shards_combine_like_the_weighted_sum(rtlib):
         want[m] = np.where(seen[m][:, None], (want[m] + term[m]).astype(np.float32), term[m])
         seen |= m
     rtlib.combine_peers(trs)
-    got = trs[0].read_accum()
+    got = trs[0].read_combined()
+    assert [t.mean_count for t in trs] == [3, 3, 3, 3]
     assert_bits_equal(got, want, "2 tile x 2 sample shards")
     one = _tracer(rtlib, 0, scene); one.render_frames(0, frames); full = one.read_accum(); one.close()
     assert np.allclose(got, full, rtol=2e-6, atol=1e-6)     # equal to the sequential running mean up to f32 rounding
@@ -84,10 +90,39 @@ def test_tile_and_sample_shards_combine_like_the_weighted_sum(rtlib):
     b = _tracer(rtlib, _devices(2)[1], scene); b.set_params(number_of_bounces=BOUNCES, rays_per_pixel=1, skybox=1, frames=-3); b.dispatch()
     pa, pb = a.read_accum(), b.read_accum()
     rtlib.combine_peers([a, b], weights=[0.75, 0.25])
-    assert_bits_equal(a.read_accum(), ((pa * np.float32(0.75)).astype(np.float32) + (pb * np.float32(0.25)).astype(np.float32)).astype(np.float32), "weighted")
+    assert_bits_equal(a.read_combined(), ((pa * np.float32(0.75)).astype(np.float32) + (pb * np.float32(0.25)).astype(np.float32)).astype(np.float32), "weighted")
     one = _tracer(rtlib, 0, scene); one.render_frames(0, 4); full4 = one.read_accum(); one.close()
-    assert np.allclose(a.read_accum(), full4, rtol=2e-6, atol=1e-6)
+    assert np.allclose(a.read_combined(), full4, rtol=2e-6, atol=1e-6)
     a.close(); b.close()
+
+
+def test_sample_shards_keep_accumulating_across_combines_and_uneven_counts(rtlib):
+    """a combine must not disturb the shards' running means (render, combine, render, combine), and shards
+    that hold different numbers of dispatches (n_frames not divisible by the world) enter with count weights."""
+    scene = _scene("room")
+    devs = _devices(3)
+    trs = [_tracer(rtlib, d, scene, frame_rank=k, frame_world=3) for k, d in enumerate(devs)]
+    for t in trs:
+        t.render_frames(0, 7)                              # ranks hold 3, 2, 2 dispatches
+    assert [t.mean_count for t in trs] == [3, 2, 2]
+    parts = [t.read_accum() for t in trs]
+    rtlib.combine_peers(trs)
+    got = trs[0].read_combined()
+    want = None
+    for p, n in zip(parts, (3, 2, 2)):
+        term = (p * (np.float32(n) / np.float32(7))).astype(np.float32)
+        want = term if want is None else (want + term).astype(np.float32)
+    assert_bits_equal(got, want, "count-weighted 3/2/2")
+    one = _tracer(rtlib, 0, scene); one.render_frames(0, 7); full7 = one.read_accum()
+    assert np.allclose(got, full7, rtol=3e-6, atol=2e-6)
+    for t in trs:
+        t.render_frames(7, 5)                              # frames 7..11 on top: 4 dispatches per rank now
+    assert [t.mean_count for t in trs] == [4, 4, 4]
+    rtlib.combine_peers(trs)
+    one.render_frames(7, 5); full12 = one.read_accum(); one.close()
+    assert np.allclose(trs[0].read_combined(), full12, rtol=3e-6, atol=2e-6)
+    for t in trs:
+        t.close()
 
 
 def test_combine_errors(rtlib):
@@ -104,7 +139,8 @@ def test_combine_errors(rtlib):
     rtlib.combine_peers([a])                                # one context: weight 1, image unchanged
     a.render_frames(0, 2); img = a.read_accum()
     rtlib.combine_peers([a])
-    assert_bits_equal(a.read_accum(), img, "single context")
+    assert_bits_equal(a.read_combined(), img, "single context")
+    assert_bits_equal(a.read_accum(), img, "single context, accum")
     a.close(); b.close()
 
 

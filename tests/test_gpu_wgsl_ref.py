@@ -110,3 +110,49 @@ def test_c5_records_through_the_cpu_oracle(rtlib, oracle):
     assert np.array_equal(gid[::st, ::st], ids[::st, ::st])
     assert (ids[::st, ::st] != MISS).sum() > 40          # the sample does see geometry
     assert_bits_equal(gi[::st, ::st], ci[::st, ::st], "c5 strided")
+
+
+# ---- launch structure and seed modes ----------------------------------------------------------------
+@pytest.mark.parametrize("name,w,h,frames,first", [("room", 96, 64, 5, 0), ("balls", 100, 76, 3, 1), ("c3_teapot", 160, 90, 4, 0)])
+def test_item_modes_agree(rtlib, name, w, h, frames, first):
+    """RT_OPT_ITEM_MODE 2 (one lane owns a pixel for all fused dispatches and applies wgsl:59-66 itself) == 1 ((pixel, dispatch)
+    items, staged frags, blend kernel) == one launch per dispatch (auto: pixel items), bit for bit."""
+    scene = _config(name, w, h) if name.startswith("c") else _builtin(name, w, h)
+    cam, sp, vs, ix, ms = scene
+    imgs = []
+    for mode, fpl in ((2, 0), (1, 0), (0, 1), (1, 2), (2, 2)):
+        tr = rtlib.RayTracer(0, w, h)
+        tr.upload_scene(sp, vs, ix, ms)
+        tr.set_camera(cam.view(rtlib.CAMERA_DT))
+        tr.set_params(number_of_bounces=4, rays_per_pixel=1, skybox=1, frames=first)
+        tr.set_option(rtlib._lib.RT_OPT_ITEM_MODE, mode)
+        tr.set_option(rtlib._lib.RT_OPT_FRAMES_PER_LAUNCH, fpl)
+        tr.render_frames(first, frames)
+        imgs.append((tr.read_accum(), tr.counters()))
+        tr.close()
+    assert imgs[0][1]["launches"] == 1 and imgs[2][1]["launches"] == frames
+    for img, ctr in imgs[1:]:
+        assert ctr["rays"] == imgs[0][1]["rays"]
+        assert_bits_equal(img, imgs[0][0], name)
+
+
+def test_wide_seed_mode_at_4k(rtlib, oracle):
+    """RT_OPT_SEED_MODE = 1: the seed's f32 -> u32 conversion wraps modulo 2^32 where strict mode saturates (3840x2160, rows
+    >= 518).  CUDA == hand oracle (== oracle/_ref when present) on a strided pixel set in wide mode; wide == strict on the rows
+    below 518 and differs above."""
+    w, h, sx, sy = 3840, 2160, 96, 54
+    scene = _builtin("balls", w, h)
+    gw, _, _ = _gpu(rtlib, scene, w, h, 2, 3, 1, 1, 0, seed_mode=1)
+    gs, _, _ = _gpu(rtlib, scene, w, h, 2, 3, 1, 1, 0, seed_mode=0)
+    with oracle.seed_mode(1):
+        cw = oracle.render(scene, w, h, 2, 3, 1, 1, 0, None, None, sx, sy)
+        assert oracle.pixel_seed(1, 518, w, h, 0) == 0x177000 and oracle.pixel_seed(0, 517, w, h, 0) == 0xff98d000
+    assert oracle.pixel_seed(1, 518, w, h, 0) == 0xFFFFFFFF
+    assert_bits_equal(gw[::sy, ::sx], cw[::sy, ::sx], "wide seed mode, 4K strided")
+    assert np.array_equal(gw[:516].view(np.uint32), gs[:516].view(np.uint32))     # rows 0..515: every seed is below 2^32 (row 517 crosses it at x = 1749)
+    assert not np.array_equal(gw[520:].view(np.uint32), gs[520:].view(np.uint32))
+    if make_ref.build() is not None:
+        from oracle import wgsl_ref as wr
+        with wr.seed_mode(1):
+            rw = wr.render(scene, w, h, 2, 3, 1, 1, 0, None, None, sx, sy)
+        assert_bits_equal(gw[::sy, ::sx], rw[::sy, ::sx], "wide seed mode vs oracle/_ref")

@@ -155,6 +155,20 @@ def test_contract_ref_equals_hand_oracle_at_4k_seed_saturation(oracle, wr):
     assert int(o[2][0]) > 200
 
 
+def test_wide_seed_mode_agrees(oracle, wr):
+    """The labelled deviation RT_OPT_SEED_MODE = 1 (out-of-range u32(f32) wraps instead of saturating) in both CPU sides."""
+    from oracle import host_ref as hr
+    w, h = 3840, 2160
+    sc = hr.scene_balls(np.float32(w) / np.float32(h))
+    with oracle.seed_mode(1), wr.seed_mode(1):
+        o, r = both(oracle, wr, sc, w, h, 2, 3, 1, 1, 0, x_step=479, y_step=127)
+        assert_identical(o, r, "4k strided, wide")
+        assert oracle.pixel_seed(0, 518, w, h, 0) == 0x176000
+    s, _ = both(oracle, wr, sc, w, h, 2, 3, 1, 1, 0, x_step=479, y_step=127)
+    assert np.array_equal(o[0][:518].view(np.uint32), s[0][:518].view(np.uint32))          # identical where the seed is below 2^32
+    assert not np.array_equal(o[0][518:].view(np.uint32), s[0][518:].view(np.uint32))
+
+
 def test_contract_ref_c1_baseline_size(oracle, wr):
     """C1 at its BASELINE.json size: `balls`, 800x800, 16 spp (8 dispatches), 4 bounces (every 5th pixel: 25,600 pixels x 8 dispatches)."""
     from oracle import host_ref as hr
