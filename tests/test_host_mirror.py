@@ -174,3 +174,19 @@ def test_fixture_shapes():
     s, meta = configs.build("c5_stress", 64, 36)
     assert len(s.spheres) == 100000 and len(s.meshes) == 128 and int(s.meshes["triangles"].sum()) == 64 * 15704
     assert meta["dispatches"] == 32
+
+
+@pytest.mark.parametrize("name", ["c1_balls", "c2_cube", "c2_cube_plain", "c3_teapot", "c4_tree", "c5_stress"])
+def test_oracle_side_configs_equal_the_products(rtlib, name):
+    """oracle/ref_configs.py (what the CPU arms of bench.py render, built without loading the product libraries) produces
+    the records of ray_tracer_b200.configs byte for byte."""
+    from oracle import ref_configs
+    from ray_tracer_b200 import configs
+    w, h = (96, 54) if name != "c1_balls" else (64, 64)
+    (cam, sp, vs, ix, ms), tex, meta = ref_configs.build(name, w, h)
+    scene, pmeta = configs.build(name, w, h)
+    pc, psp, pvs, pix, pms = scene.as_tuple()
+    assert meta == pmeta
+    assert cam.tobytes() == pc.tobytes() and sp.tobytes() == psp.tobytes() and vs.tobytes() == pvs.tobytes()
+    assert ix.tobytes() == pix.tobytes() and ms.tobytes() == pms.tobytes()
+    assert len(tex) == len(scene.textures) and all(np.array_equal(a, b) for a, b in zip(tex, scene.textures))
