@@ -41,6 +41,7 @@ struct rt_ctx {
     uint32_t staging_frames = 0;
     int n_sms = 148;
     int64_t opt_staging_bytes = 4352ll << 20;     // staging planes (RT_OPT_STAGING_MIB): 128 dispatches per launch at 1080p, 32 at 4K
+    int64_t opt_instancing = 2;                   // Mesh records that alias one index range share one object-space hierarchy (two-level BVH): 0 never, 1 when eligible, 2 auto
     int64_t opt_item_mode = 0;                    // 0: auto, 1: (pixel, dispatch) items + staging + blend kernel, 2: pixel items, running mean applied in the trace kernel
     int64_t opt_sched = 8 | (1 << 8) | (22 << 16);     // node loop runs while >= 8 lanes can step; shade once >= 22 lanes wait (swept on C3/C5)
     rt::SceneBuffers scene;
@@ -171,7 +172,7 @@ int launch(rt_ctx* c, int32_t first_frame, uint32_t n_frames, bool want_ids)
 {
     rt::SceneDev sd{};
     const rt::SceneBuffers& s = c->scene;
-    sd.prims = s.prims; sd.c0 = s.c0; sd.c1 = s.c1; sd.c2 = s.c2; sd.c3 = s.c3; sd.c4 = s.c4; sd.c5 = s.c5;
+    sd.prims = s.prims; sd.iprims = s.iprims; sd.c0 = s.c0; sd.c1 = s.c1; sd.c2 = s.c2; sd.c3 = s.c3; sd.c4 = s.c4; sd.c5 = s.c5;
     sd.tex = c->d_tex; sd.n_tex = (uint32_t)c->textures.size();
     sd.m0 = s.m0; sd.m1 = s.m1; sd.m2 = s.m2; sd.nodes = s.nodes;
     sd.n_prims = s.n_prims; sd.n_spheres = s.n_spheres; sd.root = s.root;
@@ -331,8 +332,15 @@ int rt_upload_scene(rt_ctx* c, const rt_sphere* spheres, uint32_t ns, const rt_v
     DeviceGuard g(c->device);
     CU(c, cudaStreamSynchronize(c->stream));
     uint32_t leaf = (uint32_t)(c->opt_leaf_size < 1 ? 1 : (c->opt_leaf_size > 8 ? 8 : c->opt_leaf_size));
-    cudaError_t e = rt::build_scene(c->scene, spheres, ns, vertices, nv, indices, ni, meshes, nm, leaf, (int)c->opt_builder, (int)c->opt_ploc_radius, c->stream);
+    // Mesh records aliasing one (first, triangles, offset) range become instances of one object-space hierarchy, unless the
+    // exhaustive scan or the wavefront kernels (which need flattened records) are selected at upload time
+    const int instancing = (c->opt_traversal == 0 && c->opt_kernel == 0) ? (int)c->opt_instancing : 0;
+    cudaError_t e = rt::build_scene(c->scene, spheres, ns, vertices, nv, indices, ni, meshes, nm, leaf, (int)c->opt_builder, (int)c->opt_ploc_radius, instancing, c->stream);
     if (e != cudaSuccess) { c->has_scene = false; return cuda_fail(c, e, "scene build"); }
+    if (c->scene.n_inst != 0 && c->scene.max_depth > RT_STACK - 2) {          // two levels too deep for the stack: flatten instead
+        e = rt::build_scene(c->scene, spheres, ns, vertices, nv, indices, ni, meshes, nm, leaf, (int)c->opt_builder, (int)c->opt_ploc_radius, 0, c->stream);
+        if (e != cudaSuccess) { c->has_scene = false; return cuda_fail(c, e, "scene build"); }
+    }
     // A hierarchy deeper than the traversal stack (both builders; needs thousands of coincident primitives plus far
     // outliers) is not an error: the reference renders any scene, so such a scene is traced with the exhaustive scan.
     c->scene_too_deep = c->scene.max_depth > RT_STACK - 2;
@@ -655,7 +663,10 @@ int rt_set_option(rt_ctx* c, int option, int64_t value)
 {
     if (!c) return RT_ERR_INVALID_ARGUMENT;
     switch (option) {
-    case RT_OPT_TRAVERSAL: if (value != 0 && value != 1) break; c->opt_traversal = value; return RT_OK;
+    case RT_OPT_TRAVERSAL: if (value != 0 && value != 1) break;
+        if (value == 1 && c->has_scene && c->scene.n_inst != 0) return fail(c, RT_ERR_UNSUPPORTED, "rt_set_option: the exhaustive scan needs flattened records; set RT_OPT_TRAVERSAL = 1 (or RT_OPT_INSTANCING = 0) before rt_upload_scene");
+        c->opt_traversal = value; return RT_OK;
+    case RT_OPT_INSTANCING: if (value < 0 || value > 2) break; c->opt_instancing = value; return RT_OK;
     case RT_OPT_SEED_MODE: if (value != 0 && value != 1) break; c->opt_seed_mode = value; return RT_OK;
     case RT_OPT_PRIMARY_IDS: c->opt_primary_ids = value != 0; return RT_OK;
     case RT_OPT_DETAIL_COUNTERS: c->opt_detail = value != 0; return RT_OK;
@@ -665,7 +676,9 @@ int rt_set_option(rt_ctx* c, int option, int64_t value)
     case RT_OPT_SCHED: c->opt_sched = value & 0xffffff; return RT_OK;
     case RT_OPT_BUILDER: if (value != 0 && value != 1) break; c->opt_builder = value; return RT_OK;
     case RT_OPT_PLOC_RADIUS: if (value < 1 || value > 16) break; c->opt_ploc_radius = value; return RT_OK;
-    case RT_OPT_KERNEL: if (value != 0 && value != 1) break; c->opt_kernel = value; return RT_OK;
+    case RT_OPT_KERNEL: if (value != 0 && value != 1) break;
+        if (value == 1 && c->has_scene && c->scene.n_inst != 0) return fail(c, RT_ERR_UNSUPPORTED, "rt_set_option: the wavefront kernels need flattened records; set RT_OPT_KERNEL = 1 (or RT_OPT_INSTANCING = 0) before rt_upload_scene");
+        c->opt_kernel = value; return RT_OK;
     case RT_OPT_WAVE_SLOTS: if (value < 1024 || value > (1 << 26)) break; c->opt_wave_slots = value; return RT_OK;
     case RT_OPT_STAGING_MIB: if (value < 16 || value > (1 << 17)) break; c->opt_staging_bytes = value << 20; return RT_OK;
     default: return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_set_option: unknown option");
@@ -690,6 +703,7 @@ int rt_get_option(const rt_ctx* c, int option, int64_t* value)
     case RT_OPT_WAVE_SLOTS: *value = c->opt_wave_slots; return RT_OK;
     case RT_OPT_STAGING_MIB: *value = c->opt_staging_bytes >> 20; return RT_OK;
     case RT_OPT_ITEM_MODE: *value = c->opt_item_mode; return RT_OK;
+    case RT_OPT_INSTANCING: *value = c->opt_instancing; return RT_OK;
     default: return RT_ERR_INVALID_ARGUMENT;
     }
 }

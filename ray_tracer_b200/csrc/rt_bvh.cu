@@ -30,19 +30,28 @@ namespace {
 
 struct RawScene {
     const rt_sphere* spheres; const rt_vertex* vertices; const uint32_t* indices; const rt_mesh* meshes;
-    const uint32_t* tri_start;      // [nm+1] prefix sum of mesh.triangles
-    uint32_t ns, nm, nt;
+    const uint32_t* tri_start;      // [nm+1] prefix sum of mesh.triangles: ids of the reference's scan order
+    uint32_t ns, nm, nt;            // nt = triangles that get their own (flattened) record
+    // Instancing (two-level hierarchy): meshes whose (first, triangles, offset) range is shared by several Mesh records are not
+    // flattened; each such record becomes ONE proxy primitive of the top level that points at the range's object-space hierarchy.
+    const uint32_t* flat_start;     // [nm+1] prefix sum of mesh.triangles over the flattened meshes only (== tri_start without instancing)
+    const uint32_t* inst_mesh;      // [n_inst] mesh index of every proxy
+    const int* range_of_mesh;       // [nm] -1: flattened, else index into range_info
+    const float4* range_info;       // 3 per range: object-space bounds lo, hi, (root node, first cold index, 0, 0) as int bits
+    uint32_t n_inst;
 };
+// Top-level primitive index t: [0, ns) spheres, [ns, ns + nt) flattened triangles, then the proxies.  hot / cold / bounds arrays
+// are indexed by t; the `id` stored in a hot record is the GLOBAL primitive order index (the tie-break key and the AOV).
 
 __device__ __forceinline__ int fenc(float f) { int i = __float_as_int(f); return i >= 0 ? i : i ^ 0x7fffffff; }
 __device__ __forceinline__ float fdec(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7fffffff); }
 
-// one thread per primitive id: hot/cold records in id order, exact bounds, scene bounds
-__global__ void setup_prims(RawScene rs, float4* hot /*4 per id*/, float4* c0, float4* c1, float4* c2, float4* c3, float4* c4, float4* c5,
+// one thread per top-level primitive: hot/cold records in index order, exact bounds, scene bounds
+__global__ void setup_prims(RawScene rs, float4* hot /*4 per index*/, float4* c0, float4* c1, float4* c2, float4* c3, float4* c4, float4* c5,
                             float4* bmin, float4* bmax, int* scene_bounds /*[6] encoded*/)
 {
-    uint32_t id = blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t n = rs.ns + rs.nt;
+    uint32_t id = blockIdx.x * blockDim.x + threadIdx.x;             // top-level index t
+    uint32_t n = rs.ns + rs.nt + rs.n_inst;
     float3 lo = f3(INFINITY, INFINITY, INFINITY), hi = f3(-INFINITY, -INFINITY, -INFINITY);
     if (id < n) {
         if (id < rs.ns) {
@@ -57,12 +66,13 @@ __global__ void setup_prims(RawScene rs, float4* hot /*4 per id*/, float4* c0, f
             if (c3) c3[id] = c4[id] = c5[id] = make_float4(0.f, 0.f, 0.f, 0.f);
             float ar = fabsf(r);
             lo = f3(c.x - ar, c.y - ar, c.z - ar); hi = f3(c.x + ar, c.y + ar, c.z + ar);
-        } else {
+        } else if (id < rs.ns + rs.nt) {
             uint32_t t = id - rs.ns;
-            uint32_t a = 0, b = rs.nm;               // mesh m with tri_start[m] <= t < tri_start[m+1]
-            while (b - a > 1) { uint32_t mid = (a + b) >> 1; if (rs.tri_start[mid] <= t) a = mid; else b = mid; }
+            uint32_t a = 0, b = rs.nm;               // flattened mesh m with flat_start[m] <= t < flat_start[m+1] (the last such: empty ranges are skipped)
+            while (b - a > 1) { uint32_t mid = (a + b) >> 1; if (rs.flat_start[mid] <= t) a = mid; else b = mid; }
             const rt_mesh& m = rs.meshes[a];
-            uint32_t i = t - rs.tri_start[a];
+            uint32_t i = t - rs.flat_start[a];
+            const uint32_t gid = rs.ns + rs.tri_start[a] + i;         // position in the reference's scan order (wgsl:149-185)
             const rt_vertex& va = rs.vertices[m.offset + rs.indices[m.first + i * 3u]];
             const rt_vertex& vb = rs.vertices[m.offset + rs.indices[m.first + i * 3u + 1u]];
             const rt_vertex& vc = rs.vertices[m.offset + rs.indices[m.first + i * 3u + 2u]];
@@ -72,10 +82,10 @@ __global__ void setup_prims(RawScene rs, float4* hot /*4 per id*/, float4* c0, f
             float3 C = f3(vc.pos[0], vc.pos[1], vc.pos[2]) + mp;
             float3 e1 = B - A, e2 = C - A;                              // wgsl:127-128
             float3 nrm = cross3(e1, e2);                                // wgsl:129
-            hot[4 * (size_t)id + 0] = make_float4(nrm.x, nrm.y, nrm.z, __uint_as_float(id));
+            hot[4 * (size_t)id + 0] = make_float4(nrm.x, nrm.y, nrm.z, __uint_as_float(gid));
             hot[4 * (size_t)id + 1] = make_float4(A.x, A.y, A.z, e1.x);
             hot[4 * (size_t)id + 2] = make_float4(e1.y, e1.z, e2.x, e2.y);
-            hot[4 * (size_t)id + 3] = make_float4(e2.z, 0.f, 0.f, 0.f);
+            hot[4 * (size_t)id + 3] = make_float4(e2.z, __uint_as_float(id), 0.f, 0.f);     // .y: index of the cold records
             c0[id] = make_float4(va.normal[0], va.normal[1], va.normal[2], __uint_as_float(rs.ns + a));
             c1[id] = make_float4(vb.normal[0], vb.normal[1], vb.normal[2], 0.f);
             c2[id] = make_float4(vc.normal[0], vc.normal[1], vc.normal[2], 0.f);
@@ -86,6 +96,21 @@ __global__ void setup_prims(RawScene rs, float4* hot /*4 per id*/, float4* c0, f
             }
             lo = f3(fminf(A.x, fminf(B.x, C.x)), fminf(A.y, fminf(B.y, C.y)), fminf(A.z, fminf(B.z, C.z)));
             hi = f3(fmaxf(A.x, fmaxf(B.x, C.x)), fmaxf(A.y, fmaxf(B.y, C.y)), fmaxf(A.z, fmaxf(B.z, C.z)));
+        } else {
+            // proxy of one instance: (pos, 0x80000000 | k), (root node of the range's hierarchy, first global id, first cold index, material)
+            const uint32_t k = id - rs.ns - rs.nt;
+            const uint32_t mi = rs.inst_mesh[k];
+            const rt_mesh& m = rs.meshes[mi];
+            const int g = rs.range_of_mesh[mi];
+            const float4 rlo = rs.range_info[3 * g + 0], rhi = rs.range_info[3 * g + 1], ri = rs.range_info[3 * g + 2];
+            hot[4 * (size_t)id + 0] = make_float4(m.pos[0], m.pos[1], m.pos[2], __uint_as_float(0x80000000u | k));
+            hot[4 * (size_t)id + 1] = make_float4(ri.x, __uint_as_float(rs.ns + rs.tri_start[mi]), ri.y, __uint_as_float(rs.ns + mi));
+            hot[4 * (size_t)id + 2] = hot[4 * (size_t)id + 3] = make_float4(0.f, 0.f, 0.f, 0.f);
+            c0[id] = c1[id] = c2[id] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (c3) c3[id] = c4[id] = c5[id] = make_float4(0.f, 0.f, 0.f, 0.f);
+            // every vertex the shader forms is fl(a + pos) with a inside [rlo, rhi]: rounding is monotonic, so the directed sums bound it
+            lo = f3(__fadd_rd(rlo.x, m.pos[0]), __fadd_rd(rlo.y, m.pos[1]), __fadd_rd(rlo.z, m.pos[2]));
+            hi = f3(__fadd_ru(rhi.x, m.pos[0]), __fadd_ru(rhi.y, m.pos[1]), __fadd_ru(rhi.z, m.pos[2]));
         }
         bmin[id] = make_float4(lo.x, lo.y, lo.z, 0.f);
         bmax[id] = make_float4(hi.x, hi.y, hi.z, 0.f);
@@ -451,35 +476,57 @@ cudaError_t pool_alloc(void** p, size_t bytes, cudaStream_t s)
 }
 template <typename T>
 cudaError_t dalloc(T** p, size_t n) { return pool_alloc((void**)p, (n ? n : 1) * sizeof(T), g_alloc_stream); }
+cudaError_t cudaMallocFromPoolAsyncOrDefault(void** p, size_t bytes, cudaMemPool_t pool, cudaStream_t s)
+{
+    return pool ? cudaMallocFromPoolAsync(p, bytes, pool, s) : cudaMallocAsync(p, bytes, s);
+}
 
 } // namespace
 
 void SceneBuffers::release()
 {
-    float4** ps[] = {&prims, &c0, &c1, &c2, &c3, &c4, &c5, &m0, &m1, &m2, &nodes};
+    float4** ps[] = {&prims, &c0, &c1, &c2, &c3, &c4, &c5, &m0, &m1, &m2, &nodes, &iprims};
     for (auto p : ps) { if (*p) cudaFreeAsync(*p, stream); *p = nullptr; }
     {
         void* kp[] = {keep.sph, keep.vtx, keep.idx, keep.mesh, keep.tstart, keep.hot, keep.bmin, keep.bmax, keep.lmin, keep.lmax, keep.imin, keep.imax,
-                      keep.bounds, keep.ids2, keep.new_slot, keep.children, keep.ranges, keep.pin, keep.plf, keep.flags};
+                      keep.bounds, keep.ids2, keep.new_slot, keep.children, keep.ranges, keep.pin, keep.plf, keep.flags,
+                      keep.flat_start, keep.inst_mesh, keep.range_of_mesh, keep.range_info};
         for (void* p : kp) if (p) cudaFreeAsync(p, stream);
         keep = Keep();
     }
     n_prims = n_spheres = n_tris = n_mats = n_nodes = max_depth = 0; root = -1; max_abs = 0.f; has_tex = false;
+    n_inst = n_iprims = n_cold = n_top_nodes = 0;
 }
 
 #define RT_TRY(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { err = e_; goto done; } } while (0)
 
-cudaError_t build_scene(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns, const rt_vertex* vertices,
+// What instancing adds to a top-level build (nullptr / empty: every mesh is flattened)
+struct InstPlan {
+    std::vector<int> range_of_mesh;                 // per mesh: -1 flattened, else range index
+    std::vector<uint32_t> inst_mesh;                // proxies in mesh order
+    std::vector<float4> range_info;                 // 3 per range (setup_prims)
+    uint32_t blas_nodes = 0, blas_tris = 0;         // totals appended behind the top level
+};
+
+static cudaError_t build_scene_impl(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns, const rt_vertex* vertices,
                         uint32_t nv, const uint32_t* indices, uint32_t ni, const rt_mesh* meshes, uint32_t nm,
-                        uint32_t leaf_size, int builder, int ploc_radius, cudaStream_t stream)
+                        uint32_t leaf_size, int builder, int ploc_radius, const InstPlan* plan, cudaStream_t stream)
 {
     out.release();
     out.stream = stream;
     g_alloc_stream = stream; g_alloc_pool = out.pool;
     cudaError_t err = cudaSuccess;
-    std::vector<uint32_t> tri_start(nm + 1, 0);
-    for (uint32_t m = 0; m < nm; m++) tri_start[m + 1] = tri_start[m] + meshes[m].triangles;
-    const uint32_t nt = tri_start[nm], n = ns + nt, nmat = ns + nm;
+    std::vector<uint32_t> tri_start(nm + 1, 0), flat_start(nm + 1, 0);
+    std::vector<int> range_of_mesh(nm, -1);
+    if (plan) range_of_mesh = plan->range_of_mesh;
+    for (uint32_t m = 0; m < nm; m++) {
+        tri_start[m + 1] = tri_start[m] + meshes[m].triangles;
+        flat_start[m + 1] = flat_start[m] + (range_of_mesh[m] < 0 ? meshes[m].triangles : 0u);
+    }
+    const uint32_t n_inst = plan ? (uint32_t)plan->inst_mesh.size() : 0u;
+    const uint32_t nt = flat_start[nm], n = ns + nt + n_inst, nmat = ns + nm;
+    const uint32_t n_cold = n + (plan ? plan->blas_tris : 0u);
+    uint32_t* d_flat_start = nullptr; uint32_t* d_inst_mesh = nullptr; int* d_range_of_mesh = nullptr; float4* d_range_info = nullptr;
     const int T = 256;
     if (ploc_radius < 1) ploc_radius = 1;
     if (ploc_radius > PLOC_MAX_RADIUS) ploc_radius = PLOC_MAX_RADIUS;
@@ -498,6 +545,14 @@ cudaError_t build_scene(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns
 
     RT_TRY(dalloc(&d_sph, ns)); RT_TRY(dalloc(&d_vtx, nv)); RT_TRY(dalloc(&d_idx, ni)); RT_TRY(dalloc(&d_mesh, nm));
     RT_TRY(dalloc(&d_tstart, nm + 1));
+    RT_TRY(dalloc(&d_flat_start, nm + 1)); RT_TRY(dalloc(&d_inst_mesh, n_inst)); RT_TRY(dalloc(&d_range_of_mesh, nm));
+    RT_TRY(dalloc(&d_range_info, plan ? plan->range_info.size() : 0));
+    RT_TRY(cudaMemcpyAsync(d_flat_start, flat_start.data(), (nm + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice, stream));
+    if (nm) RT_TRY(cudaMemcpyAsync(d_range_of_mesh, range_of_mesh.data(), nm * sizeof(int), cudaMemcpyHostToDevice, stream));
+    if (n_inst) {
+        RT_TRY(cudaMemcpyAsync(d_inst_mesh, plan->inst_mesh.data(), n_inst * sizeof(uint32_t), cudaMemcpyHostToDevice, stream));
+        RT_TRY(cudaMemcpyAsync(d_range_info, plan->range_info.data(), plan->range_info.size() * sizeof(float4), cudaMemcpyHostToDevice, stream));
+    }
     if (ns) RT_TRY(cudaMemcpyAsync(d_sph, spheres, ns * sizeof(rt_sphere), cudaMemcpyHostToDevice, stream));
     if (nv) RT_TRY(cudaMemcpyAsync(d_vtx, vertices, nv * sizeof(rt_vertex), cudaMemcpyHostToDevice, stream));
     if (ni) RT_TRY(cudaMemcpyAsync(d_idx, indices, ni * sizeof(uint32_t), cudaMemcpyHostToDevice, stream));
@@ -505,13 +560,13 @@ cudaError_t build_scene(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns
     RT_TRY(cudaMemcpyAsync(d_tstart, tri_start.data(), (nm + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice, stream));
 
     RT_TRY(dalloc(&out.prims, 4 * (size_t)n));
-    RT_TRY(dalloc(&out.c0, n)); RT_TRY(dalloc(&out.c1, n)); RT_TRY(dalloc(&out.c2, n));
+    RT_TRY(dalloc(&out.c0, n_cold)); RT_TRY(dalloc(&out.c1, n_cold)); RT_TRY(dalloc(&out.c2, n_cold));
     RT_TRY(dalloc(&out.m0, nmat)); RT_TRY(dalloc(&out.m1, nmat)); RT_TRY(dalloc(&out.m2, nmat));
-    out.n_prims = n; out.n_spheres = ns; out.n_tris = nt; out.n_mats = nmat;
+    out.n_prims = n; out.n_spheres = ns; out.n_tris = nt; out.n_mats = nmat; out.n_inst = n_inst; out.n_cold = n_cold;
     for (uint32_t m = 0; m < nm; m++) if (meshes[m].triangles && (meshes[m].diffuse_tex | meshes[m].normal_tex)) out.has_tex = true;
-    if (out.has_tex) { RT_TRY(dalloc(&out.c3, n)); RT_TRY(dalloc(&out.c4, n)); RT_TRY(dalloc(&out.c5, n)); }
+    if (out.has_tex) { RT_TRY(dalloc(&out.c3, n_cold)); RT_TRY(dalloc(&out.c4, n_cold)); RT_TRY(dalloc(&out.c5, n_cold)); }
     {
-        RawScene rs{d_sph, d_vtx, d_idx, d_mesh, d_tstart, ns, nm, nt};
+        RawScene rs{d_sph, d_vtx, d_idx, d_mesh, d_tstart, ns, nm, nt, d_flat_start, d_inst_mesh, d_range_of_mesh, d_range_info, n_inst};
         if (nmat) setup_materials<<<(nmat + T - 1) / T, T, 0, stream>>>(rs, out.m0, out.m1, out.m2);
         if (n == 0) { RT_TRY(cudaStreamSynchronize(stream)); goto done; }
 
@@ -530,12 +585,12 @@ cudaError_t build_scene(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns
         RT_TRY(cub::DeviceRadixSort::SortPairs(cub_tmp, cub_bytes, keys, keys2, ids, ids2, (int)n, 0, 63, stream));
         gather_boxes<<<nb, T, 0, stream>>>(n, ids2, bmin, bmax, lmin, lmax);
         if (n == 1) {
-            RT_TRY(dalloc(&out.nodes, 4));
+            RT_TRY(dalloc(&out.nodes, 4 * (size_t)(1 + (plan ? plan->blas_nodes : 0u))));
             emit_single<<<1, 1, 0, stream>>>(lmin, lmax, out.nodes);
             identity_slots<<<1, T, 0, stream>>>(n, new_slot);
             out.n_nodes = 1; out.root = 0; h_depth = 1;
         } else {
-            RT_TRY(dalloc(&out.nodes, 4 * (size_t)(n - 1)));
+            RT_TRY(dalloc(&out.nodes, 4 * (size_t)(n - 1 + (plan ? plan->blas_nodes : 0u))));
             bool use_ploc = builder == 0;
             int root = 0;
             if (use_ploc) {
@@ -594,8 +649,15 @@ cudaError_t build_scene(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns
             if (f == f && fabsf(f) <= 3.0e38f && fabsf(f) > m) m = fabsf(f);
         }
         out.max_abs = m;
+        for (int q = 0; q < 3; q++) {
+            int e0 = hb[q], e1 = hb[q + 3]; int b0 = e0 >= 0 ? e0 : e0 ^ 0x7fffffff, b1 = e1 >= 0 ? e1 : e1 ^ 0x7fffffff;
+            memcpy(&out.bounds_lo[q], &b0, 4); memcpy(&out.bounds_hi[q], &b1, 4);
+        }
+        out.n_top_nodes = out.n_nodes;
         // keep what refit_scene needs (ownership moves to `out`; the rest is freed below)
         SceneBuffers::Keep& k = out.keep;
+        k.flat_start = d_flat_start; k.inst_mesh = d_inst_mesh; k.range_of_mesh = d_range_of_mesh; k.range_info = d_range_info;
+        d_flat_start = nullptr; d_inst_mesh = nullptr; d_range_of_mesh = nullptr; d_range_info = nullptr;
         k.sph = d_sph; k.vtx = d_vtx; k.idx = d_idx; k.mesh = d_mesh; k.tstart = d_tstart; k.hot = hot; k.bmin = bmin; k.bmax = bmax;
         k.lmin = lmin; k.lmax = lmax; k.imin = imin; k.imax = imax; k.bounds = d_bounds; k.ids2 = ids2; k.new_slot = new_slot;
         k.children = children; k.ranges = ranges; k.pin = pin; k.plf = plf; k.flags = flags;
@@ -605,11 +667,134 @@ cudaError_t build_scene(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns
     }
 done:
     {
-        void* tmp[] = {d_sph, d_vtx, d_idx, d_mesh, d_tstart, hot, bmin, bmax, lmin, lmax, imin, imax, d_bounds,
+        void* tmp[] = {d_flat_start, d_inst_mesh, d_range_of_mesh, d_range_info, d_sph, d_vtx, d_idx, d_mesh, d_tstart, hot, bmin, bmax, lmin, lmax, imin, imax, d_bounds,
                        keys, keys2, ids, ids2, children, ranges, pin, plf, flags, d_depth, cub_tmp, new_slot,
                        cidA, cidB, nn, cloA, chiA, cloB, chiB, pflags, ppos, d_tot, d_state, scan_tmp};
         for (void* p : tmp) if (p) cudaFreeAsync(p, stream);
     }
+    if (err != cudaSuccess) out.release();
+    return err;
+}
+
+// ---- instancing: import of a range's object-space hierarchy behind the top level ----------------------------------
+// nodes: inner links move by node_base, leaf links by slot_base (leaf = ~((first_slot << 3) | (count - 1)))
+__global__ void import_nodes(uint32_t n_nodes, const float4* __restrict__ src, float4* __restrict__ dst, int node_base, uint32_t slot_base)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_nodes) return;
+    dst[4 * (size_t)i + 0] = src[4 * (size_t)i + 0]; dst[4 * (size_t)i + 1] = src[4 * (size_t)i + 1]; dst[4 * (size_t)i + 2] = src[4 * (size_t)i + 2];
+    const float4 l = src[4 * (size_t)i + 3];
+    int c[2] = {__float_as_int(l.x), __float_as_int(l.y)};
+    for (int q = 0; q < 2; q++) {
+        if (c[q] >= 0) c[q] += node_base;
+        else { const uint32_t leaf = (uint32_t)(~c[q]); c[q] = ~(int)((((leaf >> 3) + slot_base) << 3) | (leaf & 7u)); }
+    }
+    dst[4 * (size_t)i + 3] = make_float4(__int_as_float(c[0]), __int_as_float(c[1]), 0.f, 0.f);
+}
+// raw vertex triples in the range's tree order (the exact test re-derives A = a + pos, e1, e2, n per instance with the
+// reference's own operations, wgsl:172-174,127-129) and the vertex normals by range-local triangle index
+__global__ void import_tris(uint32_t n_tris, const float4* __restrict__ blas_prims, const rt_vertex* __restrict__ vertices, const uint32_t* __restrict__ indices,
+                            uint32_t first, uint32_t offset, float4* __restrict__ iprims, const float4* __restrict__ b0, const float4* __restrict__ b1,
+                            const float4* __restrict__ b2, float4* __restrict__ c0, float4* __restrict__ c1, float4* __restrict__ c2)
+{
+    uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n_tris) return;
+    const uint32_t tri = __float_as_uint(blas_prims[4 * (size_t)s].w);        // the sub-scene has no spheres and one mesh: id = triangle index
+    const rt_vertex& va = vertices[offset + indices[first + tri * 3u]];
+    const rt_vertex& vb = vertices[offset + indices[first + tri * 3u + 1u]];
+    const rt_vertex& vc = vertices[offset + indices[first + tri * 3u + 2u]];
+    iprims[4 * (size_t)s + 0] = make_float4(va.pos[0], va.pos[1], va.pos[2], vb.pos[0]);
+    iprims[4 * (size_t)s + 1] = make_float4(vb.pos[1], vb.pos[2], vc.pos[0], vc.pos[1]);
+    iprims[4 * (size_t)s + 2] = make_float4(vc.pos[2], __uint_as_float(tri), 0.f, 0.f);
+    iprims[4 * (size_t)s + 3] = make_float4(0.f, 0.f, 0.f, 0.f);
+    c0[s] = make_float4(b0[s].x, b0[s].y, b0[s].z, 0.f); c1[s] = b1[s]; c2[s] = b2[s];     // cold records by triangle index (s runs over them too)
+}
+
+// Meshes sharing one (first, triangles, offset) range become instances of ONE object-space hierarchy when that pays: at least two
+// records, a range worth a hierarchy of its own, no texture handles (the texture extension's tangent frame is per flattened record).
+#define RT_INST_MIN_TRIS 32u
+#define RT_INST_AUTO_TRIS 8000000ull               // ~1.4 GB of flattened records + nodes
+cudaError_t build_scene(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns, const rt_vertex* vertices,
+                        uint32_t nv, const uint32_t* indices, uint32_t ni, const rt_mesh* meshes, uint32_t nm,
+                        uint32_t leaf_size, int builder, int ploc_radius, int instancing, cudaStream_t stream)
+{
+    struct Range { uint32_t first, triangles, offset, members; };
+    std::vector<Range> ranges;
+    InstPlan plan;
+    plan.range_of_mesh.assign(nm, -1);
+    if (instancing) {
+        std::vector<int> key_of(nm, -1);
+        for (uint32_t m = 0; m < nm; m++) {
+            const rt_mesh& me = meshes[m];
+            if (me.triangles < RT_INST_MIN_TRIS || (me.diffuse_tex | me.normal_tex)) continue;
+            for (size_t g = 0; g < ranges.size(); g++)
+                if (ranges[g].first == me.first && ranges[g].triangles == me.triangles && ranges[g].offset == me.offset) { key_of[m] = (int)g; break; }
+            if (key_of[m] < 0) { key_of[m] = (int)ranges.size(); ranges.push_back(Range{me.first, me.triangles, me.offset, 0}); }
+            ranges[key_of[m]].members++;
+        }
+        std::vector<int> remap(ranges.size(), -1);
+        std::vector<Range> kept;
+        for (size_t g = 0; g < ranges.size(); g++) if (ranges[g].members >= 2) { remap[g] = (int)kept.size(); kept.push_back(ranges[g]); }
+        ranges.swap(kept);
+        // auto mode: flattened records trace faster while they fit comfortably (C5, 1.0 M instanced triangles: 4,069 Mrays/s flattened
+        // against 3,403 instanced: the per-instance test re-derives A, e1, e2 and the normal and loses the 16-byte back-face reject);
+        // instancing is for scenes whose flattened form would not: more than RT_INST_AUTO_TRIS instanced triangles
+        if (instancing == 2) {
+            uint64_t flat = 0;
+            for (const Range& r : ranges) flat += (uint64_t)r.members * r.triangles;
+            if (flat <= RT_INST_AUTO_TRIS) ranges.clear();
+        }
+        if (!ranges.empty())
+            for (uint32_t m = 0; m < nm; m++)
+                if (key_of[m] >= 0 && remap[key_of[m]] >= 0) { plan.range_of_mesh[m] = remap[key_of[m]]; plan.inst_mesh.push_back(m); }
+    }
+    if (ranges.empty()) return build_scene_impl(out, spheres, ns, vertices, nv, indices, ni, meshes, nm, leaf_size, builder, ploc_radius, nullptr, stream);
+
+    // 1. one object-space hierarchy per range (a sub-scene of one Mesh record with pos = 0: the tested builder as it is)
+    cudaError_t err = cudaSuccess;
+    std::vector<SceneBuffers> blas(ranges.size());
+    uint32_t depth_max = 0;
+    uint32_t n_top = ns + (uint32_t)plan.inst_mesh.size();
+    for (uint32_t m = 0; m < nm; m++) if (plan.range_of_mesh[m] < 0) n_top += meshes[m].triangles;
+    const uint32_t n_top_nodes = n_top > 1 ? n_top - 1 : 1;
+    for (size_t g = 0; g < ranges.size() && err == cudaSuccess; g++) {
+        rt_mesh sub; memset(&sub, 0, sizeof sub);
+        sub.first = ranges[g].first; sub.triangles = ranges[g].triangles; sub.offset = ranges[g].offset;
+        blas[g].pool = out.pool;
+        err = build_scene_impl(blas[g], nullptr, 0, vertices, nv, indices, ni, &sub, 1, leaf_size, builder, ploc_radius, nullptr, stream);
+        if (err != cudaSuccess) break;
+        const SceneBuffers& b = blas[g];
+        plan.range_info.push_back(make_float4(b.bounds_lo[0], b.bounds_lo[1], b.bounds_lo[2], 0.f));
+        plan.range_info.push_back(make_float4(b.bounds_hi[0], b.bounds_hi[1], b.bounds_hi[2], 0.f));
+        const int root = (int)(n_top_nodes + plan.blas_nodes) + b.root;
+        const uint32_t cold_base = n_top + plan.blas_tris;
+        int ri[2] = {root, (int)cold_base}; float4 info; memcpy(&info.x, &ri[0], 4); memcpy(&info.y, &ri[1], 4); info.z = info.w = 0.f;
+        plan.range_info.push_back(info);
+        plan.blas_nodes += b.n_nodes; plan.blas_tris += b.n_prims;
+        if (b.max_depth > depth_max) depth_max = b.max_depth;
+    }
+    // 2. the top level over spheres, flattened triangles and one proxy per instance
+    if (err == cudaSuccess) err = build_scene_impl(out, spheres, ns, vertices, nv, indices, ni, meshes, nm, leaf_size, builder, ploc_radius, &plan, stream);
+    // 3. the ranges' nodes / raw triangles / normals behind it
+    if (err == cudaSuccess) err = cudaMallocFromPoolAsyncOrDefault((void**)&out.iprims, 4 * (size_t)(plan.blas_tris ? plan.blas_tris : 1) * sizeof(float4), out.pool, stream);
+    if (err == cudaSuccess) {
+        const int T = 256;
+        uint32_t node_off = 0, tri_off = 0;
+        for (size_t g = 0; g < ranges.size(); g++) {
+            const SceneBuffers& b = blas[g];
+            import_nodes<<<(b.n_nodes + T - 1) / T, T, 0, stream>>>(b.n_nodes, b.nodes, out.nodes + 4 * (size_t)(out.n_top_nodes + node_off),
+                                                                    (int)(out.n_top_nodes + node_off), tri_off);
+            import_tris<<<(b.n_prims + T - 1) / T, T, 0, stream>>>(b.n_prims, b.prims, b.keep.vtx, b.keep.idx, ranges[g].first, ranges[g].offset,
+                                                                   out.iprims + 4 * (size_t)tri_off, b.c0, b.c1, b.c2,
+                                                                   out.c0 + out.n_prims + tri_off, out.c1 + out.n_prims + tri_off, out.c2 + out.n_prims + tri_off);
+            node_off += b.n_nodes; tri_off += b.n_prims;
+        }
+        out.n_nodes = out.n_top_nodes + plan.blas_nodes; out.n_iprims = plan.blas_tris;
+        out.max_depth += depth_max + 3;                 // the deepest stack: top level, rest of a leaf + continuation + marker, then the range's own depth
+        err = cudaStreamSynchronize(stream);
+        if (err == cudaSuccess) err = cudaGetLastError();
+    }
+    for (SceneBuffers& b : blas) { b.stream = stream; b.release(); }
     if (err != cudaSuccess) out.release();
     return err;
 }
@@ -625,7 +810,7 @@ cudaError_t refit_scene(SceneBuffers& sc, const rt_sphere* spheres, const rt_mes
     if (ns) RT_TRY(cudaMemcpyAsync(k.sph, spheres, ns * sizeof(rt_sphere), cudaMemcpyHostToDevice, stream));
     if (nm) RT_TRY(cudaMemcpyAsync(k.mesh, meshes, nm * sizeof(rt_mesh), cudaMemcpyHostToDevice, stream));
     {
-        RawScene rs{k.sph, k.vtx, k.idx, k.mesh, k.tstart, ns, nm, sc.n_tris};
+        RawScene rs{k.sph, k.vtx, k.idx, k.mesh, k.tstart, ns, nm, sc.n_tris, k.flat_start, k.inst_mesh, k.range_of_mesh, k.range_info, sc.n_inst};
         if (nmat) setup_materials<<<(nmat + T - 1) / T, T, 0, stream>>>(rs, sc.m0, sc.m1, sc.m2);
         if (n == 0) { RT_TRY(cudaStreamSynchronize(stream)); goto done; }
         const int nb = (n + T - 1) / T;

@@ -42,6 +42,7 @@ struct TexDev { cudaTextureObject_t obj; uint32_t width, height; };
 
 struct SceneDev {
     const float4* prims;
+    const float4* iprims;  // instanced ranges: raw vertex triples in tree order (null without instancing)
     const float4* c0; const float4* c1; const float4* c2;
     const float4* c3; const float4* c4; const float4* c5;   // texture extension, may be null
     const struct TexDev* tex; uint32_t n_tex;

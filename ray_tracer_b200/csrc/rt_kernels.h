@@ -57,10 +57,17 @@ struct SceneBuffers {
         float4 *hot = nullptr, *bmin = nullptr, *bmax = nullptr, *lmin = nullptr, *lmax = nullptr, *imin = nullptr, *imax = nullptr;
         int* bounds = nullptr; uint32_t *ids2 = nullptr, *new_slot = nullptr;
         int2 *children = nullptr, *ranges = nullptr; int *pin = nullptr, *plf = nullptr, *flags = nullptr;
+        uint32_t *flat_start = nullptr, *inst_mesh = nullptr; int* range_of_mesh = nullptr; float4* range_info = nullptr;
         uint32_t nm = 0, leaf_size = 0; int parent_shift = 0;
     } keep;
     float4 *m0 = nullptr, *m1 = nullptr, *m2 = nullptr;
     float4* nodes = nullptr;
+    // Instancing: Mesh records that alias one (first, triangles, offset) range share ONE object-space hierarchy; `prims` then
+    // holds a proxy per such record, `iprims` the ranges' raw vertex triples in tree order (4 float4 per triangle:
+    // (a.xyz, b.x) (b.yz, c.xy) (c.z, triangle index, 0, 0) (unused)), `nodes` the top level followed by the ranges' nodes.
+    float4* iprims = nullptr;
+    uint32_t n_inst = 0, n_iprims = 0, n_cold = 0, n_top_nodes = 0;
+    float bounds_lo[3] = {0, 0, 0}, bounds_hi[3] = {0, 0, 0};       // exact bounds of the top level
     uint32_t n_prims = 0, n_spheres = 0, n_tris = 0, n_mats = 0, n_nodes = 0, max_depth = 0;
     int32_t root = -1;
     int builder = 0;               // hierarchy actually built: 0 = PLOC, 1 = radix tree
@@ -72,7 +79,7 @@ struct SceneBuffers {
 // validated). Synchronous with respect to `stream` on return.
 cudaError_t build_scene(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns, const rt_vertex* vertices,
                         uint32_t nv, const uint32_t* indices, uint32_t ni, const rt_mesh* meshes, uint32_t nm,
-                        uint32_t leaf_size, int builder, int ploc_radius, cudaStream_t stream);
+                        uint32_t leaf_size, int builder, int ploc_radius, int instancing /*0 never, 1 when eligible, 2 auto*/, cudaStream_t stream);
 
 // Same topology, new positions / radii / materials: re-derives the records and bounds from the
 // updated spheres and meshes (index ranges must be unchanged) and refits the hierarchy's boxes

@@ -14,12 +14,17 @@ namespace rt {
 
 struct HitRec {
     float dst, u, v;
-    uint32_t id;
+    uint32_t id;          // global primitive order index (the reference's scan order): tie-break key, primary-id AOV
+    uint32_t aux;         // instanced scenes only: index of the cold records, or 0x80000000 | slot of the instance's proxy
 };
+#define RT_MARKER 0x7ffffffe                        // stack word: "leaving the current instance" (instanced scenes)
+#define RT_NO_INST 0xFFFFFFFFu
+// a lane can take a node step when `node` is an inner node index: not a leaf (< 0), not RT_MARKER, not RT_EMPTY (0x7fffffff)
+__device__ __forceinline__ bool is_inner(int node) { return (uint32_t)node < (uint32_t)RT_MARKER; }
 
 // wgsl:106-123 on slot data. Updates `best` under the tie rule of wgsl:154 (strict '<' in
 // the reference's scan order == smaller id wins on equal distance).
-__device__ __forceinline__ void test_sphere(float3 o, float3 d, float4 q0, float4 q1, uint32_t id, HitRec& best)
+__device__ __forceinline__ void test_sphere(float3 o, float3 d, float4 q0, float4 q1, uint32_t id, HitRec& best, uint32_t aux = 0u)
 {
     float3 oc = o - xyz(q0);
     float a = dot3(d, d);
@@ -29,7 +34,7 @@ __device__ __forceinline__ void test_sphere(float3 o, float3 d, float4 q0, float
     if (disc >= 0.0f) {
         float dst = (-b - sqrtf(disc)) / (2.0f * a);
         if (dst >= 0.0f && (dst < best.dst || (dst == best.dst && id < best.id && dst != RT_FLT_MAX))) {
-            best.dst = dst; best.id = id;
+            best.dst = dst; best.id = id; best.aux = aux;
         }
     }
 }
@@ -43,7 +48,7 @@ __device__ __forceinline__ bool triangle_faces_ray(float3 d, float3 n, float& de
     det = -dot3(d, n);
     return det >= 1e-6f;
 }
-__device__ __forceinline__ void test_triangle(float3 o, float3 d, float3 n, float det, float3 A, float3 e1, float3 e2, uint32_t id, HitRec& best)
+__device__ __forceinline__ void test_triangle(float3 o, float3 d, float3 n, float det, float3 A, float3 e1, float3 e2, uint32_t id, HitRec& best, uint32_t aux = 0u)
 {
     float3 ao = o - A;
     float3 dao = cross3(ao, d);
@@ -54,7 +59,7 @@ __device__ __forceinline__ void test_triangle(float3 o, float3 d, float3 n, floa
     float w = (1.0f - u) - v;
     if (dst >= 0.0f && u >= 0.0f && v >= 0.0f && w >= 0.0f &&
         (dst < best.dst || (dst == best.dst && id < best.id && dst != RT_FLT_MAX))) {
-        best.dst = dst; best.u = u; best.v = v; best.id = id;
+        best.dst = dst; best.u = u; best.v = v; best.id = id; best.aux = aux;
     }
 }
 
@@ -217,27 +222,36 @@ static __device__ __noinline__ void apply_textures(const SceneDev& sc, uint32_t 
 
 // One path segment's shading (wgsl:236-273). Consumes RNG exactly as the reference does and
 // replaces the ray by the bounce ray.
-template <bool TEX>
+// INST (instanced scenes): the cold records are addressed through hit.aux, the material of an instanced triangle is its proxy's.
+template <bool TEX, bool INST = false>
 __device__ __forceinline__ void shade_hit(const SceneDev& sc, const HitRec& hit, float3& ro, float3& rd, uint32_t& rng,
                                           float4& incoming, float4& color)
 {
     float3 hp = fma3(rd, hit.dst, ro);
-    float4 k0 = __ldg(sc.c0 + hit.id);
+    uint32_t cidx = hit.id, mat_inst = RT_NO_INST;
+    if (INST) {
+        if (hit.aux & 0x80000000u) {
+            const float4 p1 = __ldg(sc.prims + 4 * (size_t)(hit.aux & 0x7fffffffu) + 1);    // (root, first global id, first cold index, material)
+            cidx = __float_as_uint(p1.z) + (hit.id - __float_as_uint(p1.y));
+            mat_inst = __float_as_uint(p1.w);
+        } else cidx = hit.aux;
+    }
+    float4 k0 = __ldg(sc.c0 + cidx);
     float3 normal;
     if (hit.id < sc.n_spheres) {
         normal = normalize3(hp - xyz(k0));
     } else {
-        float4 k1 = __ldg(sc.c1 + hit.id), k2 = __ldg(sc.c2 + hit.id);
+        float4 k1 = __ldg(sc.c1 + cidx), k2 = __ldg(sc.c2 + cidx);
         float w = (1.0f - hit.u) - hit.v;
         normal = normalize3(fma3(xyz(k2), hit.v, fma3(xyz(k1), hit.u, xyz(k0) * w)));
     }
-    const uint32_t mi = __float_as_uint(k0.w);
+    const uint32_t mi = (INST && mat_inst != RT_NO_INST) ? mat_inst : __float_as_uint(k0.w);
     float4 mcolor = __ldg(sc.m0 + mi), emitted = __ldg(sc.m1 + mi);
     const float4 mat2 = __ldg(sc.m2 + mi);
     const float smooth = mat2.x;
     if (TEX && hit.id >= sc.n_spheres) {
         const uint32_t dtex = __float_as_uint(mat2.y), ntex = __float_as_uint(mat2.z);
-        if ((dtex | ntex) != 0u) apply_textures(sc, hit.id, hit.u, hit.v, dtex, ntex, normal, mcolor);
+        if ((dtex | ntex) != 0u) apply_textures(sc, cidx, hit.u, hit.v, dtex, ntex, normal, mcolor);
     }
     float3 unit_dir = normalize3(rd);
     float3 nd;

@@ -57,9 +57,6 @@ __device__ unsigned long long g_lane_stats[16];
 //              primitives are tested with most lanes busy.
 // The warp goes back to SHADE when enough lanes have finished their ray (sched_s_min), the
 // others keep their traversal state (node, stack, closest hit) across the switch.
-#ifndef RT_PARK2
-#define RT_PARK2 0                   // 1: a lane may park two leaves before it stops descending (A/B)
-#endif
 #ifndef RT_NODE_U2
 #define RT_NODE_U2 1                 // lanes able to step for a second / third node step on the same warp vote
 #endif
@@ -87,7 +84,13 @@ __device__ __forceinline__ void fold_store(const LaunchParams& lp, float4* accum
     }
 }
 
-template <bool BRUTE, bool DETAIL, bool TEX, bool PF, bool FOLD>
+// INST = true (scenes with instanced mesh ranges, SceneBuffers): the hierarchy has two levels.  A top-level leaf may hold a proxy
+// record (pos, 0x80000000 | k) (root, first id, first cold index, material); a lane that meets one pushes the rest of its leaf, its
+// next node and RT_MARKER, shifts its slab constants into the range's object space (o' = o - pos: only -o/d changes) and descends
+// into the range's own nodes.  Leaves there hold RAW vertex triples: the test forms A = a + pos, B, C, the edges and their cross
+// product per instance with the reference's own operations (wgsl:172-174,127-129), so the result is that of the flattened record
+// bit for bit.  Popping RT_MARKER with no leaf pending restores the world-space constants.
+template <bool BRUTE, bool DETAIL, bool TEX, bool PF, bool FOLD, bool INST>
 __global__ void __launch_bounds__(RT_BLOCK_THREADS, RT_MIN_BLOCKS)
 trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ staging, float4* accum,
              uint32_t* __restrict__ primary_ids, unsigned long long* __restrict__ counters,
@@ -126,13 +129,15 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
     uint32_t& pix = s_item[threadIdx.x].x;
     uint32_t& fi = s_item[threadIdx.x].y;
     total = make_float4(0.f, 0.f, 0.f, 0.f); pix = 0; fi = 0;
-    HitRec best; best.dst = RT_FLT_MAX; best.u = best.v = 0.f; best.id = RT_MISS;
+    HitRec best; best.dst = RT_FLT_MAX; best.u = best.v = 0.f; best.id = RT_MISS; best.aux = 0u;
+    uint32_t cur_inst = RT_NO_INST;                // INST: slot of the proxy whose range the lane is inside
+    auto leave_instance = [&]() {                  // back to world space: -o/d again
+        cur_inst = RT_NO_INST;
+        slab.noi_xy = f2_pack(-(ro.x * f2_lo(slab.inv_xy)), -(ro.y * f2_hi(slab.inv_xy))); slab.noi_z = -(ro.z * slab.inv_z);
+    };
     float cull = RT_FLT_MAX;                       // best.dst with slack: the distance beyond which a subtree is skipped (see RT_CULL_SLACK)
     int node = RT_EMPTY, sp = 0;                   // current node (inner >= 0, leaf < 0, or RT_EMPTY) / stack height
     uint32_t leaf_first = 0, leaf_count = 0;       // parked leaf primitives
-#if RT_PARK2
-    int leaf2 = 0;                                 // a second parked leaf (encoded child word, < 0), 0 = none
-#endif
 
     for (;;) {
         // ======================= SHADE section =======================
@@ -148,7 +153,7 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
                     bool done;
                     if (best.id != RT_MISS) {
                         if (DETAIL) n_hits++;
-                        shade_hit<TEX>(sc, best, ro, rd, rng, incoming, color);
+                        shade_hit<TEX, INST>(sc, best, ro, rd, rng, incoming, color);
                         seg++;
                         done = seg > lp.bounces;
                     } else {
@@ -250,10 +255,8 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
                 }
                 // ---- start the traversal of (ro, rd): wgsl:234 ----
                 best.dst = RT_FLT_MAX; best.u = 0.0f; best.v = 0.0f; best.id = RT_MISS; cull = RT_FLT_MAX;
+                if (INST) { best.aux = 0u; cur_inst = RT_NO_INST; }
                 sp = 1; node = RT_EMPTY; leaf_count = 0;
-#if RT_PARK2
-                leaf2 = 0;
-#endif
                 if (lp.bounces < 0) {
                     total = total + incoming; j++;                // wgsl:233 loop never runs: the path ends untraced
                     traced = false;                               // stays "shading" as a fresh lane needing a path
@@ -275,12 +278,12 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
         for (;;) {
             // ---- node loop: descend; a lane reaching a leaf parks it (once) and keeps going ----
             // (left when fewer than `thr` lanes can still take a node step; thr adapts so a thin warp still advances)
-            const int cnt0 = __popc(__ballot_sync(0xffffffffu, !shading && node >= 0 && node != RT_EMPTY));
+            const int cnt0 = __popc(__ballot_sync(0xffffffffu, !shading && is_inner(node)));
             const int thr = max(1, min(lp.sched_n_stay, (cnt0 + 1) >> 1));
             auto node_step = [&]() {
-                LANE_STAT(0, lane == 0); LANE_STAT(1, !shading && node >= 0 && node != RT_EMPTY); LANE_STAT(2, shading && !idle); LANE_STAT(3, !shading && node < 0);
+                LANE_STAT(0, lane == 0); LANE_STAT(1, !shading && is_inner(node)); LANE_STAT(2, shading && !idle); LANE_STAT(3, !shading && node < 0);
                 LANE_STAT(4, !shading && node == RT_EMPTY && leaf_count != 0u); LANE_STAT(5, idle);
-                if (!shading && node >= 0 && node != RT_EMPTY) {
+                if (!shading && is_inner(node)) {
                     if (DETAIL) n_nodes++;
                     float ltn, ltf, rtn, rtf; int cl, cr;
                     node_test(sc.nodes + 4 * (size_t)node, slab, cull, ltn, ltf, rtn, rtf, cl, cr);
@@ -296,29 +299,17 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
                     } else if (hl) node = cl;
                     else if (hr) node = cr;
                     else node = stack[--sp];
-#if RT_PARK2
-                    if (node < 0) {                              // park the leaf (two slots), keep descending
-                        if (leaf_count == 0u) {
-                            const uint32_t leaf = (uint32_t)(~node);
-                            leaf_first = leaf >> 3; leaf_count = (leaf & 7u) + 1u;
-                            node = stack[--sp];
-                        } else if (leaf2 == 0) {
-                            leaf2 = node;
-                            node = stack[--sp];
-                        }
-                    }
-#else
+                    if (INST && node == RT_MARKER && leaf_count == 0u) { leave_instance(); node = stack[--sp]; }
                     if (node < 0 && leaf_count == 0u) {          // park the leaf, keep descending
                         const uint32_t leaf = (uint32_t)(~node);
                         leaf_first = leaf >> 3; leaf_count = (leaf & 7u) + 1u;
                         node = stack[--sp];
                     }
-#endif
                 }
             };
             for (;;) {
                 // one vote pays for up to four node steps when most lanes can take them (a lane that runs out idles for the rest)
-                const int cnt = __popc(__ballot_sync(0xffffffffu, !shading && node >= 0 && node != RT_EMPTY));
+                const int cnt = __popc(__ballot_sync(0xffffffffu, !shading && is_inner(node)));
                 if (cnt < thr) break;
                 node_step();
                 if (cnt >= RT_NODE_U2) node_step();
@@ -329,13 +320,41 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
             while (__ballot_sync(0xffffffffu, !shading && leaf_count != 0u)) {
                 LANE_STAT(6, lane == 0); LANE_STAT(7, !shading && leaf_count != 0u);
                 if (!shading && leaf_count != 0u) {
+                    if (INST && cur_inst != RT_NO_INST) {
+                        // a triangle of the instanced range: raw a, b, c + the proxy's pos, then the reference's own sequence
+                        const float4* pr = sc.iprims + 4 * (size_t)leaf_first;
+                        float4 r0, r1, p0, p1;
+                        ldg256(pr, r0, r1);
+                        const float4 r2 = __ldg(pr + 2);
+                        ldg256(sc.prims + 4 * (size_t)cur_inst, p0, p1);
+                        const float3 pos = xyz(p0);
+                        const float3 A = xyz(r0) + pos, B = f3(r0.w, r1.x, r1.y) + pos, C = f3(r1.z, r1.w, r2.x) + pos;   // wgsl:172-174
+                        const float3 e1 = B - A, e2 = C - A;                                                            // wgsl:127-128
+                        const float3 nrm = cross3(e1, e2);                                                              // wgsl:129
+                        if (DETAIL) n_tri++;
+                        float det;
+                        if (triangle_faces_ray(rd, nrm, det))
+                            test_triangle(ro, rd, nrm, det, A, e1, e2, __float_as_uint(p1.y) + __float_as_uint(r2.y), best, 0x80000000u | cur_inst);
+                    } else {
                     const float4* pr = sc.prims + 4 * (size_t)leaf_first;
                     float4 q0, q1;
                     ldg256(pr, q0, q1);
                     const uint32_t id = __float_as_uint(q0.w);
-                    if (id < sc.n_spheres) {
+                    if (INST && (id & 0x80000000u)) {
+                        // proxy of an instance: remember what is left of this leaf and where to go on, then enter the range's hierarchy
+                        // (a lane whose node is RT_EMPTY popped the sentinel, sp == 0: the sentinel itself is its continuation)
+                        if (node == RT_EMPTY) sp = 1;
+                        if (leaf_count > 1u) stack[sp++] = ~(int)(((leaf_first + 1u) << 3) | (leaf_count - 2u));
+                        if (node != RT_EMPTY) stack[sp++] = node;
+                        stack[sp++] = RT_MARKER;
+                        node = __float_as_int(q1.x);
+                        cur_inst = leaf_first;
+                        slab.noi_xy = f2_fma(f2_pack(q0.x, q0.y), slab.inv_xy, slab.noi_xy);          // -(o - pos)/d = -o/d + pos/d
+                        slab.noi_z = __fmaf_rn(q0.z, slab.inv_z, slab.noi_z);
+                        leaf_count = 1u;
+                    } else if (id < sc.n_spheres) {
                         if (DETAIL) n_sph++;
-                        test_sphere(ro, rd, q0, q1, id, best);
+                        test_sphere(ro, rd, q0, q1, id, best, id);
                     } else {
                         if (DETAIL) n_tri++;
                         float det;
@@ -345,31 +364,20 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
                         if (triangle_faces_ray(rd, xyz(q0), det)) {
                             float4 q2, q3;
                             ldg256(pr + 2, q2, q3);
-                            test_triangle(ro, rd, xyz(q0), det, xyz(q1), f3(q1.w, q2.x, q2.y), f3(q2.z, q2.w, q3.x), id, best);
+                            test_triangle(ro, rd, xyz(q0), det, xyz(q1), f3(q1.w, q2.x, q2.y), f3(q2.z, q2.w, q3.x), id, best, __float_as_uint(q3.y));
                         }
+                    }
                     }
                     cull = best.dst * RT_CULL_SLACK;
                     leaf_first++;
-#if RT_PARK2
                     if (--leaf_count == 0u) {
-                        if (leaf2 != 0) {                        // the second parked leaf moves up
-                            const uint32_t leaf = (uint32_t)(~leaf2);
-                            leaf_first = leaf >> 3; leaf_count = (leaf & 7u) + 1u;
-                            leaf2 = 0;
-                            if (node < 0) { leaf2 = node; node = stack[--sp]; }
-                        } else if (node < 0) {                   // a leaf was waiting in `node`
+                        if (INST && node == RT_MARKER) { leave_instance(); node = stack[--sp]; }
+                        if (node < 0) {                              // a leaf was waiting in `node`
                             const uint32_t leaf = (uint32_t)(~node);
                             leaf_first = leaf >> 3; leaf_count = (leaf & 7u) + 1u;
                             node = stack[--sp];
                         }
                     }
-#else
-                    if (--leaf_count == 0u && node < 0) {        // a second leaf was waiting in `node`
-                        const uint32_t leaf = (uint32_t)(~node);
-                        leaf_first = leaf >> 3; leaf_count = (leaf & 7u) + 1u;
-                        node = stack[--sp];
-                    }
-#endif
                 }
             }
             // lanes with nothing left have their closest hit
@@ -443,24 +451,29 @@ typedef void (*TraceFn)(SceneDev, CameraDev, LaunchParams, float4*, float4*, uin
 // the extra requests cost 1.5 %, so the launcher picks the variant by scene size.
 #define RT_PF_MAX_PRIMS 262144u
 template <bool FOLD>
-TraceFn trace_variant_t(bool brute, bool detail, bool tex, bool pf)
+TraceFn trace_variant_t(bool brute, bool detail, bool tex, bool pf, bool inst)
 {
     static const TraceFn table[12] = {
-        trace_kernel<false, false, false, false, FOLD>, trace_kernel<false, false, true, false, FOLD>, trace_kernel<false, true, false, false, FOLD>, trace_kernel<false, true, true, false, FOLD>,
-        trace_kernel<false, false, false, true, FOLD>,  trace_kernel<false, false, true, true, FOLD>,  trace_kernel<false, true, false, true, FOLD>,  trace_kernel<false, true, true, true, FOLD>,
-        trace_kernel<true, false, false, false, FOLD>,  trace_kernel<true, false, true, false, FOLD>,  trace_kernel<true, true, false, false, FOLD>,  trace_kernel<true, true, true, false, FOLD>};
+        trace_kernel<false, false, false, false, FOLD, false>, trace_kernel<false, false, true, false, FOLD, false>, trace_kernel<false, true, false, false, FOLD, false>, trace_kernel<false, true, true, false, FOLD, false>,
+        trace_kernel<false, false, false, true, FOLD, false>,  trace_kernel<false, false, true, true, FOLD, false>,  trace_kernel<false, true, false, true, FOLD, false>,  trace_kernel<false, true, true, true, FOLD, false>,
+        trace_kernel<true, false, false, false, FOLD, false>,  trace_kernel<true, false, true, false, FOLD, false>,  trace_kernel<true, true, false, false, FOLD, false>,  trace_kernel<true, true, true, false, FOLD, false>};
+    // instanced scenes: hierarchy traversal only (the exhaustive scan needs flattened records), no push-time prefetch
+    static const TraceFn inst_table[4] = {
+        trace_kernel<false, false, false, false, FOLD, true>, trace_kernel<false, false, true, false, FOLD, true>,
+        trace_kernel<false, true, false, false, FOLD, true>,  trace_kernel<false, true, true, false, FOLD, true>};
+    if (inst) return inst_table[(detail ? 2 : 0) | (tex ? 1 : 0)];
     return table[(brute ? 8 : (pf ? 4 : 0)) | (detail ? 2 : 0) | (tex ? 1 : 0)];
 }
-TraceFn trace_variant(bool brute, bool detail, bool tex, bool pf, bool fold)
+TraceFn trace_variant(bool brute, bool detail, bool tex, bool pf, bool fold, bool inst)
 {
-    return fold ? trace_variant_t<true>(brute, detail, tex, pf) : trace_variant_t<false>(brute, detail, tex, pf);
+    return fold ? trace_variant_t<true>(brute, detail, tex, pf, inst) : trace_variant_t<false>(brute, detail, tex, pf, inst);
 }
 } // namespace
 
-int trace_blocks_per_sm(bool brute, bool detail, bool tex, bool pf, bool fold)
+int trace_blocks_per_sm(bool brute, bool detail, bool tex, bool pf, bool fold, bool inst)
 {
     int n = 0;
-    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, trace_variant(brute, detail, tex, pf, fold), RT_BLOCK_THREADS, 0);
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, trace_variant(brute, detail, tex, pf, fold, inst), RT_BLOCK_THREADS, 0);
     return (e == cudaSuccess && n > 0) ? n : 1;
 }
 
@@ -471,18 +484,20 @@ cudaError_t launch_trace(const SceneDev& sc, const CameraDev& cam, const LaunchP
                          bool brute, bool detail, bool fold, int n_sms, cudaStream_t stream)
 {
     if (lp.n_warp_tiles == 0 || lp.n_frames == 0) return cudaSuccess;
+    const bool inst = sc.iprims != nullptr;
+    if (inst && brute) return cudaErrorNotSupported;           // rt_api.cu refuses this combination with a message
     cudaError_t e = cudaMemsetAsync(queue, 0, sizeof(unsigned long long), stream);
     if (e != cudaSuccess) return e;
     const bool tex = sc.c3 != nullptr && sc.n_tex != 0u;       // texture code only when the scene carries handles and a table is bound
     const uint64_t n_items = (uint64_t)lp.n_warp_tiles * (fold ? 1u : lp.n_frames) * 32ull;
     const uint64_t per_grab = fold ? 32ull : RT_QUEUE_CHUNK;
     const uint64_t warps_needed = (n_items + per_grab - 1) / per_grab;
-    const bool pf = !brute && sc.n_prims <= RT_PF_MAX_PRIMS;
-    uint64_t blocks = (uint64_t)n_sms * trace_blocks_per_sm(brute, detail, tex, pf, fold);
+    const bool pf = !brute && !inst && sc.n_prims <= RT_PF_MAX_PRIMS;
+    uint64_t blocks = (uint64_t)n_sms * trace_blocks_per_sm(brute, detail, tex, pf, fold, inst);
     const uint64_t cap = (warps_needed + RT_BLOCK_THREADS / 32 - 1) / (RT_BLOCK_THREADS / 32);
     if (blocks > cap) blocks = cap;
     dim3 grid((unsigned)blocks), block(RT_BLOCK_THREADS);
-    trace_variant(brute, detail, tex, pf, fold)<<<grid, block, 0, stream>>>(sc, cam, lp, staging, accum, primary_ids, counters, queue);
+    trace_variant(brute, detail, tex, pf, fold, inst)<<<grid, block, 0, stream>>>(sc, cam, lp, staging, accum, primary_ids, counters, queue);
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
     return fold ? cudaSuccess : launch_blend(lp, staging, accum, stream);
 }

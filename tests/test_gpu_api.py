@@ -196,19 +196,20 @@ def test_update_records_equals_fresh_upload(rtlib):
     sp2["position"] += rng.normal(0, 25.0, sp2["position"].shape).astype(np.float32)
     sp2["radius"] *= np.float32(1.5)
     ms2["color"][:, 0] = 0.9
-    for builder in (0, 1):
+    for builder, inst in ((0, 1), (1, 1), (0, 0)):               # instanced (a top-level refit only) and flattened records
         def render(tr):
             tr.set_camera(cam); tr.set_params(number_of_bounces=3, rays_per_pixel=1, skybox=1, frames=0)
             tr.set_option(rtlib._lib.RT_OPT_PRIMARY_IDS, 1)
             tr.clear(); tr.reset_counters(); tr.render_frames(0, 1)
             return tr.read_accum(), tr.read_primary_ids(), tr.counters()["rays"]
-        a = rtlib.RayTracer(0, 96, 54); a.set_option(rtlib._lib.RT_OPT_BUILDER, builder)
+        a = rtlib.RayTracer(0, 96, 54); a.set_option(rtlib._lib.RT_OPT_BUILDER, builder); a.set_option(rtlib._lib.RT_OPT_INSTANCING, inst)
         a.upload_scene(sp, vs, ix, ms)
+        assert a.bvh_stats()["n_prims"] == (2000 + 128 if inst else 2000 + 64 * 15704)
         img0, _, _ = render(a)
         a.update_records(sp2, ms2)
         img_a, ids_a, rays_a = render(a)
-        b = rtlib.RayTracer(0, 96, 54); b.set_option(rtlib._lib.RT_OPT_BUILDER, builder)
-        b.upload_scene(sp2, vs, ix, ms2)
+        b = rtlib.RayTracer(0, 96, 54); b.set_option(rtlib._lib.RT_OPT_BUILDER, builder); b.set_option(rtlib._lib.RT_OPT_INSTANCING, 0)
+        b.upload_scene(sp2, vs, ix, ms2)                                           # the fresh upload is the flattened one
         img_b, ids_b, rays_b = render(b)
         assert not np.array_equal(img0, img_a)
         assert np.array_equal(ids_a, ids_b) and rays_a == rays_b

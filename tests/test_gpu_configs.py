@@ -9,9 +9,12 @@ from util import assert_bits_equal
 pytestmark = pytest.mark.gpu
 
 
-def _gpu(rt, scene, w, h, frames, bounces, sky, brute=False, leaf=None, builder=None, radius=None, kernel=None, slots=None, rpp=1, detail=False):
+def _gpu(rt, scene, w, h, frames, bounces, sky, brute=False, leaf=None, builder=None, radius=None, kernel=None, slots=None, rpp=1, detail=False, inst=None):
     cam, sp, vs, ix, ms = scene.as_tuple()
     tr = rt.RayTracer(0, w, h)
+    tr.set_option(rt._lib.RT_OPT_TRAVERSAL, 1 if brute else 0)      # before the upload: the exhaustive scan needs flattened records
+    if inst is not None:
+        tr.set_option(rt._lib.RT_OPT_INSTANCING, inst)
     if leaf is not None:
         tr.set_option(rt._lib.RT_OPT_LEAF_SIZE, leaf)
     if builder is not None:
@@ -30,7 +33,6 @@ def _gpu(rt, scene, w, h, frames, bounces, sky, brute=False, leaf=None, builder=
     tr.set_camera(cam)
     tr.set_params(number_of_bounces=bounces, rays_per_pixel=rpp, skybox=sky, frames=0)
     tr.set_option(rt._lib.RT_OPT_PRIMARY_IDS, 1)
-    tr.set_option(rt._lib.RT_OPT_TRAVERSAL, 1 if brute else 0)
     tr.render_frames(0, frames)
     out = tr.read_accum(), tr.read_primary_ids(), tr.counters(), tr.bvh_stats()
     tr.close()
@@ -115,11 +117,62 @@ def test_stress_scene_builds_and_matches_brute_force_on_a_crop(rtlib):
     on a small image."""
     from ray_tracer_b200 import configs
     scene, meta = configs.build("c5_stress", 64, 36)
-    a, aid, ac, st = _gpu(rtlib, scene, 64, 36, 1, 3, 1)
+    a, aid, ac, st = _gpu(rtlib, scene, 64, 36, 1, 3, 1, inst=0)
     assert st["n_prims"] == 100000 + 64 * 15704
     b, bid, bc, _ = _gpu(rtlib, scene, 64, 36, 1, 3, 1, brute=True)
     assert np.array_equal(aid, bid) and ac["rays"] == bc["rays"]
     assert_bits_equal(a, b, "c5")
+
+
+def test_instanced_hierarchy_equals_flattened_records(rtlib):
+    """C5's 128 Mesh records alias the teapot's two index ranges (wgsl:159-175 makes that translation-only instancing): with RT_OPT_INSTANCING = 1
+    they share two object-space hierarchies behind 128 proxies of a top level; the image, the primary ids and every counter equal
+    the flattened build (1.1 M records) and the exhaustive scan bit for bit, at 4K for the first two."""
+    from ray_tracer_b200 import configs
+    scene, meta = configs.build("c5_stress", 240, 136)
+    a, aid, ac, sa = _gpu(rtlib, scene, 240, 136, 2, 8, 1, detail=True, inst=1)         # instanced
+    f, fid, fc, sf = _gpu(rtlib, scene, 240, 136, 2, 8, 1, detail=True, inst=0)         # flattened
+    b, bid, bc, _ = _gpu(rtlib, scene, 240, 136, 2, 8, 1, brute=True)
+    assert sa["n_prims"] == 100000 + 128 and sf["n_prims"] == 100000 + 64 * 15704
+    assert sa["n_nodes"] == (100000 + 128 - 1) + (15704 - 2)                            # top level + one hierarchy per range
+    assert np.array_equal(aid, fid) and np.array_equal(aid, bid)
+    assert ac["rays"] == fc["rays"] == bc["rays"] and ac["hit_segments"] == fc["hit_segments"]
+    assert_bits_equal(a, f, "instanced vs flattened")
+    assert_bits_equal(a, b, "instanced vs exhaustive")
+    scene, meta = configs.build("c5_stress")
+    p = meta["params"]
+    a, aid, ac, _ = _gpu(rtlib, scene, p["width"], p["height"], 1, 8, 1, inst=1)
+    f, fid, fc, sf = _gpu(rtlib, scene, p["width"], p["height"], 1, 8, 1)               # auto mode flattens a scene of this size
+    assert sf["n_prims"] == 100000 + 64 * 15704
+    assert np.array_equal(aid, fid) and ac["rays"] == fc["rays"]
+    assert_bits_equal(a, f, "instanced vs flattened at 4K")
+
+
+def test_instanced_scene_mixed_with_flat_meshes_and_leaf_sizes(rtlib, oracle):
+    """Two instanced ranges + a flattened mesh + spheres, every leaf size (a proxy sharing a top-level leaf with another
+    primitive exercises the pushed-back rest of the leaf) and both builders, against the CPU oracle."""
+    from ray_tracer_b200 import configs, host
+    base, _ = configs.build("c3_teapot", 96, 54)
+    cam, sp, vs, ix, ms = base.as_tuple()
+    recs = []
+    for k, dx in enumerate((-120.0, 0.0, 120.0)):                # three copies of the teapot's two meshes (ranges alias)
+        for m in ms:
+            r = m.copy(); r["pos"] = (dx + m["pos"][0], 30.0 * k, 0.0); r["color"] = (0.3 + 0.3 * k, 0.5, 0.9 - 0.3 * k, 1.0)
+            recs.append(r)
+    small = ms[1].copy(); small["triangles"] = 20; small["pos"] = (0.0, -80.0, 10.0)      # below the instancing threshold: flattened
+    recs.append(small)
+    ms2 = np.array(recs, dtype=ms.dtype)
+    sp2 = np.zeros(2, sp.dtype)
+    sp2["position"] = [(0.0, 0.0, -1000.0), (60.0, -40.0, 30.0)]; sp2["radius"] = [995.0, 12.0]
+    sp2["color"] = [(0.5, 0.5, 0.5, 1.0), (1.0, 1.0, 1.0, 1.0)]; sp2["smoothness"] = [0.0, -1.0]
+    scene = host.Scene(base.camera, sp2, vs, ix, ms2)
+    ci, cid, cc = _cpu(oracle, scene, 96, 54, 1, 4, 1)
+    for leaf in (1, 2, 4, 8):
+        for builder in (0, 1):
+            gi, gid, gc, st = _gpu(rtlib, scene, 96, 54, 1, 4, 1, leaf=leaf, builder=builder, inst=1)
+            assert st["n_prims"] == 2 + 20 + 6
+            assert np.array_equal(gid, cid) and gc["rays"] == int(cc[0])
+            assert_bits_equal(gi, ci, "instanced mix, leaf %d builder %d" % (leaf, builder))
 
 
 @pytest.mark.parametrize("name,w,h,frames,slots", [("c1_balls", 320, 180, 3, None), ("c2_cube", 320, 180, 3, 4096), ("c3_teapot", 480, 270, 2, 1 << 16),
