@@ -40,7 +40,7 @@ namespace rt {
 // `staging` (lp.n_frames planes of W*H float4) and blend_kernel folds them into `accum`.
 cudaError_t launch_trace(const SceneDev& sc, const CameraDev& cam, const LaunchParams& lp, float4* staging, float4* accum,
                          uint32_t* primary_ids, unsigned long long* counters, unsigned long long* queue,
-                         bool brute, bool detail, bool fold, int n_sms, cudaStream_t stream);
+                         bool brute, bool detail, bool fold, int n_sms, cudaStream_t stream, bool with_blend = true);
 
 // Device-resident scene: SoA primitive arrays + LBVH, built on the GPU from the AoS records.
 struct SceneBuffers {

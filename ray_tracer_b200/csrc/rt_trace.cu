@@ -481,7 +481,7 @@ int trace_blocks_per_sm(bool brute, bool detail, bool tex, bool pf, bool fold, b
 // planes and blend_kernel folds them into `accum`.
 cudaError_t launch_trace(const SceneDev& sc, const CameraDev& cam, const LaunchParams& lp, float4* staging, float4* accum,
                          uint32_t* primary_ids, unsigned long long* counters, unsigned long long* queue,
-                         bool brute, bool detail, bool fold, int n_sms, cudaStream_t stream)
+                         bool brute, bool detail, bool fold, int n_sms, cudaStream_t stream, bool with_blend)
 {
     if (lp.n_warp_tiles == 0 || lp.n_frames == 0) return cudaSuccess;
     const bool inst = sc.iprims != nullptr;
@@ -499,7 +499,7 @@ cudaError_t launch_trace(const SceneDev& sc, const CameraDev& cam, const LaunchP
     dim3 grid((unsigned)blocks), block(RT_BLOCK_THREADS);
     trace_variant(brute, detail, tex, pf, fold, inst)<<<grid, block, 0, stream>>>(sc, cam, lp, staging, accum, primary_ids, counters, queue);
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
-    return fold ? cudaSuccess : launch_blend(lp, staging, accum, stream);
+    return (fold || !with_blend) ? cudaSuccess : launch_blend(lp, staging, accum, stream);
 }
 
 #ifdef RT_LANE_STATS

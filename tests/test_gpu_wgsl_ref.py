@@ -156,3 +156,29 @@ def test_wide_seed_mode_at_4k(rtlib, oracle):
         with wr.seed_mode(1):
             rw = wr.render(scene, w, h, 2, 3, 1, 1, 0, None, None, sx, sy)
         assert_bits_equal(gw[::sy, ::sx], rw[::sy, ::sx], "wide seed mode vs oracle/_ref")
+
+
+def test_pipelined_launches_are_result_invisible(rtlib):
+    """A render call that needs several launches (dispatches beyond the staging budget) alternates them between two streams
+    (RT_OPT_PIPELINE): same image and counters as serial launches and as one long launch, also when resumed and sharded."""
+    w, h, frames = 240, 136, 41
+    scene = _config("c3_teapot", w, h)
+    cam, sp, vs, ix, ms = scene
+    out = []
+    for mib, pipe, shard in ((4096, 1, None), (16, 1, None), (16, 0, None), (16, 1, (1, 2, 1, 3)), (4096, 1, (1, 2, 1, 3))):
+        tr = rtlib.RayTracer(0, w, h)
+        tr.set_option(rtlib._lib.RT_OPT_STAGING_MIB, mib); tr.set_option(rtlib._lib.RT_OPT_PIPELINE, pipe)
+        tr.upload_scene(sp, vs, ix, ms); tr.set_camera(cam.view(rtlib.CAMERA_DT))
+        tr.set_params(number_of_bounces=4, rays_per_pixel=1, skybox=1, frames=0)
+        if shard:
+            tr.set_shard(*shard)
+        tr.render_frames(0, frames)
+        tr.render_frames(frames, 5)                        # a second call resumes the running mean
+        out.append((tr.read_accum(), tr.counters()))
+        tr.close()
+    assert out[0][1]["launches"] == 2 and out[1][1]["launches"] >= 4 and out[2][1]["launches"] >= 3
+    for k in (1, 2):
+        assert out[k][1]["rays"] == out[0][1]["rays"]
+        assert_bits_equal(out[k][0], out[0][0], "pipelined / serial launches")
+    assert out[3][1]["rays"] == out[4][1]["rays"]
+    assert_bits_equal(out[3][0], out[4][0], "pipelined launches under tile + sample sharding")
