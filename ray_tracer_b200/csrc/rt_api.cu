@@ -195,6 +195,7 @@ int launch(rt_ctx* c, int32_t first_frame, uint32_t n_frames, bool want_ids, int
     const uint32_t tiles = lp.tiles_x * ((c->height + 7) / 8);
     lp.n_warp_tiles = 2u * (tiles > c->tile_rank ? (tiles - c->tile_rank + c->tile_world - 1) / c->tile_world : 0);
     lp.seed_mode = (int32_t)c->opt_seed_mode;
+    lp.queue_guide = (uint32_t)(n_frames <= 16u ? 2ull * RT_QUEUE_GUIDE : RT_QUEUE_GUIDE);
     lp.div_frames = rt::make_fastdiv(n_frames); lp.div_tiles_x = rt::make_fastdiv(lp.tiles_x); lp.div_width = rt::make_fastdiv(c->width);
     lp.rpp_scale = (lp.rpp > 0 && (lp.rpp & (lp.rpp - 1)) == 0) ? 1.0f / (float)lp.rpp : 0.0f;
     lp.sched_n_stay = (int32_t)(c->opt_sched & 0xff); if (lp.sched_n_stay < 1) lp.sched_n_stay = 1; lp.sched_l_stay = (int32_t)((c->opt_sched >> 8) & 0xff); lp.sched_s_min = (int32_t)((c->opt_sched >> 16) & 0xff);

@@ -101,7 +101,7 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
     stack[0] = RT_EMPTY;                           // sentinel under every traversal (sp starts at 1): a pop needs no emptiness test
 
     const uint64_t n_items = (uint64_t)lp.n_warp_tiles * (FOLD ? 1u : lp.n_frames) * 32ull;
-    const unsigned long long guide = (unsigned long long)gridDim.x * (RT_BLOCK_THREADS / 32) * RT_QUEUE_GUIDE;   // warps x K
+    const unsigned long long guide = (unsigned long long)gridDim.x * (RT_BLOCK_THREADS / 32) * lp.queue_guide;   // warps x K
     const size_t plane = (size_t)lp.width * lp.height;
     const float sw = (float)lp.width, sh = (float)lp.height, rppf = (float)lp.rpp;
     uint32_t n_rays = 0, n_samples = 0, n_nodes = 0, n_tri = 0, n_sph = 0, n_hits = 0;
@@ -109,7 +109,7 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
     unsigned long long ls[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, ls8 = 0;
 #endif
 
-    uint64_t pool_next = 0, pool_end = 0;          // warp-uniform: items granted to this warp
+    uint64_t pool_next = 0, pool_end = 0;          // warp-uniform: items granted to this warp (kept in registers: in shared memory C3 -4.6 %)
     bool exhausted = false;                        // warp-uniform: the global queue is empty
 
     // ---- per-lane state ---------------------------------------------------------------
