@@ -38,6 +38,8 @@ def functions(fn):
                            ("counters: one atomic", "counters")):
             if mark in l and l.strip().startswith("//") and fn == "rt_trace.cu" and n > 60:
                 out.append((n, name))
+        if fn == "rt_trace.cu" and l.startswith("trace_kernel("):
+            out.append((n, "trace_kernel: set-up, per-lane item state in shared memory"))
     return sorted(out)
 cache = {}
 def where(fn, line):
