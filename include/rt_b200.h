@@ -203,6 +203,25 @@ int rt_dispatch(rt_ctx* ctx);
  * rendered. Asynchronous. */
 int rt_render_frames(rt_ctx* ctx, int32_t first_frame, uint32_t n_frames);
 
+/* rt_render_frames without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc at this point (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it).
+ * Inputs are the context's uploaded scene, camera and params, the output its accumulation image, as
+ * for rt_render_frames (same image bit for bit, same counters); ONE launch of n_frames fused
+ * dispatches whose scratch — the work-queue head and one W*H float4 staging plane per dispatch —
+ * lives in a static device array of RT_STATIC_SCRATCH_BYTES that every GPU loading the library
+ * holds until the process exits.  The call performs no cudaMalloc / cudaFree / event or stream
+ * creation; everything else it touches was allocated by rt_create / rt_upload_*.
+ * Limits: n_frames * width * height * 16 <= RT_STATIC_SCRATCH_BYTES (1 dispatch at 1920x1080, 27 at
+ * 320x240), else RT_ERR_INVALID_ARGUMENT with the numbers in rt_last_error and nothing launched;
+ * RT_ERR_UNSUPPORTED with sample sharding (frame_world > 1) or RT_OPT_KERNEL = 1.  Not included in
+ * rt_get_counters' kernel_ms (no timing events).
+ * All calls on one device share the array, which keeps the previous call's contents (the call clears
+ * the queue head itself, in stream order): calls that overlap on the GPU — two contexts / streams of
+ * one device — race on it; serialise them. */
+#define RT_STATIC_SCRATCH_BYTES (32u << 20)
+int rt_render_frames_static(rt_ctx* ctx, int32_t first_frame, uint32_t n_frames);
+
 /* Wait for all work queued on the context (the implicit wait of queue.submit + present,
  * context.rs:291-292). */
 int rt_sync(rt_ctx* ctx);

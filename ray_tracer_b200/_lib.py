@@ -72,6 +72,7 @@ SYMBOLS = {
     "rt_set_params": (C.c_int, [_vp, _vp]),
     "rt_dispatch": (C.c_int, [_vp]),
     "rt_render_frames": (C.c_int, [_vp, _i32, _u32]),
+    "rt_render_frames_static": (C.c_int, [_vp, _i32, _u32]),
     "rt_sync": (C.c_int, [_vp]),
     "rt_resize": (C.c_int, [_vp, _u32, _u32]),
     "rt_clear": (C.c_int, [_vp]),

@@ -535,6 +535,56 @@ int rt_render_frames(rt_ctx* c, int32_t first_frame, uint32_t n_frames)
     return RT_OK;
 }
 
+// rt_render_frames for callers that may not allocate: one staged launch whose scratch is the static device array of
+// rt_trace.cu.  A separate path on purpose (launch() above is left as it is): its own copy of the launch parameters, no
+// event pair (cudaEventCreate allocates), no staging / stream / pool set-up.
+int rt_render_frames_static(rt_ctx* c, int32_t first_frame, uint32_t n_frames)
+{
+    int rc = check_ready(c);
+    if (rc != RT_OK) return rc;
+    if (n_frames == 0) return RT_OK;
+    if (n_frames > 0x3fffffffu || (int64_t)first_frame + n_frames > 0x7fffffffll) return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_render_frames_static: frame range overflows i32");
+    if (c->frame_world != 1) return fail(c, RT_ERR_UNSUPPORTED, "rt_render_frames_static: sample sharding (frame_world > 1) is not supported; tile sharding is");
+    if (c->opt_kernel != 0) return fail(c, RT_ERR_UNSUPPORTED, "rt_render_frames_static: only the persistent trace kernel (RT_OPT_KERNEL = 0)");
+    const uint64_t plane = (uint64_t)c->width * c->height * sizeof(float4), limit = rt::static_scratch_bytes();
+    if ((uint64_t)n_frames * plane > limit) {
+        char b[256];
+        snprintf(b, sizeof b, "rt_render_frames_static: %u dispatches of %ux%u need %llu bytes of staging, the static scratch holds %llu (at most %llu dispatches per call at this size)",
+                 n_frames, c->width, c->height, (unsigned long long)((uint64_t)n_frames * plane), (unsigned long long)limit, (unsigned long long)(limit / plane));
+        return fail(c, RT_ERR_INVALID_ARGUMENT, b);
+    }
+    const bool brute = c->opt_traversal == 1 || c->scene_too_deep;
+    if (brute && c->scene.iprims) return fail(c, RT_ERR_UNSUPPORTED, "rt_render_frames_static: the exhaustive scan needs flattened records (upload with RT_OPT_INSTANCING = 0)");
+    DeviceGuard g(c->device);
+    rt::SceneDev sd{};
+    const rt::SceneBuffers& s = c->scene;
+    sd.prims = s.prims; sd.iprims = s.iprims; sd.c0 = s.c0; sd.c1 = s.c1; sd.c2 = s.c2; sd.c3 = s.c3; sd.c4 = s.c4; sd.c5 = s.c5;
+    sd.tex = c->d_tex; sd.n_tex = (uint32_t)c->textures.size();
+    sd.m0 = s.m0; sd.m1 = s.m1; sd.m2 = s.m2; sd.nodes = s.nodes;
+    sd.n_prims = s.n_prims; sd.n_spheres = s.n_spheres; sd.root = s.root;
+    sd.max_abs = s.max_abs; sd.pad_scale = 1.52587890625e-05f;   // 2^-16
+    rt::LaunchParams lp{};
+    lp.width = c->width; lp.height = c->height;
+    lp.bounces = c->params.number_of_bounces; lp.rpp = c->params.rays_per_pixel; lp.toggle = c->params.skybox;
+    lp.first_frame = first_frame; lp.n_frames = n_frames; lp.blend0 = first_frame;
+    lp.tile_rank = c->tile_rank; lp.tile_world = c->tile_world; lp.frame_world = 1;
+    lp.tiles_x = (c->width + 7) / 8;
+    const uint32_t tiles = lp.tiles_x * ((c->height + 7) / 8);
+    lp.n_warp_tiles = 2u * (tiles > c->tile_rank ? (tiles - c->tile_rank + c->tile_world - 1) / c->tile_world : 0);
+    lp.seed_mode = (int32_t)c->opt_seed_mode;
+    lp.queue_guide = (uint32_t)(n_frames <= 16u ? 2ull * RT_QUEUE_GUIDE : RT_QUEUE_GUIDE);
+    lp.div_frames = rt::make_fastdiv(n_frames); lp.div_tiles_x = rt::make_fastdiv(lp.tiles_x); lp.div_width = rt::make_fastdiv(c->width);
+    lp.rpp_scale = (lp.rpp > 0 && (lp.rpp & (lp.rpp - 1)) == 0) ? 1.0f / (float)lp.rpp : 0.0f;
+    lp.sched_n_stay = (int32_t)(c->opt_sched & 0xff); if (lp.sched_n_stay < 1) lp.sched_n_stay = 1; lp.sched_l_stay = (int32_t)((c->opt_sched >> 8) & 0xff); lp.sched_s_min = (int32_t)((c->opt_sched >> 16) & 0xff);
+    cudaError_t e = rt::launch_trace_static(sd, to_dev(c->camera), lp, c->accum, c->opt_primary_ids != 0 ? c->primary_ids : nullptr, c->d_counters,
+                                            brute, c->opt_detail != 0, c->n_sms, c->device, c->stream);
+    if (e != cudaSuccess) return cuda_fail(c, e, "rt_render_frames_static");
+    c->launches++;
+    c->dispatches += n_frames;
+    { const int64_t last = (int64_t)lp.blend0 + (int64_t)n_frames - 1; c->mean_count = last >= 0 ? (uint32_t)(last + 1) : 1u; }
+    return RT_OK;
+}
+
 int rt_sync(rt_ctx* c)
 {
     if (!c) return RT_ERR_INVALID_ARGUMENT;

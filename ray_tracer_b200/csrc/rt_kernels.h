@@ -44,6 +44,17 @@ cudaError_t launch_trace(const SceneDev& sc, const CameraDev& cam, const LaunchP
                          uint32_t* primary_ids, unsigned long long* counters, unsigned long long* queue,
                          bool brute, bool detail, bool fold, int n_sms, cudaStream_t stream, bool with_blend = true);
 
+// The staged trace launch + blend with the scratch (queue head, staging planes) in a static device array of
+// RT_STATIC_SCRATCH_BYTES (rt_trace.cu): nothing is allocated.  `device` must be current.  cudaErrorInvalidValue when
+// lp.n_frames planes of W*H float4 exceed the array.
+#ifndef RT_STATIC_SCRATCH_BYTES
+#define RT_STATIC_SCRATCH_BYTES (32u << 20)      // == rt_b200.h
+#endif
+size_t static_scratch_bytes();
+cudaError_t launch_trace_static(const SceneDev& sc, const CameraDev& cam, const LaunchParams& lp, float4* accum,
+                                uint32_t* primary_ids, unsigned long long* counters, bool brute, bool detail,
+                                int n_sms, int device, cudaStream_t stream);
+
 // Device-resident scene: SoA primitive arrays + LBVH, built on the GPU from the AoS records.
 struct SceneBuffers {
     float4* prims = nullptr;

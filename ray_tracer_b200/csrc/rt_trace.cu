@@ -23,6 +23,10 @@
 #include "rt_device.cuh"
 #include "rt_kernels.h"
 #include "rt_shade.cuh"
+#include <mutex>
+
+// scratch of rt_render_frames_static (end of this file): queue head in the first 256 bytes, then the staging planes
+static __device__ __align__(256) unsigned char g_static_scratch[256 + RT_STATIC_SCRATCH_BYTES];
 
 namespace rt {
 
@@ -519,6 +523,72 @@ cudaError_t launch_blend(const LaunchParams& lp, const float4* staging, float4* 
     if (n_local == 0 || lp.n_frames == 0) return cudaSuccess;
     blend_kernel<<<(unsigned)((n_local + 255) / 256), 256, 0, stream>>>(lp, staging, accum);
     return cudaGetLastError();
+}
+
+// ---- rt_render_frames_static: the trace launch with its scratch in a static device array ---------------------------
+// For callers that may not allocate (rt_b200.h).  The scratch of a staged trace launch is the work-queue head and one
+// W*H float4 plane per fused dispatch; here both live in one file-scope array that every GPU loading this library holds
+// until the process exits: 256 bytes of header (queue head in the first 8) + RT_STATIC_SCRATCH_BYTES of planes.
+// In host code `g_static_scratch` is only a host-side stand-in for the symbol, not a device address: the address a
+// kernel can use comes from cudaGetSymbolAddress, asked once per device with that device current.
+// All calls share the array and it keeps the last call's contents: the queue head is cleared in stream order before
+// every launch (the planes need no clearing: the kernel writes every slot the blend reads), and two calls that overlap
+// on the GPU (different streams / contexts of one device) race on it.  (The array is defined at file scope, at the top.)
+
+namespace {
+const int kStaticMaxDevices = 64;
+std::mutex g_static_mu;
+void* g_static_ptr[kStaticMaxDevices];          // device address of g_static_scratch, per device ordinal
+
+// `device` must be the current device of the calling thread.
+cudaError_t static_scratch(int device, unsigned char** out)
+{
+    if (device < 0 || device >= kStaticMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lk(g_static_mu);
+    if (!g_static_ptr[device]) {
+        int cur = -1;
+        cudaError_t e = cudaGetDevice(&cur);
+        if (e != cudaSuccess) return e;
+        if (cur != device) return cudaErrorInvalidDevice;
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (e != cudaSuccess) return e;
+        if (!p || ((uintptr_t)p & 255u) != 0) return cudaErrorInvalidSymbol;
+        g_static_ptr[device] = p;
+    }
+    *out = (unsigned char*)g_static_ptr[device];
+    return cudaSuccess;
+}
+} // namespace
+
+size_t static_scratch_bytes() { return RT_STATIC_SCRATCH_BYTES; }
+
+// (pixel, dispatch) items, planes and queue head in the static array, then the blend: the same two kernels as
+// launch_trace(fold = false) on other scratch.  No allocation, no event, no synchronisation.
+cudaError_t launch_trace_static(const SceneDev& sc, const CameraDev& cam, const LaunchParams& lp, float4* accum,
+                                uint32_t* primary_ids, unsigned long long* counters, bool brute, bool detail,
+                                int n_sms, int device, cudaStream_t stream)
+{
+    if (lp.n_warp_tiles == 0 || lp.n_frames == 0) return cudaSuccess;
+    if ((uint64_t)lp.n_frames * lp.width * lp.height * sizeof(float4) > (uint64_t)RT_STATIC_SCRATCH_BYTES) return cudaErrorInvalidValue;
+    const bool inst = sc.iprims != nullptr;
+    if (inst && brute) return cudaErrorNotSupported;
+    unsigned char* base = nullptr;
+    cudaError_t e = static_scratch(device, &base);
+    if (e != cudaSuccess) return e;
+    unsigned long long* queue = (unsigned long long*)base;
+    float4* staging = (float4*)(base + 256);
+    if ((e = cudaMemsetAsync(queue, 0, sizeof(unsigned long long), stream)) != cudaSuccess) return e;
+    const bool tex = sc.c3 != nullptr && sc.n_tex != 0u;
+    const uint64_t n_items = (uint64_t)lp.n_warp_tiles * lp.n_frames * 32ull;
+    const uint64_t warps_needed = (n_items + RT_QUEUE_CHUNK - 1) / RT_QUEUE_CHUNK;
+    const bool pf = !brute && !inst && sc.n_prims <= RT_PF_MAX_PRIMS;
+    uint64_t blocks = (uint64_t)n_sms * trace_blocks_per_sm(brute, detail, tex, pf, false, inst);
+    const uint64_t cap = (warps_needed + RT_BLOCK_THREADS / 32 - 1) / (RT_BLOCK_THREADS / 32);
+    if (blocks > cap) blocks = cap;
+    trace_variant(brute, detail, tex, pf, false, inst)<<<dim3((unsigned)blocks), dim3(RT_BLOCK_THREADS), 0, stream>>>(sc, cam, lp, staging, accum, primary_ids, counters, queue);
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    return launch_blend(lp, staging, accum, stream);
 }
 
 } // namespace rt

@@ -115,6 +115,11 @@ class RayTracer:
     def render_frames(self, first_frame, n_frames):
         self._ck(self._L.rt_render_frames(self._h, int(first_frame), int(n_frames)))
 
+    def render_frames_static(self, first_frame, n_frames):
+        """rt_render_frames_static: one launch that allocates nothing (scratch in the library's static device array,
+        n_frames * W * H * 16 <= RT_STATIC_SCRATCH_BYTES).  No reference counterpart."""
+        self._ck(self._L.rt_render_frames_static(self._h, int(first_frame), int(n_frames)))
+
     def sync(self):
         self._ck(self._L.rt_sync(self._h))
 

@@ -57,6 +57,7 @@ extern "C" {
     pub fn rt_set_params(ctx: *mut RtCtx, params: *const Params) -> c_int;
     pub fn rt_dispatch(ctx: *mut RtCtx) -> c_int;
     pub fn rt_render_frames(ctx: *mut RtCtx, first_frame: i32, n_frames: u32) -> c_int;
+    pub fn rt_render_frames_static(ctx: *mut RtCtx, first_frame: i32, n_frames: u32) -> c_int;
     pub fn rt_sync(ctx: *mut RtCtx) -> c_int;
     pub fn rt_resize(ctx: *mut RtCtx, width: u32, height: u32) -> c_int;
     pub fn rt_clear(ctx: *mut RtCtx) -> c_int;
@@ -132,6 +133,8 @@ impl RayTracer {
     pub fn dispatch(&self) -> Result<()> { self.check(unsafe { rt_dispatch(self.ctx) }) }
     /// `n` redraws without input in between, fused on the device (frames = first, first+1, ...)
     pub fn render_frames(&self, first_frame: i32, n: u32) -> Result<()> { self.check(unsafe { rt_render_frames(self.ctx, first_frame, n) }) }
+    /// `render_frames` without any allocation: scratch in the library's static device array (RT_STATIC_SCRATCH_BYTES).
+    pub fn render_frames_static(&self, first_frame: i32, n: u32) -> Result<()> { self.check(unsafe { rt_render_frames_static(self.ctx, first_frame, n) }) }
     pub fn sync(&self) -> Result<()> { self.check(unsafe { rt_sync(self.ctx) }) }
     /// was `update_bind_group` after `Context::resize` (ray_tracer.rs:149, context.rs:126-142)
     pub fn resize(&mut self, width: u32, height: u32) -> Result<()> { self.check(unsafe { rt_resize(self.ctx, width, height) })?; self.width = width; self.height = height; Ok(()) }
