@@ -139,6 +139,8 @@ enum {
     RT_OPT_WAVE_SLOTS = 11,      /* path slots of the wavefront pool (128 B each; default 2^21) */
     RT_OPT_STAGING_MIB = 12,     /* budget of the staging planes (one W*H float4 plane per fused dispatch), MiB (default 4352: 128 dispatches per launch at 1080p, 32 at 4K); bounds the dispatches per launch together with RT_OPT_FRAMES_PER_LAUNCH; allocated at the first fused launch */
     RT_OPT_INSTANCING = 14,      /* Mesh records that alias one (first, triangles, offset) range (at least two records, 32 triangles, no texture handles) can share ONE object-space hierarchy and appear as proxies in a top-level hierarchy (two-level BVH) instead of being flattened; the triangle test then adds the record's pos per instance with the reference's own operations (wgsl:172-174), so results do not depend on it.  1: instance every eligible range (64x less scene memory on C5, rt_update_records of an instance = a top-level refit; measured 16 % slower than flattened records there); 0: flatten every record; 2 (default): instance only when flattening would exceed 8 M triangles.  Takes effect at the next rt_upload_scene; the exhaustive scan (RT_OPT_TRAVERSAL = 1) and the wavefront kernels (RT_OPT_KERNEL = 1) always flatten and must be selected before the upload of such a scene */
+    RT_OPT_NODE_FORMAT = 16,     /* hierarchy nodes of flat (non-instanced) scenes: 0 (default) = by size: 64-byte float nodes up to 262,144 primitives, packed 32-byte nodes (box centres on a 16-bit grid, half extents as bf16, one 256-bit load per node visit) above; 1 = float, 2 = packed; takes effect at the next rt_upload_scene; results do not depend on it */
+    RT_OPT_NODES_PACKED = 17,    /* read-only (rt_get_option): 1 when the uploaded scene's hierarchy holds packed nodes (see RT_OPT_NODE_FORMAT; instanced scenes and scenes whose bounds are not finite never do) */
     RT_OPT_PIPELINE = 15,        /* 1 (default): when one rt_render_frames call needs several launches (more dispatches than the staging budget holds), they alternate between two streams, half of the staging planes each, so that a launch's blocks fill the SMs the previous one's drain leaves idle (the blends keep dispatch order); 0: one launch after the other; results do not depend on it */
     RT_OPT_ITEM_MODE = 13        /* work items of the trace kernel: 1 = one (pixel, dispatch) pair, frags staged and folded in dispatch order by a blend kernel; 2 = one pixel with all fused dispatches, the progressive store (wgsl:59-66) applied by the owning lane, no staging memory (coarse items: slower on fused launches); 0 = auto (default): 2 for single-dispatch launches, else 1; results do not depend on it */
 };

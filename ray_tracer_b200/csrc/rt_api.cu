@@ -46,6 +46,7 @@ struct rt_ctx {
     cudaEvent_t ev_fork = nullptr, ev_blend[2] = {nullptr, nullptr};
     int n_sms = 148;
     int64_t opt_staging_bytes = 4352ll << 20;     // staging planes (RT_OPT_STAGING_MIB): 128 dispatches per launch at 1080p, 32 at 4K
+    int64_t opt_node_format = 0;                  // 0: by scene size, 1: float nodes, 2: packed nodes (RT_OPT_NODE_FORMAT)
     int64_t opt_pipeline = 1;                     // 1: the launches of one render call overlap on two streams (RT_OPT_PIPELINE)
     int64_t opt_instancing = 2;                   // Mesh records that alias one index range share one object-space hierarchy (two-level BVH): 0 never, 1 when eligible, 2 auto
     int64_t opt_item_mode = 0;                    // 0: auto, 1: (pixel, dispatch) items + staging + blend kernel, 2: pixel items, running mean applied in the trace kernel
@@ -185,6 +186,7 @@ int launch(rt_ctx* c, int32_t first_frame, uint32_t n_frames, bool want_ids, int
     sd.m0 = s.m0; sd.m1 = s.m1; sd.m2 = s.m2; sd.nodes = s.nodes;
     sd.n_prims = s.n_prims; sd.n_spheres = s.n_spheres; sd.root = s.root;
     sd.max_abs = s.max_abs; sd.pad_scale = 1.52587890625e-05f;   // 2^-16
+    sd.packed = s.packed ? 1 : 0; sd.grid_o = make_float3(s.grid_o[0], s.grid_o[1], s.grid_o[2]); sd.grid_c = make_float3(s.grid_c[0], s.grid_c[1], s.grid_c[2]);
     rt::LaunchParams lp{};
     lp.width = c->width; lp.height = c->height;
     lp.bounces = c->params.number_of_bounces; lp.rpp = c->params.rays_per_pixel; lp.toggle = c->params.skybox;
@@ -362,10 +364,10 @@ int rt_upload_scene(rt_ctx* c, const rt_sphere* spheres, uint32_t ns, const rt_v
     // Mesh records aliasing one (first, triangles, offset) range become instances of one object-space hierarchy, unless the
     // exhaustive scan or the wavefront kernels (which need flattened records) are selected at upload time
     const int instancing = (c->opt_traversal == 0 && c->opt_kernel == 0) ? (int)c->opt_instancing : 0;
-    cudaError_t e = rt::build_scene(c->scene, spheres, ns, vertices, nv, indices, ni, meshes, nm, leaf, (int)c->opt_builder, (int)c->opt_ploc_radius, instancing, c->stream);
+    cudaError_t e = rt::build_scene(c->scene, spheres, ns, vertices, nv, indices, ni, meshes, nm, leaf, (int)c->opt_builder, (int)c->opt_ploc_radius, instancing, (int)c->opt_node_format, c->stream);
     if (e != cudaSuccess) { c->has_scene = false; return cuda_fail(c, e, "scene build"); }
     if (c->scene.n_inst != 0 && c->scene.max_depth > RT_STACK - 2) {          // two levels too deep for the stack: flatten instead
-        e = rt::build_scene(c->scene, spheres, ns, vertices, nv, indices, ni, meshes, nm, leaf, (int)c->opt_builder, (int)c->opt_ploc_radius, 0, c->stream);
+        e = rt::build_scene(c->scene, spheres, ns, vertices, nv, indices, ni, meshes, nm, leaf, (int)c->opt_builder, (int)c->opt_ploc_radius, 0, (int)c->opt_node_format, c->stream);
         if (e != cudaSuccess) { c->has_scene = false; return cuda_fail(c, e, "scene build"); }
     }
     // A hierarchy deeper than the traversal stack (both builders; needs thousands of coincident primitives plus far
@@ -563,6 +565,7 @@ int rt_render_frames_static(rt_ctx* c, int32_t first_frame, uint32_t n_frames)
     sd.m0 = s.m0; sd.m1 = s.m1; sd.m2 = s.m2; sd.nodes = s.nodes;
     sd.n_prims = s.n_prims; sd.n_spheres = s.n_spheres; sd.root = s.root;
     sd.max_abs = s.max_abs; sd.pad_scale = 1.52587890625e-05f;   // 2^-16
+    sd.packed = s.packed ? 1 : 0; sd.grid_o = make_float3(s.grid_o[0], s.grid_o[1], s.grid_o[2]); sd.grid_c = make_float3(s.grid_c[0], s.grid_c[1], s.grid_c[2]);
     rt::LaunchParams lp{};
     lp.width = c->width; lp.height = c->height;
     lp.bounces = c->params.number_of_bounces; lp.rpp = c->params.rays_per_pixel; lp.toggle = c->params.skybox;
@@ -783,6 +786,7 @@ int rt_set_option(rt_ctx* c, int option, int64_t value)
         c->opt_traversal = value; return RT_OK;
     case RT_OPT_INSTANCING: if (value < 0 || value > 2) break; c->opt_instancing = value; return RT_OK;
     case RT_OPT_PIPELINE: if (value != 0 && value != 1) break; c->opt_pipeline = value; return RT_OK;
+    case RT_OPT_NODE_FORMAT: if (value < 0 || value > 2) break; c->opt_node_format = value; return RT_OK;
     case RT_OPT_SEED_MODE: if (value != 0 && value != 1) break; c->opt_seed_mode = value; return RT_OK;
     case RT_OPT_PRIMARY_IDS: c->opt_primary_ids = value != 0; return RT_OK;
     case RT_OPT_DETAIL_COUNTERS: c->opt_detail = value != 0; return RT_OK;
@@ -821,6 +825,8 @@ int rt_get_option(const rt_ctx* c, int option, int64_t* value)
     case RT_OPT_ITEM_MODE: *value = c->opt_item_mode; return RT_OK;
     case RT_OPT_INSTANCING: *value = c->opt_instancing; return RT_OK;
     case RT_OPT_PIPELINE: *value = c->opt_pipeline; return RT_OK;
+    case RT_OPT_NODE_FORMAT: *value = c->opt_node_format; return RT_OK;
+    case RT_OPT_NODES_PACKED: *value = (c->has_scene && c->scene.packed) ? 1 : 0; return RT_OK;
     default: return RT_ERR_INVALID_ARGUMENT;
     }
 }

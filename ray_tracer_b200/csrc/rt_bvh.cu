@@ -284,7 +284,7 @@ __global__ void ploc_nn(const int* __restrict__ st, int radius, const float4* __
 {
     __shared__ float4 slo[PLOC_THREADS + 2 * PLOC_MAX_RADIUS], shi[PLOC_THREADS + 2 * PLOC_MAX_RADIUS];
     const int m = st[0], force_pairs = st[2];
-    if (m <= 1 || (int)(blockIdx.x * PLOC_THREADS) >= m) return;      // block-uniform
+    if (m <= st[4] || (int)(blockIdx.x * PLOC_THREADS) >= m) return;  // block-uniform; st[4]: cluster count at which ploc_tail takes over (1 = never)
     const int base = blockIdx.x * PLOC_THREADS - radius;
     for (int t = threadIdx.x; t < PLOC_THREADS + 2 * radius; t += PLOC_THREADS) {
         int g = base + t;
@@ -314,7 +314,7 @@ __global__ void ploc_flags(const int* __restrict__ st, const int* __restrict__ n
 {
     const int m = st[0];
     int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (m <= 1 || i >= m) return;
+    if (m <= st[4] || i >= m) return;
     int j = nn[i];
     bool mutual = j >= 0 && nn[j] == i;
     unsigned long long keep = (!mutual || i < j) ? 1ull : 0ull, merge = (mutual && i < j) ? 1ull : 0ull;
@@ -330,7 +330,7 @@ __global__ void ploc_scatter(const int* __restrict__ st, const int* __restrict__
 {
     const int m = st[0], node_base = st[1];
     int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (m <= 1 || i >= m) return;
+    if (m <= st[4] || i >= m) return;
     const int j = nn[i];
     const bool mutual = j >= 0 && nn[j] == i;
     const unsigned long long p = pos[i];
@@ -361,11 +361,96 @@ __global__ void ploc_scatter(const int* __restrict__ st, const int* __restrict__
 // pair (only possible with tied areas) forces neighbour pairs next time
 __global__ void ploc_advance(int* st, const unsigned int* __restrict__ totals)
 {
-    if (st[0] <= 1) return;
+    if (st[0] <= st[4]) return;
     st[1] += (int)totals[1];
     st[2] = totals[1] == 0u;
     st[0] = (int)totals[0];
     st[3] += 1;
+}
+
+// The last rounds in ONE block: once the cluster list fits PLOC_TAIL threads it lives in shared memory and the rounds
+// (same neighbour search, same mutual-pair rule, same numbering of survivors and new nodes as ploc_nn / ploc_flags /
+// scan / ploc_scatter / ploc_advance, so the tree is the same) run back to back with block barriers between them instead
+// of five launches each: the teapot's ~40 rounds are ~6 launched rounds + this kernel.
+#define PLOC_TAIL 1024
+__global__ void __launch_bounds__(PLOC_TAIL) ploc_tail(int* st, int radius, const int* __restrict__ cid, const float4* __restrict__ clo, const float4* __restrict__ chi,
+                                                       int2* __restrict__ children, float4* __restrict__ imin, float4* __restrict__ imax,
+                                                       int* __restrict__ par_inner, int* __restrict__ par_leaf)
+{
+    __shared__ float4 slo[PLOC_TAIL], shi[PLOC_TAIL];
+    __shared__ int scid[PLOC_TAIL], snn[PLOC_TAIL];
+    __shared__ unsigned int swarp[PLOC_TAIL / 32];
+    __shared__ int s_m, s_base, s_force, s_rounds;
+    const int i = threadIdx.x, lane = i & 31, warp = i >> 5;
+    if (i == 0) { s_m = st[0]; s_base = st[1]; s_force = st[2]; s_rounds = 0; }
+    __syncthreads();
+    if (s_m > PLOC_TAIL) return;
+    if (i < s_m) { scid[i] = cid[i]; slo[i] = clo[i]; shi[i] = chi[i]; }
+    __syncthreads();
+    while (s_m > 1) {
+        const int m = s_m, node_base = s_base, force_pairs = s_force;
+        // nearest neighbour (ploc_nn)
+        if (i < m) {
+            int bj;
+            if (force_pairs) bj = ((i ^ 1) < m) ? (i ^ 1) : -1;
+            else {
+                int partner = i ^ 1;
+                if (partner >= m) partner = i - 1;
+                const float4 alo = slo[i], ahi = shi[i];
+                float best = INFINITY; bj = partner; int brank = 0x7fffffff;
+                const int j0 = max(0, i - radius), j1 = min(m - 1, i + radius);
+                for (int j = j0; j <= j1; j++) {
+                    if (j == i) continue;
+                    const float a = union_area(alo, ahi, slo[j], shi[j]);
+                    const int rank = (j == (i ^ 1)) ? 0 : 2 * abs(j - i) + (j > i ? 1 : 0);
+                    if (a < best || (a == best && rank < brank)) { best = a; bj = j; brank = rank; }
+                }
+            }
+            snn[i] = bj;
+        }
+        __syncthreads();
+        // keep / merge flags and their exclusive prefix sums (ploc_flags + scan): keep in the high half, merge in the low half
+        int j = -1; bool mutual = false;
+        unsigned int flag = 0u;
+        if (i < m) {
+            j = snn[i];
+            mutual = j >= 0 && snn[j] == i;
+            flag = ((!mutual || i < j) ? 0x10000u : 0u) | ((mutual && i < j) ? 1u : 0u);
+        }
+        unsigned int incl = flag;
+        for (int o = 1; o < 32; o <<= 1) { const unsigned int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+        if (lane == 31) swarp[warp] = incl;
+        // what this thread will write, read before anything is overwritten
+        int a = 0, b = 0; float4 alo = make_float4(0.f, 0.f, 0.f, 0.f), ahi = alo, blo = alo, bhi = alo;
+        if (i < m) { a = scid[i]; alo = slo[i]; ahi = shi[i]; if (mutual && i < j) { b = scid[j]; blo = slo[j]; bhi = shi[j]; } }
+        __syncthreads();
+        if (warp == 0) {
+            unsigned int w = swarp[lane], winc = w;
+            for (int o = 1; o < 32; o <<= 1) { const unsigned int t = __shfl_up_sync(0xffffffffu, winc, o); if (lane >= o) winc += t; }
+            swarp[lane] = winc - w;                       // exclusive offset of every warp
+            if (lane == 31) { s_m = (int)(winc >> 16); s_base = node_base + (int)(winc & 0xffffu); s_force = (winc & 0xffffu) == 0u; s_rounds++; }
+        }
+        __syncthreads();
+        if (i < m) {
+            const unsigned int excl = swarp[warp] + incl - flag;
+            const unsigned int out = excl >> 16, mrg = excl & 0xffffu;
+            if (!mutual) {
+                scid[out] = a; slo[out] = alo; shi[out] = ahi;
+            } else if (i < j) {                            // ploc_scatter
+                const int node = node_base + (int)mrg;
+                const int cnt = __float_as_int(alo.w) + __float_as_int(blo.w);
+                const float4 lo = make_float4(fminf(alo.x, blo.x), fminf(alo.y, blo.y), fminf(alo.z, blo.z), __int_as_float(cnt));
+                const float4 hi = make_float4(fmaxf(ahi.x, bhi.x), fmaxf(ahi.y, bhi.y), fmaxf(ahi.z, bhi.z), 0.f);
+                children[node] = make_int2(a, b);
+                imin[node] = lo; imax[node] = hi;
+                if (a >= 0) par_inner[a] = node << 1; else par_leaf[~a] = node << 1;
+                if (b >= 0) par_inner[b] = (node << 1) | 1; else par_leaf[~b] = (node << 1) | 1;
+                scid[out] = node; slo[out] = lo; shi[out] = hi;
+            }
+        }
+        __syncthreads();
+    }
+    if (i == 0) { st[0] = s_m; st[1] = s_base; st[2] = s_force; st[3] += s_rounds; }
 }
 
 // Final primitive layout of a PLOC tree: a node's first slot = number of primitives to its
@@ -456,6 +541,59 @@ __global__ void emit_nodes(int n_inner, const int2* children, const int2* ranges
     nodes[4 * (size_t)i + 3] = make_float4(__int_as_float(el), __int_as_float(er), 0.f, 0.f);
 }
 
+// ---- packed nodes (node_test_packed, rt_device.cuh) -------------------------------------------------------------------
+// grid = bounds[6..11] as float bits: origin xyz, cell xyz (cell = extent / 65535, at least 1e-30)
+__global__ void make_grid(int* bounds)
+{
+    const int k = threadIdx.x;
+    if (k >= 3) return;
+    const float lo = fdec(bounds[k]), hi = fdec(bounds[k + 3]);
+    bounds[6 + k] = __float_as_int(lo);
+    bounds[9 + k] = __float_as_int(fmaxf((hi - lo) * (1.0f / 65535.0f), 1e-30f));
+}
+// One (child, axis) word: the box centre on the grid in the low half, the half extent ABOUT THAT GRID POINT, enlarged by
+// 1.25 cells (the traversal's reconstruction error, see node_test_packed) and rounded up to bf16, in the high half.
+// A half extent that is not finite becomes +inf: the axis then never culls.
+__device__ __forceinline__ uint32_t pack_axis(float lo, float hi, float o, float cell)
+{
+    const float g = (0.5f * lo + 0.5f * hi - o) / cell;
+    const float q = fminf(fmaxf(rintf(g), 0.0f), 65535.0f);        // a NaN centre lands on 0; its half extent below is NaN -> inf
+    const float cq = __fmaf_rn(q, cell, o);
+    float h = fmaxf(hi - cq, cq - lo) + 1.25f * cell;
+    h = __fmaf_ru(h, 4.76837158e-07f, h);                          // 2^-21: the roundings of cq and of the two differences
+    uint32_t hb = __float_as_uint(h);
+    if (!(h <= 3.0e38f) || !(hi - cq == hi - cq) || !(cq - lo == cq - lo)) hb = 0x7f800000u;
+    else hb = (hb + 0xffffu) & 0xffff0000u;
+    return hb | (uint32_t)q;
+}
+__global__ void emit_nodes_packed(int n_inner, const int2* children, const int2* ranges, const uint32_t* new_slot, const float4* lmin, const float4* lmax,
+                                  const float4* imin, const float4* imax, int leaf_size, const int* bounds, float4* nodes)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_inner) return;
+    const float3 o = f3(__int_as_float(bounds[6]), __int_as_float(bounds[7]), __int_as_float(bounds[8]));
+    const float3 c = f3(__int_as_float(bounds[9]), __int_as_float(bounds[10]), __int_as_float(bounds[11]));
+    int2 ch = children[i];
+    float4 alo = ch.x >= 0 ? imin[ch.x] : lmin[~ch.x], ahi = ch.x >= 0 ? imax[ch.x] : lmax[~ch.x];
+    float4 blo = ch.y >= 0 ? imin[ch.y] : lmin[~ch.y], bhi = ch.y >= 0 ? imax[ch.y] : lmax[~ch.y];
+    int el = encode_child(ch.x, ranges, new_slot, leaf_size), er = encode_child(ch.y, ranges, new_slot, leaf_size);
+    // word order of node_test_packed(): (L.x, L.y | L.z, R.z) (R.x, R.y | left, right)
+    nodes[2 * (size_t)i + 0] = make_float4(__uint_as_float(pack_axis(alo.x, ahi.x, o.x, c.x)), __uint_as_float(pack_axis(alo.y, ahi.y, o.y, c.y)),
+                                           __uint_as_float(pack_axis(alo.z, ahi.z, o.z, c.z)), __uint_as_float(pack_axis(blo.z, bhi.z, o.z, c.z)));
+    nodes[2 * (size_t)i + 1] = make_float4(__uint_as_float(pack_axis(blo.x, bhi.x, o.x, c.x)), __uint_as_float(pack_axis(blo.y, bhi.y, o.y, c.y)),
+                                           __int_as_float(el), __int_as_float(er));
+}
+__global__ void emit_single_packed(const float4* lmin, const float4* lmax, const int* bounds, float4* nodes)
+{
+    const float3 o = f3(__int_as_float(bounds[6]), __int_as_float(bounds[7]), __int_as_float(bounds[8]));
+    const float3 c = f3(__int_as_float(bounds[9]), __int_as_float(bounds[10]), __int_as_float(bounds[11]));
+    float4 lo = lmin[0], hi = lmax[0];
+    const uint32_t never = 0xff800000u;                            // right child: half extent -inf on every axis (never hit)
+    nodes[0] = make_float4(__uint_as_float(pack_axis(lo.x, hi.x, o.x, c.x)), __uint_as_float(pack_axis(lo.y, hi.y, o.y, c.y)),
+                           __uint_as_float(pack_axis(lo.z, hi.z, o.z, c.z)), __uint_as_float(never));
+    nodes[1] = make_float4(__uint_as_float(never), __uint_as_float(never), __int_as_float(~0), __int_as_float(~0));
+}
+
 __global__ void emit_single(const float4* lmin, const float4* lmax, float4* nodes)
 {
     float4 lo = lmin[0], hi = lmax[0];
@@ -496,6 +634,7 @@ void SceneBuffers::release()
     }
     n_prims = n_spheres = n_tris = n_mats = n_nodes = max_depth = 0; root = -1; max_abs = 0.f; has_tex = false;
     n_inst = n_iprims = n_cold = n_top_nodes = 0;
+    packed = false;
 }
 
 #define RT_TRY(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { err = e_; goto done; } } while (0)
@@ -508,9 +647,20 @@ struct InstPlan {
     uint32_t blas_nodes = 0, blas_tris = 0;         // totals appended behind the top level
 };
 
+// grid of the packed nodes out of the copied-back bounds block (make_grid); false when it is not finite
+static bool read_grid(const int* hb, float* go, float* gc)
+{
+    bool ok = true;
+    for (int k = 0; k < 3; k++) {
+        memcpy(&go[k], &hb[6 + k], 4); memcpy(&gc[k], &hb[9 + k], 4);
+        ok = ok && go[k] == go[k] && fabsf(go[k]) <= 3.0e38f && gc[k] == gc[k] && gc[k] <= 3.0e38f;
+    }
+    return ok;
+}
+
 static cudaError_t build_scene_impl(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns, const rt_vertex* vertices,
                         uint32_t nv, const uint32_t* indices, uint32_t ni, const rt_mesh* meshes, uint32_t nm,
-                        uint32_t leaf_size, int builder, int ploc_radius, const InstPlan* plan, cudaStream_t stream)
+                        uint32_t leaf_size, int builder, int ploc_radius, const InstPlan* plan, int want_packed /*-1: by size*/, cudaStream_t stream)
 {
     out.release();
     out.stream = stream;
@@ -526,6 +676,7 @@ static cudaError_t build_scene_impl(SceneBuffers& out, const rt_sphere* spheres,
     const uint32_t n_inst = plan ? (uint32_t)plan->inst_mesh.size() : 0u;
     const uint32_t nt = flat_start[nm], n = ns + nt + n_inst, nmat = ns + nm;
     const uint32_t n_cold = n + (plan ? plan->blas_tris : 0u);
+    bool packed = want_packed < 0 ? n > RT_PF_MAX_PRIMS : want_packed != 0;   // by size: small scenes keep float nodes (rt_trace.cu: the prefetching kernel variants)
     uint32_t* d_flat_start = nullptr; uint32_t* d_inst_mesh = nullptr; int* d_range_of_mesh = nullptr; float4* d_range_info = nullptr;
     const int T = 256;
     if (ploc_radius < 1) ploc_radius = 1;
@@ -540,7 +691,7 @@ static cudaError_t build_scene_impl(SceneBuffers& out, const rt_sphere* spheres,
     unsigned long long *pflags = nullptr, *ppos = nullptr; unsigned int* d_tot = nullptr; int* d_state = nullptr;
     void* cub_tmp = nullptr; size_t cub_bytes = 0;
     void* scan_tmp = nullptr; size_t scan_bytes = 0;
-    int hb[6]; int h_init[6] = {0x7fffffff, 0x7fffffff, 0x7fffffff, (int)0x80000000, (int)0x80000000, (int)0x80000000};
+    int hb[12]; int h_init[6] = {0x7fffffff, 0x7fffffff, 0x7fffffff, (int)0x80000000, (int)0x80000000, (int)0x80000000};
     int h_depth = 0;
 
     RT_TRY(dalloc(&d_sph, ns)); RT_TRY(dalloc(&d_vtx, nv)); RT_TRY(dalloc(&d_idx, ni)); RT_TRY(dalloc(&d_mesh, nm));
@@ -572,13 +723,14 @@ static cudaError_t build_scene_impl(SceneBuffers& out, const rt_sphere* spheres,
 
         RT_TRY(dalloc(&hot, 4 * (size_t)n)); RT_TRY(dalloc(&bmin, n)); RT_TRY(dalloc(&bmax, n));
         RT_TRY(dalloc(&lmin, n)); RT_TRY(dalloc(&lmax, n)); RT_TRY(dalloc(&imin, n)); RT_TRY(dalloc(&imax, n));
-        RT_TRY(dalloc(&d_bounds, 6)); RT_TRY(dalloc(&keys, n)); RT_TRY(dalloc(&keys2, n)); RT_TRY(dalloc(&ids, n)); RT_TRY(dalloc(&ids2, n));
+        RT_TRY(dalloc(&d_bounds, 12)); RT_TRY(dalloc(&keys, n)); RT_TRY(dalloc(&keys2, n)); RT_TRY(dalloc(&ids, n)); RT_TRY(dalloc(&ids2, n));
         RT_TRY(dalloc(&children, n)); RT_TRY(dalloc(&ranges, n)); RT_TRY(dalloc(&pin, n)); RT_TRY(dalloc(&plf, n)); RT_TRY(dalloc(&flags, n));
         RT_TRY(dalloc(&d_depth, 1)); RT_TRY(dalloc(&new_slot, n));
         RT_TRY(cudaMemcpyAsync(d_bounds, h_init, sizeof(h_init), cudaMemcpyHostToDevice, stream));
 
         const int nb = (n + T - 1) / T;
         setup_prims<<<nb, T, 0, stream>>>(rs, hot, out.c0, out.c1, out.c2, out.c3, out.c4, out.c5, bmin, bmax, d_bounds);
+        make_grid<<<1, 32, 0, stream>>>(d_bounds);
         morton_keys<<<nb, T, 0, stream>>>(n, bmin, bmax, d_bounds, keys, ids);
         RT_TRY(cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, keys, keys2, ids, ids2, (int)n, 0, 63, stream));
         RT_TRY(pool_alloc(&cub_tmp, cub_bytes, stream));
@@ -586,7 +738,8 @@ static cudaError_t build_scene_impl(SceneBuffers& out, const rt_sphere* spheres,
         gather_boxes<<<nb, T, 0, stream>>>(n, ids2, bmin, bmax, lmin, lmax);
         if (n == 1) {
             RT_TRY(dalloc(&out.nodes, 4 * (size_t)(1 + (plan ? plan->blas_nodes : 0u))));
-            emit_single<<<1, 1, 0, stream>>>(lmin, lmax, out.nodes);
+            if (packed) emit_single_packed<<<1, 1, 0, stream>>>(lmin, lmax, d_bounds, out.nodes);
+            else emit_single<<<1, 1, 0, stream>>>(lmin, lmax, out.nodes);
             identity_slots<<<1, T, 0, stream>>>(n, new_slot);
             out.n_nodes = 1; out.root = 0; h_depth = 1;
         } else {
@@ -600,10 +753,12 @@ static cudaError_t build_scene_impl(SceneBuffers& out, const rt_sphere* spheres,
                 RT_TRY(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, pflags, ppos, (int)n, stream));
                 RT_TRY(pool_alloc(&scan_tmp, scan_bytes, stream));
                 ploc_init<<<nb, T, 0, stream>>>((int)n, lmin, lmax, cidA, cloA, chiA);
-                RT_TRY(dalloc(&d_state, 4));
-                int h_state[4] = {(int)n, 0, 0, 0};              // clusters left, nodes created, force flag, rounds done
+                RT_TRY(dalloc(&d_state, 5));
+                const int tail = ploc_radius <= PLOC_MAX_RADIUS ? PLOC_TAIL : 1;
+                int h_state[5] = {(int)n, 0, 0, 0, tail};        // clusters left, nodes created, force flag, rounds done, cluster count at which ploc_tail takes over
                 RT_TRY(cudaMemcpyAsync(d_state, h_state, sizeof h_state, cudaMemcpyHostToDevice, stream));
-                for (int checks = 0; h_state[0] > 1; checks++) {
+                int* const cid0[2] = {cidA, cidB}; float4* const clo0[2] = {cloA, cloB}; float4* const chi0[2] = {chiA, chiB};
+                for (int checks = 0; h_state[0] > tail; checks++) {
                     if (checks > 4096) { RT_TRY(cudaErrorUnknown); }   // cannot happen: every round merges at least one pair
                     const int m_ub = h_state[0];                 // the cluster count only shrinks: grids and the scan are sized for the last known one
                     const int mb = (m_ub + PLOC_THREADS - 1) / PLOC_THREADS;
@@ -618,6 +773,10 @@ static cudaError_t build_scene_impl(SceneBuffers& out, const rt_sphere* spheres,
                     }
                     RT_TRY(cudaMemcpyAsync(h_state, d_state, sizeof h_state, cudaMemcpyDeviceToHost, stream));
                     RT_TRY(cudaStreamSynchronize(stream));
+                }
+                if (tail > 1) {                                  // rounds launched after the list fell to `tail` returned at once: the list is where round h_state[3] left it
+                    const int cur = h_state[3] & 1;
+                    ploc_tail<<<1, PLOC_TAIL, 0, stream>>>(d_state, ploc_radius, cid0[cur], clo0[cur], chi0[cur], children, imin, imax, pin, plf);
                 }
                 root = (int)n - 2;                               // the last node created
                 RT_TRY(cudaMemsetAsync(d_depth, 0, sizeof(int), stream));
@@ -635,13 +794,22 @@ static cudaError_t build_scene_impl(SceneBuffers& out, const rt_sphere* spheres,
                 identity_slots<<<nb, T, 0, stream>>>(n, new_slot);
                 RT_TRY(cudaMemcpyAsync(&h_depth, d_depth, sizeof(int), cudaMemcpyDeviceToHost, stream));
             }
-            emit_nodes<<<nb, T, 0, stream>>>((int)n - 1, children, ranges, new_slot, lmin, lmax, imin, imax, (int)leaf_size, out.nodes);
+            if (packed) emit_nodes_packed<<<nb, T, 0, stream>>>((int)n - 1, children, ranges, new_slot, lmin, lmax, imin, imax, (int)leaf_size, d_bounds, out.nodes);
+            else emit_nodes<<<nb, T, 0, stream>>>((int)n - 1, children, ranges, new_slot, lmin, lmax, imin, imax, (int)leaf_size, out.nodes);
             out.n_nodes = n - 1; out.root = root; out.builder = use_ploc ? 0 : 1;
         }
         gather_slots<<<(4 * n + T - 1) / T, T, 0, stream>>>(n, ids2, new_slot, hot, out.prims);
         RT_TRY(cudaMemcpyAsync(hb, d_bounds, sizeof(hb), cudaMemcpyDeviceToHost, stream));
         RT_TRY(cudaStreamSynchronize(stream));
         RT_TRY(cudaGetLastError());
+        if (packed && !read_grid(hb, out.grid_o, out.grid_c)) {      // bounds that are not finite have no grid: emit float nodes instead
+            packed = false;
+            if (n == 1) emit_single<<<1, 1, 0, stream>>>(lmin, lmax, out.nodes);
+            else emit_nodes<<<nb, T, 0, stream>>>((int)n - 1, children, ranges, new_slot, lmin, lmax, imin, imax, (int)leaf_size, out.nodes);
+            RT_TRY(cudaStreamSynchronize(stream));
+            RT_TRY(cudaGetLastError());
+        }
+        out.packed = packed;
         out.max_depth = (uint32_t)h_depth;
         float m = 0.f;
         for (int k = 0; k < 6; k++) {
@@ -716,7 +884,7 @@ __global__ void import_tris(uint32_t n_tris, const float4* __restrict__ blas_pri
 #define RT_INST_AUTO_TRIS 8000000ull               // ~1.4 GB of flattened records + nodes
 cudaError_t build_scene(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns, const rt_vertex* vertices,
                         uint32_t nv, const uint32_t* indices, uint32_t ni, const rt_mesh* meshes, uint32_t nm,
-                        uint32_t leaf_size, int builder, int ploc_radius, int instancing, cudaStream_t stream)
+                        uint32_t leaf_size, int builder, int ploc_radius, int instancing, int node_format, cudaStream_t stream)
 {
     struct Range { uint32_t first, triangles, offset, members; };
     std::vector<Range> ranges;
@@ -748,7 +916,7 @@ cudaError_t build_scene(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns
             for (uint32_t m = 0; m < nm; m++)
                 if (key_of[m] >= 0 && remap[key_of[m]] >= 0) { plan.range_of_mesh[m] = remap[key_of[m]]; plan.inst_mesh.push_back(m); }
     }
-    if (ranges.empty()) return build_scene_impl(out, spheres, ns, vertices, nv, indices, ni, meshes, nm, leaf_size, builder, ploc_radius, nullptr, stream);
+    if (ranges.empty()) return build_scene_impl(out, spheres, ns, vertices, nv, indices, ni, meshes, nm, leaf_size, builder, ploc_radius, nullptr, RT_PACKED_NODES ? (node_format == 0 ? -1 : node_format == 2) : 0, stream);
 
     // 1. one object-space hierarchy per range (a sub-scene of one Mesh record with pos = 0: the tested builder as it is)
     cudaError_t err = cudaSuccess;
@@ -761,7 +929,7 @@ cudaError_t build_scene(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns
         rt_mesh sub; memset(&sub, 0, sizeof sub);
         sub.first = ranges[g].first; sub.triangles = ranges[g].triangles; sub.offset = ranges[g].offset;
         blas[g].pool = out.pool;
-        err = build_scene_impl(blas[g], nullptr, 0, vertices, nv, indices, ni, &sub, 1, leaf_size, builder, ploc_radius, nullptr, stream);
+        err = build_scene_impl(blas[g], nullptr, 0, vertices, nv, indices, ni, &sub, 1, leaf_size, builder, ploc_radius, nullptr, 0, stream);
         if (err != cudaSuccess) break;
         const SceneBuffers& b = blas[g];
         plan.range_info.push_back(make_float4(b.bounds_lo[0], b.bounds_lo[1], b.bounds_lo[2], 0.f));
@@ -774,7 +942,7 @@ cudaError_t build_scene(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns
         if (b.max_depth > depth_max) depth_max = b.max_depth;
     }
     // 2. the top level over spheres, flattened triangles and one proxy per instance
-    if (err == cudaSuccess) err = build_scene_impl(out, spheres, ns, vertices, nv, indices, ni, meshes, nm, leaf_size, builder, ploc_radius, &plan, stream);
+    if (err == cudaSuccess) err = build_scene_impl(out, spheres, ns, vertices, nv, indices, ni, meshes, nm, leaf_size, builder, ploc_radius, &plan, 0, stream);
     // 3. the ranges' nodes / raw triangles / normals behind it
     if (err == cudaSuccess) err = cudaMallocFromPoolAsyncOrDefault((void**)&out.iprims, 4 * (size_t)(plan.blas_tris ? plan.blas_tris : 1) * sizeof(float4), out.pool, stream);
     if (err == cudaSuccess) {
@@ -806,7 +974,7 @@ cudaError_t refit_scene(SceneBuffers& sc, const rt_sphere* spheres, const rt_mes
     const int T = 256;
     cudaError_t err = cudaSuccess;
     if (n == 0) return cudaSuccess;                    // nothing is ever hit: no record is read
-    int hb[6]; int h_init[6] = {0x7fffffff, 0x7fffffff, 0x7fffffff, (int)0x80000000, (int)0x80000000, (int)0x80000000};
+    int hb[12]; int h_init[6] = {0x7fffffff, 0x7fffffff, 0x7fffffff, (int)0x80000000, (int)0x80000000, (int)0x80000000};
     if (ns) RT_TRY(cudaMemcpyAsync(k.sph, spheres, ns * sizeof(rt_sphere), cudaMemcpyHostToDevice, stream));
     if (nm) RT_TRY(cudaMemcpyAsync(k.mesh, meshes, nm * sizeof(rt_mesh), cudaMemcpyHostToDevice, stream));
     {
@@ -816,18 +984,28 @@ cudaError_t refit_scene(SceneBuffers& sc, const rt_sphere* spheres, const rt_mes
         const int nb = (n + T - 1) / T;
         RT_TRY(cudaMemcpyAsync(k.bounds, h_init, sizeof(h_init), cudaMemcpyHostToDevice, stream));
         setup_prims<<<nb, T, 0, stream>>>(rs, k.hot, sc.c0, sc.c1, sc.c2, sc.c3, sc.c4, sc.c5, k.bmin, k.bmax, k.bounds);
+        make_grid<<<1, 32, 0, stream>>>(k.bounds);
         gather_boxes<<<nb, T, 0, stream>>>(n, k.ids2, k.bmin, k.bmax, k.lmin, k.lmax);
         if (n == 1) {
-            emit_single<<<1, 1, 0, stream>>>(k.lmin, k.lmax, sc.nodes);
+            if (sc.packed) emit_single_packed<<<1, 1, 0, stream>>>(k.lmin, k.lmax, k.bounds, sc.nodes);
+            else emit_single<<<1, 1, 0, stream>>>(k.lmin, k.lmax, sc.nodes);
         } else {
             RT_TRY(cudaMemsetAsync(k.flags, 0, n * sizeof(int), stream));
             refit_boxes<<<nb, T, 0, stream>>>((int)n, sc.root, k.parent_shift, k.children, k.pin, k.plf, k.lmin, k.lmax, k.imin, k.imax, k.flags);
-            emit_nodes<<<nb, T, 0, stream>>>((int)n - 1, k.children, k.ranges, k.new_slot, k.lmin, k.lmax, k.imin, k.imax, (int)k.leaf_size, sc.nodes);
+            if (sc.packed) emit_nodes_packed<<<nb, T, 0, stream>>>((int)n - 1, k.children, k.ranges, k.new_slot, k.lmin, k.lmax, k.imin, k.imax, (int)k.leaf_size, k.bounds, sc.nodes);
+            else emit_nodes<<<nb, T, 0, stream>>>((int)n - 1, k.children, k.ranges, k.new_slot, k.lmin, k.lmax, k.imin, k.imax, (int)k.leaf_size, sc.nodes);
         }
         gather_slots<<<(4 * n + T - 1) / T, T, 0, stream>>>(n, k.ids2, k.new_slot, k.hot, sc.prims);
         RT_TRY(cudaMemcpyAsync(hb, k.bounds, sizeof(hb), cudaMemcpyDeviceToHost, stream));
         RT_TRY(cudaStreamSynchronize(stream));
         RT_TRY(cudaGetLastError());
+        if (sc.packed && !read_grid(hb, sc.grid_o, sc.grid_c)) {     // the moved records' bounds are not finite: float nodes from now on (the buffer is sized for them)
+            sc.packed = false;
+            if (n == 1) emit_single<<<1, 1, 0, stream>>>(k.lmin, k.lmax, sc.nodes);
+            else emit_nodes<<<nb, T, 0, stream>>>((int)n - 1, k.children, k.ranges, k.new_slot, k.lmin, k.lmax, k.imin, k.imax, (int)k.leaf_size, sc.nodes);
+            RT_TRY(cudaStreamSynchronize(stream));
+            RT_TRY(cudaGetLastError());
+        }
         float m = 0.f;
         for (int q = 0; q < 6; q++) {
             int e = hb[q]; int b = e >= 0 ? e : e ^ 0x7fffffff; float f; memcpy(&f, &b, 4);

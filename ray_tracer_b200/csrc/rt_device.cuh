@@ -53,6 +53,9 @@ struct SceneDev {
     int32_t root;          // root node index, or -1 when the scene is empty
     float max_abs;         // largest |coordinate| of the scene bounds
     float pad_scale;       // box padding = pad_scale * max(max_abs, |ray origin|)
+    // packed nodes (flat scenes; 32 B per node, see node_test_packed): the 16-bit grid the box centres are stored on
+    int32_t packed;        // 1: `nodes` holds packed nodes (2 float4 each); 0: centre / half-extent floats (4 float4 each)
+    float3 grid_o, grid_c; // grid origin and cell size per axis
 };
 
 struct CameraDev {         // the fields of CameraUniform the shader reads (wgsl:69-80)
@@ -167,6 +170,64 @@ __device__ __forceinline__ void node_test(const float4* np, const RaySlab& s, fl
     const f2_t Q0 = f2_fma(a3, s.ainv_xy, s.pi_xy);      // (L.b.x, L.b.y)
     const f2_t Q1 = f2_fma(b0, ainv_zz, pi_zz);          // (L.b.z, R.b.z)
     const f2_t Q2 = f2_fma(b1, s.ainv_xy, s.pi_xy);      // (R.b.x, R.b.y)
+    const f2_t N0 = f2_sub(P0, Q0), F0 = f2_add(P0, Q0), N1 = f2_sub(P1, Q1), F1 = f2_add(P1, Q1), N2 = f2_sub(P2, Q2), F2 = f2_add(P2, Q2);
+    ltn = fmaxf(fmaxf(f2_lo(N0), f2_hi(N0)), fmaxf(f2_lo(N1), 0.0f));
+    ltf = fminf(fminf(f2_lo(F0), f2_hi(F0)), fminf(f2_lo(F1), cull));
+    rtn = fmaxf(fmaxf(f2_lo(N2), f2_hi(N2)), fmaxf(f2_hi(N1), 0.0f));
+    rtf = fminf(fminf(f2_lo(F2), f2_hi(F2)), fminf(f2_hi(F1), cull));
+}
+
+// ---- packed nodes: 32 bytes, ONE 256-bit load per node visit ------------------------------------------------------
+// ncu on C3 (profiles/r2_summary.md): the L1 data pipe is the busiest unit of the kernel (79 % of its wavefront peak) and two
+// thirds of its wavefronts are the node loads — every divergent lane costs a wavefront per LDG.256, and a 64-byte node
+// is two of them.  A packed node is six words + two links: word (child, axis) = (half extent as bf16, rounded up) << 16 |
+// (box centre on a 16-bit grid over the scene bounds).  The traversal uses the WORD ITSELF as the half extent (as a
+// float it is the bf16 value plus at most 2^-7 of it: a slightly larger box, still conservative) and turns the centre
+// into a float with one logic operation per pair: 0x4B000000 | q is the float 2^23 + q, and the grid's scale and offset
+// (and the -2^23) are folded into the per-ray slab constants: a = (2^23 + q) * S + B with S = cell / d,
+// B = (grid origin - o) / d - 2^23 * S.  So a node visit is 1 LDG.256 + 3 64-bit LOP + the same 6 FFMA2 + 6 FADD2.
+// Error budget (all in units of one grid cell = scene extent / 65535): centre rounding 0.5, rounding of S times 2^23 0.5,
+// rounding of B 0.5; the emitted half extent is taken about the grid centre and enlarged by 1.25 cells + bf16 round-up
+// (rt_bvh.cu pack_axis).  Not parity-relevant: conservative culling only, the exact tests decide.
+__device__ __forceinline__ void slab_setup_packed(RaySlab& s, float3 ro, float3 rd, float max_abs, float pad_scale, float3 go, float3 gc)
+{
+    const float ix = __fdividef(1.0f, rd.x), iy = __fdividef(1.0f, rd.y), iz = __fdividef(1.0f, rd.z);
+    const float pad = pad_scale * fmaxf(fmaxf(max_abs, fabsf(ro.x)), fmaxf(fabsf(ro.y), fabsf(ro.z)));
+    const float ax = fabsf(ix), ay = fabsf(iy), az = fabsf(iz);
+    const float sx = gc.x * ix, sy = gc.y * iy, sz = gc.z * iz;
+    s.inv_xy = f2_pack(sx, sy); s.inv_z = sz;                                                   // S
+    s.noi_xy = f2_pack(__fmaf_rn(-8388608.0f, sx, (go.x - ro.x) * ix), __fmaf_rn(-8388608.0f, sy, (go.y - ro.y) * iy));
+    s.noi_z = __fmaf_rn(-8388608.0f, sz, (go.z - ro.z) * iz);                                   // B
+    s.ainv_xy = f2_pack(ax, ay); s.ainv_z = az;
+    s.pi_xy = f2_pack(pad * ax, pad * ay); s.pi_z = pad * az;
+}
+// 2^23 + q per half: (word & 0xffff) | 0x4B000000.  `magic` = 0x4B000000 must sit in a register for this to be ONE logic
+// operation per word (an instruction takes a single immediate): node_magic() hands it out through an opaque asm so that
+// the compiler keeps it instead of rebuilding it at every use.
+__device__ __forceinline__ unsigned node_magic() { unsigned m; asm volatile("mov.u32 %0, 0x4b000000;" : "=r"(m)); return m; }
+__device__ __forceinline__ f2_t f2_magic(f2_t w, unsigned magic)
+{
+    unsigned lo, hi;
+    asm("lop3.b32 %0, %1, 0xffff, %2, 0xea;" : "=r"(lo) : "r"((unsigned)(w & 0xffffffffull)), "r"(magic));
+    asm("lop3.b32 %0, %1, 0xffff, %2, 0xea;" : "=r"(hi) : "r"((unsigned)(w >> 32)), "r"(magic));
+    return (f2_t)lo | ((f2_t)hi << 32);
+}
+// np: the node's two float4 = words (L.x, L.y | L.z, R.z) (R.x, R.y | left, right)
+__device__ __forceinline__ void node_test_packed(const float4* np, const RaySlab& s, float cull, unsigned magic,
+                                                 float& ltn, float& ltf, float& rtn, float& rtf, int& cl, int& cr)
+{
+    f2_t h0, h1, h2, lk;
+    ldg256_f2(np, h0, h1, h2, lk);
+    cl = (int)(unsigned)(lk & 0xffffffffull); cr = (int)(unsigned)(lk >> 32);
+    const f2_t c0 = f2_magic(h0, magic), c1 = f2_magic(h1, magic), c2 = f2_magic(h2, magic);
+    const f2_t inv_zz = f2_pack(s.inv_z, s.inv_z), noi_zz = f2_pack(s.noi_z, s.noi_z);
+    const f2_t ainv_zz = f2_pack(s.ainv_z, s.ainv_z), pi_zz = f2_pack(s.pi_z, s.pi_z);
+    const f2_t P0 = f2_fma(c0, s.inv_xy, s.noi_xy);      // (L.a.x, L.a.y)
+    const f2_t P1 = f2_fma(c1, inv_zz, noi_zz);          // (L.a.z, R.a.z)
+    const f2_t P2 = f2_fma(c2, s.inv_xy, s.noi_xy);      // (R.a.x, R.a.y)
+    const f2_t Q0 = f2_fma(h0, s.ainv_xy, s.pi_xy);      // (L.b.x, L.b.y): the words themselves as half extents
+    const f2_t Q1 = f2_fma(h1, ainv_zz, pi_zz);          // (L.b.z, R.b.z)
+    const f2_t Q2 = f2_fma(h2, s.ainv_xy, s.pi_xy);      // (R.b.x, R.b.y)
     const f2_t N0 = f2_sub(P0, Q0), F0 = f2_add(P0, Q0), N1 = f2_sub(P1, Q1), F1 = f2_add(P1, Q1), N2 = f2_sub(P2, Q2), F2 = f2_add(P2, Q2);
     ltn = fmaxf(fmaxf(f2_lo(N0), f2_hi(N0)), fmaxf(f2_lo(N1), 0.0f));
     ltf = fminf(fminf(f2_lo(F0), f2_hi(F0)), fminf(f2_lo(F1), cull));

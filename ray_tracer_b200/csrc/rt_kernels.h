@@ -28,6 +28,10 @@
 
 namespace rt {
 
+#define RT_PF_MAX_PRIMS 262144u      // scenes up to this many primitives: push-time node prefetch, 64-byte float nodes; above: packed 32-byte nodes
+#ifndef RT_PACKED_NODES
+#define RT_PACKED_NODES 1            // 0 (tuning builds): 64-byte float nodes for flat scenes too
+#endif
 #ifndef RT_QUEUE_CHUNK
 #define RT_QUEUE_CHUNK 256ull     // work items a warp takes from the global queue per atomic (while plenty remain): 8 dispatches of one 8x4 tile.
                                   // Fewer tiles in flight per SM = warmer L1: 256 against 128 C3 +1.9 %, C4 +2.6 %, C2 +5.5 %, C5 +0.2 %; 512 C3 -5 %; 32 C3 -9 %
@@ -81,6 +85,8 @@ struct SceneBuffers {
     float4* iprims = nullptr;
     uint32_t n_inst = 0, n_iprims = 0, n_cold = 0, n_top_nodes = 0;
     float bounds_lo[3] = {0, 0, 0}, bounds_hi[3] = {0, 0, 0};       // exact bounds of the top level
+    bool packed = false;                                            // `nodes` holds packed 32-byte nodes (flat scenes with finite bounds; node_test_packed); else 64-byte float nodes
+    float grid_o[3] = {0, 0, 0}, grid_c[3] = {1, 1, 1};             // their 16-bit grid: origin and cell size per axis
     uint32_t n_prims = 0, n_spheres = 0, n_tris = 0, n_mats = 0, n_nodes = 0, max_depth = 0;
     int32_t root = -1;
     int builder = 0;               // hierarchy actually built: 0 = PLOC, 1 = radix tree
@@ -92,7 +98,7 @@ struct SceneBuffers {
 // validated). Synchronous with respect to `stream` on return.
 cudaError_t build_scene(SceneBuffers& out, const rt_sphere* spheres, uint32_t ns, const rt_vertex* vertices,
                         uint32_t nv, const uint32_t* indices, uint32_t ni, const rt_mesh* meshes, uint32_t nm,
-                        uint32_t leaf_size, int builder, int ploc_radius, int instancing /*0 never, 1 when eligible, 2 auto*/, cudaStream_t stream);
+                        uint32_t leaf_size, int builder, int ploc_radius, int instancing /*0 never, 1 when eligible, 2 auto*/, int node_format /*0 by size, 1 float, 2 packed (flat scenes)*/, cudaStream_t stream);
 
 // Same topology, new positions / radii / materials: re-derives the records and bounds from the
 // updated spheres and meshes (index ranges must be unchanged) and refits the hierarchy's boxes

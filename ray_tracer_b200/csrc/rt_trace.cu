@@ -124,6 +124,12 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
     int32_t j = 0, seg = 0;
     float4 incoming = make_float4(0.f, 0.f, 0.f, 0.f), color = incoming;
     float3 ro = f3(0.f, 0.f, 0.f), rd = ro;        // current ray
+    // Packed 32-byte nodes (node_test_packed) for large flat scenes: the variants without the push-time prefetch.  Same-box A/B
+    // against 64-byte float nodes: C5 (1.1 M primitives, L1 data pipe at 85 %) +8.2 %, but C3 -0.1 %, C4 -2.5 %, C2 -4.7 %,
+    // C1 -1.5 % (cache-resident scenes gain nothing from the halved node traffic and pay 7 more instructions per node visit
+    // and 1.2 % more visits), so the builder packs only above RT_PF_MAX_PRIMS primitives.
+    constexpr bool PK = RT_PACKED_NODES && !INST && !PF && !BRUTE;
+    const unsigned magic = PK ? node_magic() : 0u;  // 0x4B000000 in a register
     RaySlab slab;                                  // slab-test constants of the current ray: 1/d, -o/d, |1/d|, pad*|1/d|
     slab.inv_xy = slab.noi_xy = slab.ainv_xy = slab.pi_xy = 0ull; slab.inv_z = slab.noi_z = slab.ainv_z = slab.pi_z = 0.f;
     // item state touched once per camera path lives in shared memory (keeps the traversal loops at 64 registers)
@@ -140,7 +146,11 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
         slab.noi_xy = f2_pack(-(ro.x * f2_lo(slab.inv_xy)), -(ro.y * f2_hi(slab.inv_xy))); slab.noi_z = -(ro.z * slab.inv_z);
     };
     float cull = RT_FLT_MAX;                       // best.dst with slack: the distance beyond which a subtree is skipped (see RT_CULL_SLACK)
-    int node = RT_EMPTY, sp = 0;                   // current node (inner >= 0, leaf < 0, or RT_EMPTY) / stack height
+    int node = RT_EMPTY;                           // current node (inner >= 0, leaf < 0, or RT_EMPTY)
+    int* sp = stack;                               // the stack top as an ADDRESS: a push / pop is one STL / LDL and one add, no index scaling (3 LEA fewer per node step: C3 +0.6 %, C4 +0.8 %)
+#define RT_SP_RESET() (sp = stack + 1)
+#define RT_PUSH(v) (*sp++ = (v))
+#define RT_POP() (*--sp)
     uint32_t leaf_first = 0, leaf_count = 0;       // parked leaf primitives
 
     for (;;) {
@@ -179,7 +189,7 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
                             j = 0; total = make_float4(0.f, 0.f, 0.f, 0.f);
                         } else { has_item = false; need_path = false; }
                     } else {
-                        staging[(size_t)fi * plane + pix] = fr;
+                        __stcs(staging + ((size_t)fi * plane + pix), fr);        // written once, read once by the blend: streaming store (+0.3..0.5 %)
                         has_item = false; need_path = false;
                     }
                 }
@@ -260,7 +270,7 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
                 // ---- start the traversal of (ro, rd): wgsl:234 ----
                 best.dst = RT_FLT_MAX; best.u = 0.0f; best.v = 0.0f; best.id = RT_MISS; cull = RT_FLT_MAX;
                 if (INST) { best.aux = 0u; cur_inst = RT_NO_INST; }
-                sp = 1; node = RT_EMPTY; leaf_count = 0;
+                RT_SP_RESET(); node = RT_EMPTY; leaf_count = 0;
                 if (lp.bounces < 0) {
                     total = total + incoming; j++;                // wgsl:233 loop never runs: the path ends untraced
                     traced = false;                               // stays "shading" as a fresh lane needing a path
@@ -270,7 +280,8 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
                 } else if (sc.root < 0) {
                     traced = true;                                // empty scene: immediate miss
                 } else {
-                    slab_setup(slab, ro, rd, sc.max_abs, sc.pad_scale);
+                    if (!PK) slab_setup(slab, ro, rd, sc.max_abs, sc.pad_scale);
+                    else slab_setup_packed(slab, ro, rd, sc.max_abs, sc.pad_scale, sc.grid_o, sc.grid_c);
                     node = sc.root;
                     traced = true; shading = false;
                 }
@@ -290,24 +301,25 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
                 if (!shading && is_inner(node)) {
                     if (DETAIL) n_nodes++;
                     float ltn, ltf, rtn, rtf; int cl, cr;
-                    node_test(sc.nodes + 4 * (size_t)node, slab, cull, ltn, ltf, rtn, rtf, cl, cr);
+                    if (!PK) node_test(sc.nodes + 4 * (size_t)node, slab, cull, ltn, ltf, rtn, rtf, cl, cr);
+                    else node_test_packed(sc.nodes + 2 * (size_t)node, slab, cull, magic, ltn, ltf, rtn, rtf, cl, cr);
                     const bool hl = ltn <= ltf, hr = rtn <= rtf;
                     if (hl && hr) {
                         const bool left_first = ltn <= rtn;
-                        stack[sp++] = left_first ? cr : cl;
+                        RT_PUSH(left_first ? cr : cl);
                         node = left_first ? cl : cr;
                         if (PF) {                                // small scenes: start fetching the postponed child's node now
                             const int far_ = left_first ? cr : cl;
-                            if (far_ >= 0) asm volatile("prefetch.global.L1 [%0];" :: "l"(sc.nodes + 4 * (size_t)far_));
+                            if (far_ >= 0) asm volatile("prefetch.global.L1 [%0];" :: "l"(sc.nodes + (PK ? 2 : 4) * (size_t)far_));
                         }
                     } else if (hl) node = cl;
                     else if (hr) node = cr;
-                    else node = stack[--sp];
-                    if (INST && node == RT_MARKER && leaf_count == 0u) { leave_instance(); node = stack[--sp]; }
+                    else node = RT_POP();
+                    if (INST && node == RT_MARKER && leaf_count == 0u) { leave_instance(); node = RT_POP(); }
                     if (node < 0 && leaf_count == 0u) {          // park the leaf, keep descending
                         const uint32_t leaf = (uint32_t)(~node);
                         leaf_first = leaf >> 3; leaf_count = (leaf & 7u) + 1u;
-                        node = stack[--sp];
+                        node = RT_POP();
                     }
                 }
             };
@@ -347,10 +359,10 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
                     if (INST && (id & 0x80000000u)) {
                         // proxy of an instance: remember what is left of this leaf and where to go on, then enter the range's hierarchy
                         // (a lane whose node is RT_EMPTY popped the sentinel, sp == 0: the sentinel itself is its continuation)
-                        if (node == RT_EMPTY) sp = 1;
-                        if (leaf_count > 1u) stack[sp++] = ~(int)(((leaf_first + 1u) << 3) | (leaf_count - 2u));
-                        if (node != RT_EMPTY) stack[sp++] = node;
-                        stack[sp++] = RT_MARKER;
+                        if (node == RT_EMPTY) RT_SP_RESET();
+                        if (leaf_count > 1u) RT_PUSH(~(int)(((leaf_first + 1u) << 3) | (leaf_count - 2u)));
+                        if (node != RT_EMPTY) RT_PUSH(node);
+                        RT_PUSH(RT_MARKER);
                         node = __float_as_int(q1.x);
                         cur_inst = leaf_first;
                         slab.noi_xy = f2_fma(f2_pack(q0.x, q0.y), slab.inv_xy, slab.noi_xy);          // -(o - pos)/d = -o/d + pos/d
@@ -375,11 +387,11 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
                     cull = best.dst * RT_CULL_SLACK;
                     leaf_first++;
                     if (--leaf_count == 0u) {
-                        if (INST && node == RT_MARKER) { leave_instance(); node = stack[--sp]; }
+                        if (INST && node == RT_MARKER) { leave_instance(); node = RT_POP(); }
                         if (node < 0) {                              // a leaf was waiting in `node`
                             const uint32_t leaf = (uint32_t)(~node);
                             leaf_first = leaf >> 3; leaf_count = (leaf & 7u) + 1u;
-                            node = stack[--sp];
+                            node = RT_POP();
                         }
                     }
                 }
@@ -453,7 +465,6 @@ typedef void (*TraceFn)(SceneDev, CameraDev, LaunchParams, float4*, float4*, uin
 // PF: prefetch the postponed child of a two-hit node step into L1.  Pays while the hierarchy and the records fit the
 // caches (C3 +0.8 %, C4 +1.8 %, C2 +0.4 %); on C5 (1.1 M primitives, 140 MB of nodes + records, L1 data pipe at 85 %)
 // the extra requests cost 1.5 %, so the launcher picks the variant by scene size.
-#define RT_PF_MAX_PRIMS 262144u
 template <bool FOLD>
 TraceFn trace_variant_t(bool brute, bool detail, bool tex, bool pf, bool inst)
 {
@@ -488,15 +499,17 @@ cudaError_t launch_trace(const SceneDev& sc, const CameraDev& cam, const LaunchP
                          bool brute, bool detail, bool fold, int n_sms, cudaStream_t stream, bool with_blend)
 {
     if (lp.n_warp_tiles == 0 || lp.n_frames == 0) return cudaSuccess;
-    const bool inst = sc.iprims != nullptr;
-    if (inst && brute) return cudaErrorNotSupported;           // rt_api.cu refuses this combination with a message
+    if (sc.iprims != nullptr && brute) return cudaErrorNotSupported;   // rt_api.cu refuses this combination with a message
+    const bool pf = !brute && sc.iprims == nullptr && !sc.packed && sc.n_prims <= RT_PF_MAX_PRIMS;
+    // float nodes are read by the PF variants (small scenes) and the INST variants (instanced scenes; also large flat scenes
+    // whose bounds are not finite and so have no packed nodes); the variants in between read packed nodes
+    const bool inst = sc.iprims != nullptr || (RT_PACKED_NODES && !brute && !pf && !sc.packed);
     cudaError_t e = cudaMemsetAsync(queue, 0, sizeof(unsigned long long), stream);
     if (e != cudaSuccess) return e;
     const bool tex = sc.c3 != nullptr && sc.n_tex != 0u;       // texture code only when the scene carries handles and a table is bound
     const uint64_t n_items = (uint64_t)lp.n_warp_tiles * (fold ? 1u : lp.n_frames) * 32ull;
     const uint64_t per_grab = fold ? 32ull : RT_QUEUE_CHUNK;
     const uint64_t warps_needed = (n_items + per_grab - 1) / per_grab;
-    const bool pf = !brute && !inst && sc.n_prims <= RT_PF_MAX_PRIMS;
     uint64_t blocks = (uint64_t)n_sms * trace_blocks_per_sm(brute, detail, tex, pf, fold, inst);
     const uint64_t cap = (warps_needed + RT_BLOCK_THREADS / 32 - 1) / (RT_BLOCK_THREADS / 32);
     if (blocks > cap) blocks = cap;
@@ -571,8 +584,9 @@ cudaError_t launch_trace_static(const SceneDev& sc, const CameraDev& cam, const 
 {
     if (lp.n_warp_tiles == 0 || lp.n_frames == 0) return cudaSuccess;
     if ((uint64_t)lp.n_frames * lp.width * lp.height * sizeof(float4) > (uint64_t)RT_STATIC_SCRATCH_BYTES) return cudaErrorInvalidValue;
-    const bool inst = sc.iprims != nullptr;
-    if (inst && brute) return cudaErrorNotSupported;
+    if (sc.iprims != nullptr && brute) return cudaErrorNotSupported;
+    const bool pf = !brute && sc.iprims == nullptr && !sc.packed && sc.n_prims <= RT_PF_MAX_PRIMS;
+    const bool inst = sc.iprims != nullptr || (RT_PACKED_NODES && !brute && !pf && !sc.packed);
     unsigned char* base = nullptr;
     cudaError_t e = static_scratch(device, &base);
     if (e != cudaSuccess) return e;
@@ -582,7 +596,6 @@ cudaError_t launch_trace_static(const SceneDev& sc, const CameraDev& cam, const 
     const bool tex = sc.c3 != nullptr && sc.n_tex != 0u;
     const uint64_t n_items = (uint64_t)lp.n_warp_tiles * lp.n_frames * 32ull;
     const uint64_t warps_needed = (n_items + RT_QUEUE_CHUNK - 1) / RT_QUEUE_CHUNK;
-    const bool pf = !brute && !inst && sc.n_prims <= RT_PF_MAX_PRIMS;
     uint64_t blocks = (uint64_t)n_sms * trace_blocks_per_sm(brute, detail, tex, pf, false, inst);
     const uint64_t cap = (warps_needed + RT_BLOCK_THREADS / 32 - 1) / (RT_BLOCK_THREADS / 32);
     if (blocks > cap) blocks = cap;

@@ -118,6 +118,7 @@ wave_trace(SceneDev sc, WaveDev wv, int n_stay, int refill_min)
     float3 ro = f3(0.f, 0.f, 0.f), rd = ro;
     RaySlab slab;
     slab.inv_xy = slab.noi_xy = slab.ainv_xy = slab.pi_xy = 0ull; slab.inv_z = slab.noi_z = slab.ainv_z = slab.pi_z = 0.f;
+    const unsigned magic = node_magic();
     HitRec best; best.dst = RT_FLT_MAX; best.u = best.v = 0.f; best.id = RT_MISS;
     float cull = RT_FLT_MAX;                         // best.dst with slack (RT_CULL_SLACK, rt_kernels.h)
     int node = WV_EMPTY, sp = 1;
@@ -146,7 +147,8 @@ wave_trace(SceneDev sc, WaveDev wv, int n_stay, int refill_min)
                 if (BRUTE) leaf_count = sc.n_prims;
                 else if (sc.root >= 0) {
                     node = sc.root;
-                    slab_setup(slab, ro, rd, sc.max_abs, sc.pad_scale);
+                    if (sc.packed) slab_setup_packed(slab, ro, rd, sc.max_abs, sc.pad_scale, sc.grid_o, sc.grid_c);
+                    else slab_setup(slab, ro, rd, sc.max_abs, sc.pad_scale);
                 }
                 active = true;
                 n_rays++;
@@ -165,7 +167,8 @@ wave_trace(SceneDev sc, WaveDev wv, int n_stay, int refill_min)
                 if (active && node >= 0 && node != WV_EMPTY) {
                     if (DETAIL) n_nodes++;
                     float ltn, ltf, rtn, rtf; int cl, cr;
-                    node_test(sc.nodes + 4 * (size_t)node, slab, cull, ltn, ltf, rtn, rtf, cl, cr);
+                    if (sc.packed) node_test_packed(sc.nodes + 2 * (size_t)node, slab, cull, magic, ltn, ltf, rtn, rtf, cl, cr);
+                    else node_test(sc.nodes + 4 * (size_t)node, slab, cull, ltn, ltf, rtn, rtf, cl, cr);
                     const bool hl = ltn <= ltf, hr = rtn <= rtf;
                     if (hl && hr) {
                         const bool left_first = ltn <= rtn;

@@ -170,6 +170,11 @@ class RayTracer:
     def set_option(self, option, value):
         self._ck(self._L.rt_set_option(self._h, int(option), int(value)))
 
+    def get_option(self, option):
+        v = C.c_int64()
+        self._ck(self._L.rt_get_option(self._h, int(option), C.byref(v)))
+        return int(v.value)
+
     # -- read-out ----------------------------------------------------------------------
     def read_accum(self, out=None):
         if out is None:

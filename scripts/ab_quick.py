@@ -1,5 +1,7 @@
-"""Kernel-only rate of the in-tree (or RT_B200_LIB) build: python scripts/ab_quick.py [config:frames ...] [--sched n,s]"""
+"""Kernel-only rate of the in-tree (or RT_B200_LIB) build: python scripts/ab_quick.py [config:frames ...]
+Prints a CRC of the accumulation image and the ray count per job: variants must agree on both."""
 import sys
+import zlib
 sys.path.insert(0, ".")
 import ray_tracer_b200 as rt
 from ray_tracer_b200 import configs
@@ -18,5 +20,6 @@ for job in jobs:
         tr.render_frames(0, frames); tr.sync()
         c = tr.counters()
         best = max(best, c["rays"] / c["kernel_ms"] / 1e3)
-    print("%-10s %4d dispatches  launches %d  best of 3: %9.1f Mrays/s  (%.3f ms)" % (name, frames, c["launches"], best, c["rays"] / best / 1e3), flush=True)
+    crc = zlib.crc32(tr.read_accum().tobytes())
+    print("%-10s %4d dispatches  launches %d  best of 3: %9.1f Mrays/s  (%.3f ms)  rays %d  image crc %08x" % (name, frames, c["launches"], best, c["rays"] / best / 1e3, c["rays"], crc), flush=True)
     tr.close()

@@ -9,7 +9,7 @@ from util import assert_bits_equal
 pytestmark = pytest.mark.gpu
 
 
-def _gpu(rt, scene, w, h, frames, bounces, sky, brute=False, leaf=None, builder=None, radius=None, kernel=None, slots=None, rpp=1, detail=False, inst=None):
+def _gpu(rt, scene, w, h, frames, bounces, sky, brute=False, leaf=None, builder=None, radius=None, kernel=None, slots=None, rpp=1, detail=False, inst=None, nodes=None):
     cam, sp, vs, ix, ms = scene.as_tuple()
     tr = rt.RayTracer(0, w, h)
     tr.set_option(rt._lib.RT_OPT_TRAVERSAL, 1 if brute else 0)      # before the upload: the exhaustive scan needs flattened records
@@ -27,6 +27,8 @@ def _gpu(rt, scene, w, h, frames, bounces, sky, brute=False, leaf=None, builder=
         tr.set_option(rt._lib.RT_OPT_WAVE_SLOTS, slots)
     if detail:
         tr.set_option(rt._lib.RT_OPT_DETAIL_COUNTERS, 1)
+    if nodes is not None:
+        tr.set_option(rt._lib.RT_OPT_NODE_FORMAT, nodes)
     tr.upload_scene(sp, vs, ix, ms)
     if scene.textures:
         tr.upload_textures(scene.textures)
@@ -34,7 +36,9 @@ def _gpu(rt, scene, w, h, frames, bounces, sky, brute=False, leaf=None, builder=
     tr.set_params(number_of_bounces=bounces, rays_per_pixel=rpp, skybox=sky, frames=0)
     tr.set_option(rt._lib.RT_OPT_PRIMARY_IDS, 1)
     tr.render_frames(0, frames)
-    out = tr.read_accum(), tr.read_primary_ids(), tr.counters(), tr.bvh_stats()
+    st = tr.bvh_stats()
+    st["packed"] = tr.get_option(rt._lib.RT_OPT_NODES_PACKED)
+    out = tr.read_accum(), tr.read_primary_ids(), tr.counters(), st
     tr.close()
     return out
 
@@ -112,16 +116,78 @@ def test_degenerate_scenes_build(rtlib, oracle):
     assert_bits_equal(a, b, "identical spheres")
 
 
+@pytest.mark.parametrize("name,w,h,frames,kernel", [("c3_teapot", 240, 136, 2, None), ("c4_tree", 240, 136, 2, None), ("c2_cube", 240, 136, 2, None),
+                                                      ("c1_balls", 200, 200, 3, None), ("c3_teapot", 160, 90, 2, 1)])
+def test_packed_nodes_are_result_invisible(rtlib, name, w, h, frames, kernel):
+    """RT_OPT_NODE_FORMAT: packed 32-byte nodes (centres on a 16-bit grid, bf16 half extents — larger boxes, never smaller)
+    == 64-byte float nodes == the exhaustive scan, bit for bit; by default small scenes get float nodes."""
+    from ray_tracer_b200 import configs
+    scene, meta = configs.build(name, w, h)
+    p = meta["params"]
+    f, fid, fc, fst = _gpu(rtlib, scene, w, h, frames, p["number_of_bounces"], p["skybox"], nodes=1, kernel=kernel)
+    q, qid, qc, qst = _gpu(rtlib, scene, w, h, frames, p["number_of_bounces"], p["skybox"], nodes=2, kernel=kernel, detail=True)
+    d, did, dc, dst = _gpu(rtlib, scene, w, h, frames, p["number_of_bounces"], p["skybox"], detail=True)
+    b, bid, bc, _ = _gpu(rtlib, scene, w, h, frames, p["number_of_bounces"], p["skybox"], brute=True)
+    assert fst["packed"] == 0 and qst["packed"] == 1 and dst["packed"] == 0
+    assert np.array_equal(qid, bid) and np.array_equal(fid, bid) and qc["rays"] == fc["rays"] == bc["rays"]
+    assert_bits_equal(q, b, name + " packed vs exhaustive")
+    assert_bits_equal(f, b, name + " float vs exhaustive")
+    assert dc["node_visits"] <= qc["node_visits"] <= 1.1 * dc["node_visits"]      # the packed boxes cost a few percent more visits
+
+
+def test_packed_nodes_degenerate_bounds_and_refit(rtlib):
+    """Packed nodes on a scene that is flat along an axis (cell size floor), on bounds that are not finite (no grid: float
+    nodes are emitted instead) and through rt_update_records (the grid moves with the records)."""
+    from ray_tracer_b200 import host
+    L = rtlib._lib
+    scene = host.Scene.room(np.float32(1.5))
+    cam, sp, vs, ix, ms = scene.as_tuple()
+    w, h = 120, 80
+
+    def run(sp_, vs_, ms_, fmt, brute=False, moved=None):
+        tr = rtlib.RayTracer(0, w, h)
+        tr.set_option(L.RT_OPT_TRAVERSAL, 1 if brute else 0); tr.set_option(L.RT_OPT_NODE_FORMAT, fmt)
+        tr.upload_scene(sp_, vs_, ix, ms_)
+        if moved is not None:
+            tr.update_records(*moved)
+        tr.set_camera(cam); tr.set_params(number_of_bounces=3, rays_per_pixel=1, skybox=1, frames=0)
+        tr.render_frames(0, 2)
+        out = tr.read_accum(), tr.get_option(L.RT_OPT_NODES_PACKED)
+        tr.close()
+        return out
+
+    # (a) everything in the plane z = -3: extent 0 along z
+    vs2 = vs.copy(); vs2["pos"][:, 2] = -3.0
+    sp0 = sp[:0]
+    a, pa = run(sp0, vs2, ms, 2); b, _ = run(sp0, vs2, ms, 1, brute=True)
+    assert pa == 1
+    assert_bits_equal(a, b, "planar scene, packed nodes")
+    # (b) one vertex at infinity: no finite grid, float nodes take over
+    vs3 = vs.copy(); vs3["pos"][0, 0] = np.inf
+    a, pa = run(sp, vs3, ms, 2); b, _ = run(sp, vs3, ms, 1, brute=True)
+    assert pa == 0
+    assert_bits_equal(a, b, "infinite vertex: fallback to float nodes", any_nan=True)
+    # (c) refit: spheres and meshes moved far outside the uploaded bounds
+    sp4 = sp.copy(); sp4["position"][:, 0] += 40.0
+    ms4 = ms.copy(); ms4["pos"][:, 1] -= 25.0
+    a, pa = run(sp, vs, ms, 2, moved=(sp4, ms4)); b, _ = run(sp4, vs, ms4, 1, brute=True)
+    assert pa == 1
+    assert_bits_equal(a, b, "refit with packed nodes")
+
+
 def test_stress_scene_builds_and_matches_brute_force_on_a_crop(rtlib):
     """C5 (100k spheres + 64 teapot instances = 1.1 M primitives): LBVH vs exhaustive GPU mode
     on a small image."""
     from ray_tracer_b200 import configs
     scene, meta = configs.build("c5_stress", 64, 36)
     a, aid, ac, st = _gpu(rtlib, scene, 64, 36, 1, 3, 1, inst=0)
-    assert st["n_prims"] == 100000 + 64 * 15704
+    assert st["n_prims"] == 100000 + 64 * 15704 and st["packed"] == 1      # above 262,144 primitives: packed nodes by default
     b, bid, bc, _ = _gpu(rtlib, scene, 64, 36, 1, 3, 1, brute=True)
     assert np.array_equal(aid, bid) and ac["rays"] == bc["rays"]
     assert_bits_equal(a, b, "c5")
+    f, fid, fc, fst = _gpu(rtlib, scene, 64, 36, 1, 3, 1, inst=0, nodes=1)       # a large scene with float nodes runs on the INST kernel variants
+    assert fst["packed"] == 0 and np.array_equal(fid, bid) and fc["rays"] == bc["rays"]
+    assert_bits_equal(f, b, "c5, float nodes")
 
 
 def test_instanced_hierarchy_equals_flattened_records(rtlib):
