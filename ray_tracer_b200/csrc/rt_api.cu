@@ -61,7 +61,7 @@ struct rt_ctx {
     rt_params params{};
     rt_camera_uniform camera{};
     uint32_t tile_rank = 0, tile_world = 1, frame_rank = 0, frame_world = 1;
-    int64_t opt_traversal = 0, opt_seed_mode = 0, opt_primary_ids = 0, opt_detail = 0, opt_frames_per_launch = 0, opt_leaf_size = 2, opt_builder = 0, opt_ploc_radius = 3, opt_kernel = 0, opt_wave_slots = 1 << 21;
+    int64_t opt_traversal = 0, opt_seed_mode = 0, opt_primary_ids = 0, opt_detail = 0, opt_frames_per_launch = 0, opt_leaf_size = 0, opt_builder = 0, opt_ploc_radius = 0, opt_kernel = 0, opt_wave_slots = 1 << 21;
     rt::WavePool wave;                            // path-slot pool of the wavefront kernels (RT_OPT_KERNEL = 1)
     uint64_t dispatches = 0, launches = 0;
     double kernel_ms = 0.0;
@@ -356,19 +356,27 @@ int rt_upload_scene(rt_ctx* c, const rt_sphere* spheres, uint32_t ns, const rt_v
         }
         total_tris += me.triangles;
     }
-    if ((uint64_t)ns + total_tris >= (1ull << 28))
-        return fail(c, RT_ERR_UNSUPPORTED, "rt_upload_scene: more than 2^28 primitives");
+    if ((uint64_t)ns + total_tris >= (1ull << 27))         // node addresses are 32-bit byte offsets: 2^27 packed nodes of 32 bytes
+        return fail(c, RT_ERR_UNSUPPORTED, "rt_upload_scene: more than 2^27 primitives");
     DeviceGuard g(c->device);
     CU(c, cudaStreamSynchronize(c->stream));
-    uint32_t leaf = (uint32_t)(c->opt_leaf_size < 1 ? 1 : (c->opt_leaf_size > 8 ? 8 : c->opt_leaf_size));
+    // 0 = by size (scripts/builder_sweep.py): leaves of 2 and a +-3 window up to 262,144 primitives; above, where the packed nodes make
+    // node visits cheap relative to record fetches, leaves of 1 and a +-2 window (C5: 4,702 against 4,412 Mrays/s)
+    const bool large = (uint64_t)ns + total_tris > RT_PF_MAX_PRIMS;
+    const uint32_t leaf = (uint32_t)(c->opt_leaf_size < 1 ? (large ? 1 : 2) : (c->opt_leaf_size > 8 ? 8 : c->opt_leaf_size));
+    const int radius = (int)(c->opt_ploc_radius < 1 ? (large ? 2 : 3) : c->opt_ploc_radius);
     // Mesh records aliasing one (first, triangles, offset) range become instances of one object-space hierarchy, unless the
     // exhaustive scan or the wavefront kernels (which need flattened records) are selected at upload time
     const int instancing = (c->opt_traversal == 0 && c->opt_kernel == 0) ? (int)c->opt_instancing : 0;
-    cudaError_t e = rt::build_scene(c->scene, spheres, ns, vertices, nv, indices, ni, meshes, nm, leaf, (int)c->opt_builder, (int)c->opt_ploc_radius, instancing, (int)c->opt_node_format, c->stream);
+    cudaError_t e = rt::build_scene(c->scene, spheres, ns, vertices, nv, indices, ni, meshes, nm, leaf, (int)c->opt_builder, radius, instancing, (int)c->opt_node_format, c->stream);
     if (e != cudaSuccess) { c->has_scene = false; return cuda_fail(c, e, "scene build"); }
     if (c->scene.n_inst != 0 && c->scene.max_depth > RT_STACK - 2) {          // two levels too deep for the stack: flatten instead
-        e = rt::build_scene(c->scene, spheres, ns, vertices, nv, indices, ni, meshes, nm, leaf, (int)c->opt_builder, (int)c->opt_ploc_radius, 0, (int)c->opt_node_format, c->stream);
+        e = rt::build_scene(c->scene, spheres, ns, vertices, nv, indices, ni, meshes, nm, leaf, (int)c->opt_builder, radius, 0, (int)c->opt_node_format, c->stream);
         if (e != cudaSuccess) { c->has_scene = false; return cuda_fail(c, e, "scene build"); }
+    }
+    if (!c->scene.packed && (uint64_t)c->scene.n_nodes >= (1ull << 26)) {      // ... and 2^26 float nodes of 64 bytes (forced float nodes, bounds that are not finite, instanced scenes)
+        c->has_scene = false;
+        return fail(c, RT_ERR_UNSUPPORTED, "rt_upload_scene: more than 2^26 hierarchy nodes in the 64-byte format (RT_OPT_NODE_FORMAT = 1, instancing, or bounds that are not finite)");
     }
     // A hierarchy deeper than the traversal stack (both builders; needs thousands of coincident primitives plus far
     // outliers) is not an error: the reference renders any scene, so such a scene is traced with the exhaustive scan.
@@ -398,6 +406,10 @@ int rt_update_records(rt_ctx* c, const rt_sphere* spheres, uint32_t ns, const rt
     CU(c, cudaStreamSynchronize(c->stream));
     cudaError_t e = rt::refit_scene(c->scene, spheres, meshes, c->stream);
     if (e != cudaSuccess) { c->has_scene = false; return cuda_fail(c, e, "scene refit"); }
+    if (!c->scene.packed && (uint64_t)c->scene.n_nodes >= (1ull << 26)) {      // the moved bounds are not finite any more and the scene is too large for float nodes
+        c->has_scene = false;
+        return fail(c, RT_ERR_UNSUPPORTED, "rt_update_records: more than 2^26 hierarchy nodes in the 64-byte format (bounds that are not finite)");
+    }
     c->mesh_ranges.assign(meshes, meshes + nm);
     return RT_OK;
 }
@@ -792,10 +804,10 @@ int rt_set_option(rt_ctx* c, int option, int64_t value)
     case RT_OPT_DETAIL_COUNTERS: c->opt_detail = value != 0; return RT_OK;
     case RT_OPT_FRAMES_PER_LAUNCH: if (value < 0 || value > (1 << 20)) break; c->opt_frames_per_launch = value; return RT_OK;
     case RT_OPT_ITEM_MODE: if (value < 0 || value > 2) break; c->opt_item_mode = value; return RT_OK;
-    case RT_OPT_LEAF_SIZE: if (value < 1 || value > 8) break; c->opt_leaf_size = value; return RT_OK;
+    case RT_OPT_LEAF_SIZE: if (value < 0 || value > 8) break; c->opt_leaf_size = value; return RT_OK;
     case RT_OPT_SCHED: c->opt_sched = value & 0xffffff; return RT_OK;
     case RT_OPT_BUILDER: if (value != 0 && value != 1) break; c->opt_builder = value; return RT_OK;
-    case RT_OPT_PLOC_RADIUS: if (value < 1 || value > 16) break; c->opt_ploc_radius = value; return RT_OK;
+    case RT_OPT_PLOC_RADIUS: if (value < 0 || value > 16) break; c->opt_ploc_radius = value; return RT_OK;
     case RT_OPT_KERNEL: if (value != 0 && value != 1) break;
         if (value == 1 && c->has_scene && c->scene.n_inst != 0) return fail(c, RT_ERR_UNSUPPORTED, "rt_set_option: the wavefront kernels need flattened records; set RT_OPT_KERNEL = 1 (or RT_OPT_INSTANCING = 0) before rt_upload_scene");
         c->opt_kernel = value; return RT_OK;

@@ -301,8 +301,10 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
                 if (!shading && is_inner(node)) {
                     if (DETAIL) n_nodes++;
                     float ltn, ltf, rtn, rtf; int cl, cr;
-                    if (!PK) node_test(sc.nodes + 4 * (size_t)node, slab, cull, ltn, ltf, rtn, rtf, cl, cr);
-                    else node_test_packed(sc.nodes + 2 * (size_t)node, slab, cull, magic, ltn, ltf, rtn, rtf, cl, cr);
+                    // the node's address from a 32-bit byte offset (rt_upload_scene bounds the node count accordingly): LEA + carry on the uniform
+                    // base instead of a per-thread constant load feeding a 64-bit multiply-add in front of every node fetch (C3 +0.6 %, C5 +1.3 %)
+                    if (!PK) node_test((const float4*)((const char*)sc.nodes + ((uint32_t)node << 6)), slab, cull, ltn, ltf, rtn, rtf, cl, cr);
+                    else node_test_packed((const float4*)((const char*)sc.nodes + ((uint32_t)node << 5)), slab, cull, magic, ltn, ltf, rtn, rtf, cl, cr);
                     const bool hl = ltn <= ltf, hr = rtn <= rtf;
                     if (hl && hr) {
                         const bool left_first = ltn <= rtn;
@@ -310,7 +312,7 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
                         node = left_first ? cl : cr;
                         if (PF) {                                // small scenes: start fetching the postponed child's node now
                             const int far_ = left_first ? cr : cl;
-                            if (far_ >= 0) asm volatile("prefetch.global.L1 [%0];" :: "l"(sc.nodes + (PK ? 2 : 4) * (size_t)far_));
+                            if (far_ >= 0) asm volatile("prefetch.global.L1 [%0];" :: "l"((const char*)sc.nodes + ((uint32_t)far_ << (PK ? 5 : 6))));
                         }
                     } else if (hl) node = cl;
                     else if (hr) node = cr;
