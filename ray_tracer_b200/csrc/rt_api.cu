@@ -4,7 +4,9 @@
 #include <math.h>
 #include <stdio.h>
 #include <string.h>
+#include <set>
 #include <string>
+#include <tuple>
 #include <vector>
 #include "rt_kernels.h"
 
@@ -340,6 +342,7 @@ int rt_upload_scene(rt_ctx* c, const rt_sphere* spheres, uint32_t ns, const rt_v
         return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_upload_scene: NULL array with non-zero count");
     // The shader indexes unchecked (wgsl:161-170); here every address is validated up front.
     uint64_t total_tris = 0;
+    std::set<std::tuple<uint32_t, uint32_t, uint32_t>> checked;
     for (uint32_t m = 0; m < nm; m++) {
         const rt_mesh& me = meshes[m];
         if (me.triangles == 0) continue;
@@ -348,6 +351,8 @@ int rt_upload_scene(rt_ctx* c, const rt_sphere* spheres, uint32_t ns, const rt_v
             char b[160]; snprintf(b, sizeof b, "rt_upload_scene: mesh %u reads indices[%u..%llu) of %u", m, me.first, (unsigned long long)end, ni);
             return fail(c, RT_ERR_BAD_INDEX, b);
         }
+        // records that alias one (first, triangles, offset) range (instances) are checked once
+        if (!checked.insert(std::make_tuple(me.first, me.triangles, me.offset)).second) { total_tris += me.triangles; continue; }
         for (uint64_t k = me.first; k < end; k++) {
             if ((uint64_t)me.offset + indices[k] >= nv) {
                 char b[160]; snprintf(b, sizeof b, "rt_upload_scene: mesh %u index %llu -> vertex %llu of %u", m, (unsigned long long)k, (unsigned long long)me.offset + indices[k], nv);

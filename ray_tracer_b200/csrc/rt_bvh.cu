@@ -1012,6 +1012,10 @@ cudaError_t refit_scene(SceneBuffers& sc, const rt_sphere* spheres, const rt_mes
             if (f == f && fabsf(f) <= 3.0e38f && fabsf(f) > m) m = fabsf(f);
         }
         sc.max_abs = m;
+        for (int q = 0; q < 3; q++) {
+            int e0 = hb[q], e1 = hb[q + 3]; int b0 = e0 >= 0 ? e0 : e0 ^ 0x7fffffff, b1 = e1 >= 0 ? e1 : e1 ^ 0x7fffffff;
+            memcpy(&sc.bounds_lo[q], &b0, 4); memcpy(&sc.bounds_hi[q], &b1, 4);
+        }
     }
 done:
     return err;

@@ -16,3 +16,7 @@ timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --
 timeout 300 python scripts/profile_run.py c3_teapot 128 > $O/profile_run.txt 2>&1 && \
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:trace_kernel -s 1 -c 1 -f -o $O/prof_r2_c3 python scripts/profile_run.py c3_teapot 128 > $O/ncu_full.log 2>&1
 cat $O/profile_run.txt; tail -3 $O/ncu_full.log
+timeout 300 python scripts/profile_run.py c5_stress 8 > $O/profile_run_c5.txt 2>&1 && \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:trace_kernel -s 1 -c 1 -f -o $O/prof_r2_c5 python scripts/profile_run.py c5_stress 8 > $O/ncu_full_c5.log 2>&1
+cat $O/profile_run_c5.txt; tail -3 $O/ncu_full_c5.log
+timeout 200 python scripts/e2e_probe.py > $O/e2e_probe.txt 2>&1; cat $O/e2e_probe.txt
