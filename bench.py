@@ -439,7 +439,7 @@ def run_ours(args, rank, world, local_rank):
                          "traffic": (ncu_traffic(args.config) or {}).get("dram_bytes_per_launch"), "traffic_detail": ncu_traffic(args.config),
                          "peak_source": "FFMA microbenchmark run in this process (rt_measure_fp32_peak); theoretical 148x128x2x%.0f MHz = %.1f" % (
                              pk.get("sm_max_mhz", 1965.0), 148 * 128 * 2 * pk.get("sm_max_mhz", 1965.0) * 1e6 / 1e12),
-                         "kernel": "rt::trace_kernel<BRUTE=false,DETAIL=false,TEX=%s,PF=%s,FOLD=false>" % ("true" if scene.textures else "false", "true" if (int(ms["triangles"].sum()) + int(sp.size)) <= 262144 else "false"), "launch_ms": launch_s * 1e3,
+                         "kernel": "rt::trace_kernel<BRUTE=false,DETAIL=false,TEX=%s,PF=%s,FOLD=false,INST=false>%s" % ("true" if scene.textures else "false", "true" if (int(ms["triangles"].sum()) + int(sp.size)) <= 262144 else "false", "" if (int(ms["triangles"].sum()) + int(sp.size)) <= 262144 else " (packed 32-byte nodes)"), "launch_ms": launch_s * 1e3,
                          "flops_per_launch": flops_step / launches_per_step,
                          "per_ray": {"node_visits": det["node_visits"] / det["rays"], "tri_tests": det["tri_tests"] / det["rays"],
                                      "sphere_tests": det["sphere_tests"] / det["rays"], "hit_fraction": det["hit_segments"] / det["rays"]},
