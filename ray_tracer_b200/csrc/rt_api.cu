@@ -200,6 +200,9 @@ int launch(rt_ctx* c, int32_t first_frame, uint32_t n_frames, bool want_ids, int
     lp.n_warp_tiles = 2u * (tiles > c->tile_rank ? (tiles - c->tile_rank + c->tile_world - 1) / c->tile_world : 0);
     lp.seed_mode = (int32_t)c->opt_seed_mode;
     lp.queue_guide = (uint32_t)(n_frames <= 16u ? 2ull * RT_QUEUE_GUIDE : RT_QUEUE_GUIDE);
+    lp.queue_chunk = (uint32_t)RT_QUEUE_CHUNK;
+    if ((c->opt_sched >> 24) & 0xff) lp.queue_chunk = 32u * (uint32_t)((c->opt_sched >> 24) & 0xff);      // tuning: RT_OPT_SCHED bits 24-31 = grab size / 32, bits 32-39 = guide
+    if ((c->opt_sched >> 32) & 0xff) lp.queue_guide = (uint32_t)((c->opt_sched >> 32) & 0xff);
     lp.div_frames = rt::make_fastdiv(n_frames); lp.div_tiles_x = rt::make_fastdiv(lp.tiles_x); lp.div_width = rt::make_fastdiv(c->width);
     lp.rpp_scale = (lp.rpp > 0 && (lp.rpp & (lp.rpp - 1)) == 0) ? 1.0f / (float)lp.rpp : 0.0f;
     lp.sched_n_stay = (int32_t)(c->opt_sched & 0xff); if (lp.sched_n_stay < 1) lp.sched_n_stay = 1; lp.sched_l_stay = (int32_t)((c->opt_sched >> 8) & 0xff); lp.sched_s_min = (int32_t)((c->opt_sched >> 16) & 0xff);
@@ -593,6 +596,9 @@ int rt_render_frames_static(rt_ctx* c, int32_t first_frame, uint32_t n_frames)
     lp.n_warp_tiles = 2u * (tiles > c->tile_rank ? (tiles - c->tile_rank + c->tile_world - 1) / c->tile_world : 0);
     lp.seed_mode = (int32_t)c->opt_seed_mode;
     lp.queue_guide = (uint32_t)(n_frames <= 16u ? 2ull * RT_QUEUE_GUIDE : RT_QUEUE_GUIDE);
+    lp.queue_chunk = (uint32_t)RT_QUEUE_CHUNK;
+    if ((c->opt_sched >> 24) & 0xff) lp.queue_chunk = 32u * (uint32_t)((c->opt_sched >> 24) & 0xff);      // tuning: RT_OPT_SCHED bits 24-31 = grab size / 32, bits 32-39 = guide
+    if ((c->opt_sched >> 32) & 0xff) lp.queue_guide = (uint32_t)((c->opt_sched >> 32) & 0xff);
     lp.div_frames = rt::make_fastdiv(n_frames); lp.div_tiles_x = rt::make_fastdiv(lp.tiles_x); lp.div_width = rt::make_fastdiv(c->width);
     lp.rpp_scale = (lp.rpp > 0 && (lp.rpp & (lp.rpp - 1)) == 0) ? 1.0f / (float)lp.rpp : 0.0f;
     lp.sched_n_stay = (int32_t)(c->opt_sched & 0xff); if (lp.sched_n_stay < 1) lp.sched_n_stay = 1; lp.sched_l_stay = (int32_t)((c->opt_sched >> 8) & 0xff); lp.sched_s_min = (int32_t)((c->opt_sched >> 16) & 0xff);
@@ -810,7 +816,7 @@ int rt_set_option(rt_ctx* c, int option, int64_t value)
     case RT_OPT_FRAMES_PER_LAUNCH: if (value < 0 || value > (1 << 20)) break; c->opt_frames_per_launch = value; return RT_OK;
     case RT_OPT_ITEM_MODE: if (value < 0 || value > 2) break; c->opt_item_mode = value; return RT_OK;
     case RT_OPT_LEAF_SIZE: if (value < 0 || value > 8) break; c->opt_leaf_size = value; return RT_OK;
-    case RT_OPT_SCHED: c->opt_sched = value & 0xffffff; return RT_OK;
+    case RT_OPT_SCHED: c->opt_sched = value & 0xffffffffffll; return RT_OK;
     case RT_OPT_BUILDER: if (value != 0 && value != 1) break; c->opt_builder = value; return RT_OK;
     case RT_OPT_PLOC_RADIUS: if (value < 0 || value > 16) break; c->opt_ploc_radius = value; return RT_OK;
     case RT_OPT_KERNEL: if (value != 0 && value != 1) break;

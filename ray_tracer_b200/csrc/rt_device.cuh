@@ -93,6 +93,7 @@ struct LaunchParams {
     uint32_t frame_world;      // stride between frames rendered by this rank
     uint32_t tiles_x, n_warp_tiles;  // 8x8 shard tiles per row; 8x4 warp tiles owned by this rank (2 per shard tile)
     int32_t seed_mode;
+    uint32_t queue_chunk;      // items per grab while plenty remain (a multiple of 32)
     uint32_t queue_guide;      // guided self-scheduling of the item queue: grab = remaining / (warps x queue_guide), see rt_kernels.h
     int32_t sched_n_stay, sched_l_stay, sched_s_min;   // warp scheduler thresholds (lanes)
     FastDiv div_frames, div_tiles_x, div_width;         // item decode without integer divisions

@@ -208,7 +208,7 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
                             const unsigned long long cur = *(volatile unsigned long long*)queue;
                             const unsigned long long rem = cur < n_items ? n_items - cur : 0ull;
                             chunk = (rem / guide) & ~31ull;
-                            chunk = chunk < 32ull ? 32ull : (chunk > RT_QUEUE_CHUNK ? RT_QUEUE_CHUNK : chunk);
+                            chunk = chunk < 32ull ? 32ull : (chunk > (unsigned long long)lp.queue_chunk ? (unsigned long long)lp.queue_chunk : chunk);
                         }
                         g = atomicAdd(queue, chunk);
                     }
@@ -510,7 +510,7 @@ cudaError_t launch_trace(const SceneDev& sc, const CameraDev& cam, const LaunchP
     if (e != cudaSuccess) return e;
     const bool tex = sc.c3 != nullptr && sc.n_tex != 0u;       // texture code only when the scene carries handles and a table is bound
     const uint64_t n_items = (uint64_t)lp.n_warp_tiles * (fold ? 1u : lp.n_frames) * 32ull;
-    const uint64_t per_grab = fold ? 32ull : RT_QUEUE_CHUNK;
+    const uint64_t per_grab = fold ? 32ull : (uint64_t)lp.queue_chunk;
     const uint64_t warps_needed = (n_items + per_grab - 1) / per_grab;
     uint64_t blocks = (uint64_t)n_sms * trace_blocks_per_sm(brute, detail, tex, pf, fold, inst);
     const uint64_t cap = (warps_needed + RT_BLOCK_THREADS / 32 - 1) / (RT_BLOCK_THREADS / 32);
@@ -597,7 +597,7 @@ cudaError_t launch_trace_static(const SceneDev& sc, const CameraDev& cam, const 
     if ((e = cudaMemsetAsync(queue, 0, sizeof(unsigned long long), stream)) != cudaSuccess) return e;
     const bool tex = sc.c3 != nullptr && sc.n_tex != 0u;
     const uint64_t n_items = (uint64_t)lp.n_warp_tiles * lp.n_frames * 32ull;
-    const uint64_t warps_needed = (n_items + RT_QUEUE_CHUNK - 1) / RT_QUEUE_CHUNK;
+    const uint64_t warps_needed = (n_items + lp.queue_chunk - 1) / lp.queue_chunk;
     uint64_t blocks = (uint64_t)n_sms * trace_blocks_per_sm(brute, detail, tex, pf, false, inst);
     const uint64_t cap = (warps_needed + RT_BLOCK_THREADS / 32 - 1) / (RT_BLOCK_THREADS / 32);
     if (blocks > cap) blocks = cap;
