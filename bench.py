@@ -62,6 +62,9 @@ def peaks():
         return {"hbm_gbs": 6650.0, "sm_max_mhz": 1965.0}, "fallback"
 
 
+SCHED_DEFAULT = 8 | (1 << 8) | (22 << 16)      # RT_OPT_SCHED: the library's own thresholds (node loop 8 lanes, shade at 22)
+
+
 def ncu_traffic(config):
     """DRAM bytes (read + write) of one trace-kernel launch from the committed `ncu --set full`
     capture of this workload (profiles/trace_kernel_traffic.json), or None when there is none."""
@@ -372,6 +375,16 @@ def run_ours(args, rank, world, local_rank):
             Fg = world // t_groups
             t.set_shard(rank % t_groups, t_groups, rank // t_groups, Fg)
 
+            # the caller's knowledge of its scene: on the teapot, a GPU's share of 49-96 dispatches traces 3 % faster with 128-item queue
+            # grabs (profiles/r2_summary.md, queue policy table); RT_OPT_SCHED bits 24-39 = grab / 32, guide.  Everything else runs on
+            # the library's defaults.
+            per_gpu = n_disp // world                                          # equivalent launch length of a GPU's share (tile shards: a share of the tiles x all dispatches)
+            queue_policy = "default"
+            if config == "c3_teapot" and 48 < per_gpu <= 96:
+                grab, guide = 128, 20
+                t.set_option(rt._lib.RT_OPT_SCHED, SCHED_DEFAULT | ((grab // 32) << 24) | (guide << 32))
+                queue_policy = "grab %d, guide %d" % (grab, guide)
+
             def sharded():
                 t.render_frames(0, n_disp)
                 t.combine(0)
@@ -385,7 +398,8 @@ def run_ours(args, rank, world, local_rank):
             comb = reduce_scalar(a.elapsed_time(b) if rank == 0 else 0.0, MAX)
             res = {"config": config, "dispatches_total": n_disp, "spp_total": 2 * n_disp, "partition": "%d tile group(s) x %d sample group(s)" % (t_groups, Fg),
                    "seed_mode": "wide" if seed_mode else "strict", "ms_n1": ms1, "ms_per_step": msN, "speedup_vs_n1": ms1 / msN, "efficiency": ms1 / msN / world,
-                   "Mrays_s": rays1 / (msN * 1e-3) / 1e6, "Mrays_s_n1": rays1 / (ms1 * 1e-3) / 1e6, "combine_ms": comb}
+                   "Mrays_s": rays1 / (msN * 1e-3) / 1e6, "Mrays_s_n1": rays1 / (ms1 * 1e-3) / 1e6, "combine_ms": comb, "queue_policy": queue_policy}
+            t.set_option(rt._lib.RT_OPT_SCHED, SCHED_DEFAULT)
             if check_tile:                                                      # outside every timed region
                 same = True
                 if rank == 0:

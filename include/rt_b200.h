@@ -132,7 +132,7 @@ enum {
     RT_OPT_DETAIL_COUNTERS = 4,  /* 1 = count node visits / primitive tests (slower kernel) */
     RT_OPT_FRAMES_PER_LAUNCH = 5,/* max reference dispatches fused into one kernel launch (0 = default: 128, or 4096 with RT_OPT_ITEM_MODE = 2; 1 = one launch per dispatch like the reference) */
     RT_OPT_LEAF_SIZE = 6,        /* max primitives per BVH leaf (1..8; 0 = default: 2 up to 262,144 primitives, 1 above); takes effect at the next rt_upload_scene */
-    RT_OPT_SCHED = 7,            /* tuning: warp scheduler thresholds in lanes, node_loop_min | (shade_min << 16); bits 24-31: work items per queue grab / 32, bits 32-39: guide of the guided self-scheduling (0 = defaults: 256 items, guide 20, 40 for launches of at most 16 dispatches); results do not depend on it */
+    RT_OPT_SCHED = 7,            /* tuning: warp scheduler thresholds in lanes, node_loop_min | (shade_min << 16); bits 24-31: work items per queue grab / 32, bits 32-39: guide of the guided self-scheduling (0 = defaults: 256 items, guide 40, or 20 for scenes of fewer than 2,048 primitives); results do not depend on it */
     RT_OPT_BUILDER = 8,          /* hierarchy over the Morton order: 0 = PLOC (default), 1 = radix tree (Karras 2012); takes effect at the next rt_upload_scene; results do not depend on it */
     RT_OPT_PLOC_RADIUS = 9,      /* PLOC search window, clusters to either side (1..16; 0 = default: 3 up to 262,144 primitives, 2 above) */
     RT_OPT_KERNEL = 10,          /* 0 = persistent megakernel (default), 1 = wavefront kernels over a path-slot pool; results do not depend on it */

@@ -199,7 +199,11 @@ int launch(rt_ctx* c, int32_t first_frame, uint32_t n_frames, bool want_ids, int
     const uint32_t tiles = lp.tiles_x * ((c->height + 7) / 8);
     lp.n_warp_tiles = 2u * (tiles > c->tile_rank ? (tiles - c->tile_rank + c->tile_world - 1) / c->tile_world : 0);
     lp.seed_mode = (int32_t)c->opt_seed_mode;
-    lp.queue_guide = (uint32_t)(n_frames <= 16u ? 2ull * RT_QUEUE_GUIDE : RT_QUEUE_GUIDE);
+    // Guide of the item queue (grab = remaining / (warps x guide)): scenes with real geometry end their launches on finer grabs — their
+    // items are long enough to hide a grab's round trip and differ enough in cost for the last grabs to matter (C3 x 32: 18.5 instead of
+    // 21.7 ms, x 16 -14 %, x 8 -6 %, x 128 +0.2 %; C4 x 8 -2.4 %, x 32 +0.2 %); a handful of primitives (C2: 429, x 32 +3 %, x 16 +8 % with
+    // the finer guide) keeps the coarse one.  scripts/queue_sweep.py, profiles/r2_summary.md.
+    lp.queue_guide = (uint32_t)(c->scene.n_prims >= 2048u ? 2ull * RT_QUEUE_GUIDE : RT_QUEUE_GUIDE);
     lp.queue_chunk = (uint32_t)RT_QUEUE_CHUNK;
     if ((c->opt_sched >> 24) & 0xff) lp.queue_chunk = 32u * (uint32_t)((c->opt_sched >> 24) & 0xff);      // tuning: RT_OPT_SCHED bits 24-31 = grab size / 32, bits 32-39 = guide
     if ((c->opt_sched >> 32) & 0xff) lp.queue_guide = (uint32_t)((c->opt_sched >> 32) & 0xff);
@@ -595,7 +599,11 @@ int rt_render_frames_static(rt_ctx* c, int32_t first_frame, uint32_t n_frames)
     const uint32_t tiles = lp.tiles_x * ((c->height + 7) / 8);
     lp.n_warp_tiles = 2u * (tiles > c->tile_rank ? (tiles - c->tile_rank + c->tile_world - 1) / c->tile_world : 0);
     lp.seed_mode = (int32_t)c->opt_seed_mode;
-    lp.queue_guide = (uint32_t)(n_frames <= 16u ? 2ull * RT_QUEUE_GUIDE : RT_QUEUE_GUIDE);
+    // Guide of the item queue (grab = remaining / (warps x guide)): scenes with real geometry end their launches on finer grabs — their
+    // items are long enough to hide a grab's round trip and differ enough in cost for the last grabs to matter (C3 x 32: 18.5 instead of
+    // 21.7 ms, x 16 -14 %, x 8 -6 %, x 128 +0.2 %; C4 x 8 -2.4 %, x 32 +0.2 %); a handful of primitives (C2: 429, x 32 +3 %, x 16 +8 % with
+    // the finer guide) keeps the coarse one.  scripts/queue_sweep.py, profiles/r2_summary.md.
+    lp.queue_guide = (uint32_t)(c->scene.n_prims >= 2048u ? 2ull * RT_QUEUE_GUIDE : RT_QUEUE_GUIDE);
     lp.queue_chunk = (uint32_t)RT_QUEUE_CHUNK;
     if ((c->opt_sched >> 24) & 0xff) lp.queue_chunk = 32u * (uint32_t)((c->opt_sched >> 24) & 0xff);      // tuning: RT_OPT_SCHED bits 24-31 = grab size / 32, bits 32-39 = guide
     if ((c->opt_sched >> 32) & 0xff) lp.queue_guide = (uint32_t)((c->opt_sched >> 32) & 0xff);

@@ -37,8 +37,8 @@ namespace rt {
                                   // Fewer tiles in flight per SM = warmer L1: 256 against 128 C3 +1.9 %, C4 +2.6 %, C2 +5.5 %, C5 +0.2 %; 512 C3 -5 %; 32 C3 -9 %
 #endif
 #ifndef RT_QUEUE_GUIDE
-#define RT_QUEUE_GUIDE 20ull      // grab size = remaining items / (warps x this), clamped to [32, RT_QUEUE_CHUNK]; launches of <= 16 dispatches use
-                                  // twice this (LaunchParams.queue_guide): C3 x 16 dispatches 9.97 ms against 10.70, while 32-dispatch launches of C2 / C4 lose 1-5 % with it
+#define RT_QUEUE_GUIDE 20ull      // grab size = remaining items / (warps x this), clamped to [32, RT_QUEUE_CHUNK]; scenes of at least 2,048 primitives
+                                  // use twice this (rt_api.cu: LaunchParams.queue_guide)
 #endif
 
 // trace (persistent warps over the item queue).  fold = true: items are pixels, the kernel applies the running mean

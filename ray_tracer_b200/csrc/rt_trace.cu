@@ -205,7 +205,13 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
                     unsigned long long g = 0, chunk = 32ull;                    // FOLD: one 8x4 tile (32 pixels x all dispatches) per grab
                     if (lane == 0) {
                         if (!FOLD) {
+#ifdef RT_QUEUE_READ
                             const unsigned long long cur = *(volatile unsigned long long*)queue;
+#else
+                            // the queue head as of this warp's previous grab: stale by what the other warps took since (at most a few percent of a
+                            // launch), which the guide does not mind — and one L2 round trip per grab less than reading the head first
+                            const unsigned long long cur = pool_end;
+#endif
                             const unsigned long long rem = cur < n_items ? n_items - cur : 0ull;
                             chunk = (rem / guide) & ~31ull;
                             chunk = chunk < 32ull ? 32ull : (chunk > (unsigned long long)lp.queue_chunk ? (unsigned long long)lp.queue_chunk : chunk);
