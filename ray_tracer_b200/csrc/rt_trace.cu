@@ -30,6 +30,17 @@ static __device__ __align__(256) unsigned char g_static_scratch[256 + RT_STATIC_
 
 namespace rt {
 
+#ifdef RT_TIME_PROBE
+// tuning builds only: when every warp of the last launch started its last SHADE pass and when it left the kernel (globaltimer, ns)
+__device__ unsigned long long g_warp_times[2 * 8192];
+extern "C" int rt_debug_warp_times(unsigned long long* out, int n)
+{
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e == cudaSuccess) e = cudaMemcpyFromSymbol(out, g_warp_times, (size_t)n * 2 * sizeof(unsigned long long));
+    return e == cudaSuccess ? 0 : -1;
+}
+__device__ __forceinline__ unsigned long long probe_now() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+#endif
 #ifdef RT_LANE_STATS
 // tuning builds only (scripts/build_variant.sh stats "-DRT_LANE_STATS"): where the lanes of a warp are while it runs
 // the node loop / leaf loop / SHADE, summed over the launch; read with rt_debug_lane_stats (not part of the ABI).
@@ -115,6 +126,9 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
 
     uint64_t pool_next = 0, pool_end = 0;          // warp-uniform: items granted to this warp (kept in registers: in shared memory C3 -4.6 %)
     bool exhausted = false;                        // warp-uniform: the global queue is empty
+#ifdef RT_TIME_PROBE
+    unsigned long long t_exhausted = 0;
+#endif
 
     // ---- per-lane state ---------------------------------------------------------------
     bool shading = true;                           // lane is between rays (else: mid-traversal)
@@ -219,6 +233,9 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
                         g = atomicAdd(queue, chunk);
                     }
                     g = __shfl_sync(0xffffffffu, g, 0); chunk = __shfl_sync(0xffffffffu, chunk, 0);
+#ifdef RT_TIME_PROBE
+                    if (g >= n_items && !exhausted) t_exhausted = probe_now();
+#endif
                     if (g >= n_items) { exhausted = true; break; }
                     pool_next = g; pool_end = (g + chunk < n_items) ? g + chunk : n_items;
                 }
@@ -412,6 +429,9 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
         }
     }
 
+#ifdef RT_TIME_PROBE
+    if (lane == 0) { const uint32_t w = blockIdx.x * (RT_BLOCK_THREADS / 32) + (threadIdx.x >> 5); if (w < 8192u) { g_warp_times[2 * w] = t_exhausted; g_warp_times[2 * w + 1] = probe_now(); } }
+#endif
     // counters: one atomic per warp
     unsigned long long r = n_rays, s = n_samples, nn = n_nodes, nt = n_tri, ns = n_sph, nh = n_hits;
     for (int o = 16; o > 0; o >>= 1) {
