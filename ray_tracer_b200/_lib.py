@@ -54,6 +54,7 @@ RT_OPT_TRAVERSAL, RT_OPT_SEED_MODE, RT_OPT_PRIMARY_IDS, RT_OPT_DETAIL_COUNTERS =
 RT_OPT_FRAMES_PER_LAUNCH, RT_OPT_LEAF_SIZE, RT_OPT_SCHED = 5, 6, 7
 RT_OPT_BUILDER, RT_OPT_PLOC_RADIUS, RT_OPT_KERNEL, RT_OPT_WAVE_SLOTS, RT_OPT_STAGING_MIB = 8, 9, 10, 11, 12
 RT_OPT_ITEM_MODE, RT_OPT_INSTANCING, RT_OPT_PIPELINE, RT_OPT_NODE_FORMAT, RT_OPT_NODES_PACKED = 13, 14, 15, 16, 17
+RT_OPT_TILE_ORDER = 18
 RT_OK, RT_ERR_INVALID_ARGUMENT, RT_ERR_CUDA, RT_ERR_NO_SCENE = 0, -1, -2, -3
 RT_ERR_OUT_OF_MEMORY, RT_ERR_BAD_INDEX, RT_ERR_UNSUPPORTED = -4, -5, -6
 MISS = 0xFFFFFFFF

@@ -98,6 +98,10 @@ struct LaunchParams {
     int32_t sched_n_stay, sched_l_stay, sched_s_min;   // warp scheduler thresholds (lanes)
     FastDiv div_frames, div_tiles_x, div_width;         // item decode without integer divisions
     float rpp_scale;                                    // 1/rpp when rpp is a power of two (x/2^k == x*2^-k exactly), else 0
+    // heaviest tiles first (rt_api.cu: tile order): the order in which this rank's 8x8 tiles enter the queue (local tile index -> local tile
+    // index; null: raster order) and where the launch's first dispatch leaves every tile's segment count for the next order (or null)
+    const uint32_t* tile_order;
+    uint32_t* tile_cost;
 };
 
 // 256-bit read-only load (sm_100: LDG.E.256): two float4 from a 32-byte-aligned address in one

@@ -131,6 +131,22 @@ cudaError_t launch_wave(const SceneDev& sc, const CameraDev& cam, const LaunchPa
                         uint32_t* primary_ids, unsigned long long* counters, bool brute, bool detail, int n_sms, cudaStream_t stream);
 cudaError_t launch_blend(const LaunchParams& lp, const float4* staging, float4* accum, cudaStream_t stream);
 
+// Heaviest tiles first (rt_order.cu): per-tile weights collected by the trace kernel, sorted into the next call's tile order.
+struct TileOrder {
+    uint32_t *cost = nullptr, *order[2] = {nullptr, nullptr}, *keys = nullptr, *keys_out = nullptr, *vals = nullptr, *stats = nullptr;
+    void* tmp = nullptr; size_t tmp_bytes = 0;
+    uint32_t n = 0; uint64_t geom = 0; int cur = 0; bool valid = false;
+    bool fed = false;                                   // a launch since the last update collected weights
+    uint32_t* h_flat = nullptr; cudaEvent_t ev_flat = nullptr; bool flat_pending = false;
+    bool disabled = false;                              // the weights turned out flat: raster order, nothing collected (until rearm())
+    void poll();
+    void rearm() { disabled = false; }
+    cudaError_t ensure(uint32_t n_local, uint64_t geometry, cudaStream_t stream);   // (re)allocates for this rank's tile list; a new geometry starts in raster order
+    cudaError_t update(cudaStream_t stream);
+    void release();
+    const uint32_t* current() const { return valid ? order[cur] : nullptr; }
+};
+
 cudaError_t launch_tonemap(const float4* accum, uint8_t* rgba8, size_t n_pixels, cudaStream_t stream);
 
 // ---- multi-GPU image combine over peer memory (rt_combine.cu) -----------------------------------

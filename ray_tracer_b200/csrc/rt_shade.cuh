@@ -126,6 +126,7 @@ __device__ __forceinline__ uint32_t pixel_seed(uint32_t x, uint32_t y, uint32_t 
 // Work item g -> (pixel, dispatch): items are numbered tile-major, dispatch-minor, 32 pixels (an 8x4
 // warp tile) at a time; shard tile t belongs to rank t % tile_world.  False when the pixel lies
 // outside the image (the tile grid is rounded up).
+template <bool ORD>
 __device__ __forceinline__ bool decode_item(const LaunchParams& lp, uint64_t g, uint32_t& px, uint32_t& py, uint32_t& fi)
 {
     const uint32_t pos = (uint32_t)(g & 31ull);
@@ -133,22 +134,32 @@ __device__ __forceinline__ bool decode_item(const LaunchParams& lp, uint64_t g, 
     uint32_t wt;
     if ((tf >> 32) == 0ull) { wt = lp.div_frames.div((uint32_t)tf); fi = (uint32_t)tf - wt * lp.n_frames; }
     else { fi = (uint32_t)(tf % lp.n_frames); wt = (uint32_t)(tf / lp.n_frames); }
-    const uint32_t t = (wt >> 1) * lp.tile_world + lp.tile_rank;
+    const uint32_t lt = (ORD && lp.tile_order) ? __ldg(lp.tile_order + (wt >> 1)) : (wt >> 1);
+    const uint32_t t = lt * lp.tile_world + lp.tile_rank;
     const uint32_t ty = lp.div_tiles_x.div(t), tx = t - ty * lp.tiles_x;
     px = tx * 8u + (pos & 7u);
     py = ty * 8u + (wt & 1u) * 4u + (pos >> 3);
     return px < lp.width && py < lp.height;
 }
 // FOLD items: work item g -> pixel (one item per pixel of this rank's tiles, all fused dispatches), same tile numbering.
+template <bool ORD>
 __device__ __forceinline__ bool decode_pixel(const LaunchParams& lp, uint64_t g, uint32_t& px, uint32_t& py)
 {
     const uint32_t pos = (uint32_t)(g & 31ull);
     const uint32_t wt = (uint32_t)(g >> 5);
-    const uint32_t t = (wt >> 1) * lp.tile_world + lp.tile_rank;
+    const uint32_t lt = (ORD && lp.tile_order) ? __ldg(lp.tile_order + (wt >> 1)) : (wt >> 1);
+    const uint32_t t = lt * lp.tile_world + lp.tile_rank;
     const uint32_t ty = lp.div_tiles_x.div(t), tx = t - ty * lp.tiles_x;
     px = tx * 8u + (pos & 7u);
     py = ty * 8u + (wt & 1u) * 4u + (pos >> 3);
     return px < lp.width && py < lp.height;
+}
+// local index (in this rank's list) of the 8x8 tile a pixel lies in
+__device__ __forceinline__ uint32_t local_tile_of(const LaunchParams& lp, uint32_t pix)
+{
+    const uint32_t py = lp.div_width.div(pix), px = pix - py * lp.width;
+    const uint32_t t = (py >> 3) * lp.tiles_x + (px >> 3);
+    return (t - lp.tile_rank) / lp.tile_world;
 }
 // wgsl:326 `pixel_color / f32(rpp)`: an exact power-of-two scale when it can be, else the IEEE division
 __device__ __forceinline__ float4 frag_of_total(const LaunchParams& lp, float4 total)

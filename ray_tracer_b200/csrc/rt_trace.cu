@@ -105,7 +105,7 @@ __device__ __forceinline__ void fold_store(const LaunchParams& lp, float4* accum
 // into the range's own nodes.  Leaves there hold RAW vertex triples: the test forms A = a + pos, B, C, the edges and their cross
 // product per instance with the reference's own operations (wgsl:172-174,127-129), so the result is that of the flattened record
 // bit for bit.  Popping RT_MARKER with no leaf pending restores the world-space constants.
-template <bool BRUTE, bool DETAIL, bool TEX, bool PF, bool FOLD, bool INST>
+template <bool BRUTE, bool DETAIL, bool TEX, bool PF, bool FOLD, bool INST, bool ORD>
 __global__ void __launch_bounds__(RT_BLOCK_THREADS, RT_MIN_BLOCKS)
 trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ staging, float4* accum,
              uint32_t* __restrict__ primary_ids, unsigned long long* __restrict__ counters,
@@ -188,7 +188,11 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
                         if (lp.toggle != 0) incoming = incoming + environment_light(rd) * color;  // wgsl:274-279
                         done = true;
                     }
-                    if (done) { total = total + incoming; j++; need_path = true; }                   // wgsl:323
+                    if (done) {                                                                    // wgsl:323
+                        total = total + incoming; j++; need_path = true;
+                        // this tile's weight in the next call's order: the segments of the first dispatch's paths, every 4th pixel
+                        if (ORD && lp.tile_cost != nullptr && fi == 0u && (pix & 3u) == 0u) atomicAdd(lp.tile_cost + local_tile_of(lp, pix), (uint32_t)seg + 1u);
+                    }
                 } else {
                     need_path = true;                                                              // fresh item
                 }
@@ -245,8 +249,8 @@ trace_kernel(SceneDev sc, CameraDev cam, LaunchParams lp, float4* __restrict__ s
                 if (mine && rank < avail) {
                     uint32_t px, py;
                     bool inside;
-                    if (FOLD) { inside = decode_pixel(lp, pool_next + rank, px, py); fi = 0; }
-                    else inside = decode_item(lp, pool_next + rank, px, py, fi);
+                    if (FOLD) { inside = decode_pixel<ORD>(lp, pool_next + rank, px, py); fi = 0; }
+                    else inside = decode_item<ORD>(lp, pool_next + rank, px, py, fi);
                     if (inside) {                                                // else: outside the image, ask again
                         pix = py * lp.width + px;
                         rng = pixel_seed(px, py, lp.width, lp.height, lp.first_frame + (int32_t)(fi * lp.frame_world), lp.seed_mode);
@@ -493,30 +497,33 @@ typedef void (*TraceFn)(SceneDev, CameraDev, LaunchParams, float4*, float4*, uin
 // PF: prefetch the postponed child of a two-hit node step into L1.  Pays while the hierarchy and the records fit the
 // caches (C3 +0.8 %, C4 +1.8 %, C2 +0.4 %); on C5 (1.1 M primitives, 140 MB of nodes + records, L1 data pipe at 85 %)
 // the extra requests cost 1.5 %, so the launcher picks the variant by scene size.
-template <bool FOLD>
+template <bool FOLD, bool ORD>
 TraceFn trace_variant_t(bool brute, bool detail, bool tex, bool pf, bool inst)
 {
     static const TraceFn table[12] = {
-        trace_kernel<false, false, false, false, FOLD, false>, trace_kernel<false, false, true, false, FOLD, false>, trace_kernel<false, true, false, false, FOLD, false>, trace_kernel<false, true, true, false, FOLD, false>,
-        trace_kernel<false, false, false, true, FOLD, false>,  trace_kernel<false, false, true, true, FOLD, false>,  trace_kernel<false, true, false, true, FOLD, false>,  trace_kernel<false, true, true, true, FOLD, false>,
-        trace_kernel<true, false, false, false, FOLD, false>,  trace_kernel<true, false, true, false, FOLD, false>,  trace_kernel<true, true, false, false, FOLD, false>,  trace_kernel<true, true, true, false, FOLD, false>};
+        trace_kernel<false, false, false, false, FOLD, false, ORD>, trace_kernel<false, false, true, false, FOLD, false, ORD>, trace_kernel<false, true, false, false, FOLD, false, ORD>, trace_kernel<false, true, true, false, FOLD, false, ORD>,
+        trace_kernel<false, false, false, true, FOLD, false, ORD>,  trace_kernel<false, false, true, true, FOLD, false, ORD>,  trace_kernel<false, true, false, true, FOLD, false, ORD>,  trace_kernel<false, true, true, true, FOLD, false, ORD>,
+        trace_kernel<true, false, false, false, FOLD, false, ORD>,  trace_kernel<true, false, true, false, FOLD, false, ORD>,  trace_kernel<true, true, false, false, FOLD, false, ORD>,  trace_kernel<true, true, true, false, FOLD, false, ORD>};
     // instanced scenes: hierarchy traversal only (the exhaustive scan needs flattened records), no push-time prefetch
     static const TraceFn inst_table[4] = {
-        trace_kernel<false, false, false, false, FOLD, true>, trace_kernel<false, false, true, false, FOLD, true>,
-        trace_kernel<false, true, false, false, FOLD, true>,  trace_kernel<false, true, true, false, FOLD, true>};
+        trace_kernel<false, false, false, false, FOLD, true, ORD>, trace_kernel<false, false, true, false, FOLD, true, ORD>,
+        trace_kernel<false, true, false, false, FOLD, true, ORD>,  trace_kernel<false, true, true, false, FOLD, true, ORD>};
     if (inst) return inst_table[(detail ? 2 : 0) | (tex ? 1 : 0)];
     return table[(brute ? 8 : (pf ? 4 : 0)) | (detail ? 2 : 0) | (tex ? 1 : 0)];
 }
-TraceFn trace_variant(bool brute, bool detail, bool tex, bool pf, bool fold, bool inst)
+// ord: the variants that hand tiles out in the learned order and collect the next one's weights (rt_order.cu) — short launches only,
+// so that the long ones run the very code they ran without it (compiled into one kernel it cost C3 x 128 0.4 % and C4 x 32 1.4 %)
+TraceFn trace_variant(bool brute, bool detail, bool tex, bool pf, bool fold, bool inst, bool ord)
 {
-    return fold ? trace_variant_t<true>(brute, detail, tex, pf, inst) : trace_variant_t<false>(brute, detail, tex, pf, inst);
+    if (ord) return fold ? trace_variant_t<true, true>(brute, detail, tex, pf, inst) : trace_variant_t<false, true>(brute, detail, tex, pf, inst);
+    return fold ? trace_variant_t<true, false>(brute, detail, tex, pf, inst) : trace_variant_t<false, false>(brute, detail, tex, pf, inst);
 }
 } // namespace
 
-int trace_blocks_per_sm(bool brute, bool detail, bool tex, bool pf, bool fold, bool inst)
+int trace_blocks_per_sm(bool brute, bool detail, bool tex, bool pf, bool fold, bool inst, bool ord)
 {
     int n = 0;
-    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, trace_variant(brute, detail, tex, pf, fold, inst), RT_BLOCK_THREADS, 0);
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, trace_variant(brute, detail, tex, pf, fold, inst, ord), RT_BLOCK_THREADS, 0);
     return (e == cudaSuccess && n > 0) ? n : 1;
 }
 
@@ -538,11 +545,12 @@ cudaError_t launch_trace(const SceneDev& sc, const CameraDev& cam, const LaunchP
     const uint64_t n_items = (uint64_t)lp.n_warp_tiles * (fold ? 1u : lp.n_frames) * 32ull;
     const uint64_t per_grab = fold ? 32ull : (uint64_t)lp.queue_chunk;
     const uint64_t warps_needed = (n_items + per_grab - 1) / per_grab;
-    uint64_t blocks = (uint64_t)n_sms * trace_blocks_per_sm(brute, detail, tex, pf, fold, inst);
+    const bool ord = lp.tile_order != nullptr || lp.tile_cost != nullptr;
+    uint64_t blocks = (uint64_t)n_sms * trace_blocks_per_sm(brute, detail, tex, pf, fold, inst, ord);
     const uint64_t cap = (warps_needed + RT_BLOCK_THREADS / 32 - 1) / (RT_BLOCK_THREADS / 32);
     if (blocks > cap) blocks = cap;
     dim3 grid((unsigned)blocks), block(RT_BLOCK_THREADS);
-    trace_variant(brute, detail, tex, pf, fold, inst)<<<grid, block, 0, stream>>>(sc, cam, lp, staging, accum, primary_ids, counters, queue);
+    trace_variant(brute, detail, tex, pf, fold, inst, ord)<<<grid, block, 0, stream>>>(sc, cam, lp, staging, accum, primary_ids, counters, queue);
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
     return (fold || !with_blend) ? cudaSuccess : launch_blend(lp, staging, accum, stream);
 }
@@ -624,10 +632,10 @@ cudaError_t launch_trace_static(const SceneDev& sc, const CameraDev& cam, const 
     const bool tex = sc.c3 != nullptr && sc.n_tex != 0u;
     const uint64_t n_items = (uint64_t)lp.n_warp_tiles * lp.n_frames * 32ull;
     const uint64_t warps_needed = (n_items + lp.queue_chunk - 1) / lp.queue_chunk;
-    uint64_t blocks = (uint64_t)n_sms * trace_blocks_per_sm(brute, detail, tex, pf, false, inst);
+    uint64_t blocks = (uint64_t)n_sms * trace_blocks_per_sm(brute, detail, tex, pf, false, inst, false);
     const uint64_t cap = (warps_needed + RT_BLOCK_THREADS / 32 - 1) / (RT_BLOCK_THREADS / 32);
     if (blocks > cap) blocks = cap;
-    trace_variant(brute, detail, tex, pf, false, inst)<<<dim3((unsigned)blocks), dim3(RT_BLOCK_THREADS), 0, stream>>>(sc, cam, lp, staging, accum, primary_ids, counters, queue);
+    trace_variant(brute, detail, tex, pf, false, inst, false)<<<dim3((unsigned)blocks), dim3(RT_BLOCK_THREADS), 0, stream>>>(sc, cam, lp, staging, accum, primary_ids, counters, queue);
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
     return launch_blend(lp, staging, accum, stream);
 }

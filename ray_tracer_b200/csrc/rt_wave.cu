@@ -327,7 +327,7 @@ wave_miss(CameraDev cam, WaveDev wv, LaunchParams lp, float4* __restrict__ stagi
                 if (g >= n_items) need_ray = false;                                        // no work left: the slot dies
                 else {
                     uint32_t px, py;
-                    if (decode_item(lp, g, px, py, fi)) {                                  // else: outside the image, ask again
+                    if (decode_item<false>(lp, g, px, py, fi)) {                                  // else: outside the image, ask again
                         pix = py * lp.width + px;
                         rng = pixel_seed(px, py, lp.width, lp.height, lp.first_frame + (int32_t)(fi * lp.frame_world), lp.seed_mode);
                         j = 0; has_item = true;

@@ -40,7 +40,7 @@ const _: () = {
 };
 
 pub mod opt { pub const TRAVERSAL: i32 = 1; pub const SEED_MODE: i32 = 2; pub const PRIMARY_IDS: i32 = 3; pub const DETAIL_COUNTERS: i32 = 4;
-              pub const FRAMES_PER_LAUNCH: i32 = 5; pub const LEAF_SIZE: i32 = 6; pub const SCHED: i32 = 7; pub const BUILDER: i32 = 8; pub const PLOC_RADIUS: i32 = 9; pub const KERNEL: i32 = 10; pub const WAVE_SLOTS: i32 = 11; pub const STAGING_MIB: i32 = 12; pub const ITEM_MODE: i32 = 13; pub const INSTANCING: i32 = 14; pub const PIPELINE: i32 = 15; pub const NODE_FORMAT: i32 = 16; pub const NODES_PACKED: i32 = 17; }
+              pub const FRAMES_PER_LAUNCH: i32 = 5; pub const LEAF_SIZE: i32 = 6; pub const SCHED: i32 = 7; pub const BUILDER: i32 = 8; pub const PLOC_RADIUS: i32 = 9; pub const KERNEL: i32 = 10; pub const WAVE_SLOTS: i32 = 11; pub const STAGING_MIB: i32 = 12; pub const ITEM_MODE: i32 = 13; pub const INSTANCING: i32 = 14; pub const PIPELINE: i32 = 15; pub const NODE_FORMAT: i32 = 16; pub const NODES_PACKED: i32 = 17; pub const TILE_ORDER: i32 = 18; }
 
 #[repr(C)] pub struct RtCtx { _private: [u8; 0] }
 

@@ -1,43 +1,31 @@
-"""Find pixels whose value depends on the traversal schedule: re-render the same scene (same hierarchy) until two
-images differ, then compare both with exhaustive brute force on the tiles involved.
-  python scripts/order_probe.py c5_stress 2 [builder] [tries]"""
-import sys
-import numpy as np
+"""RT_OPT_TILE_ORDER (heaviest tiles of the previous call first) on / off against launch length:
+python scripts/order_probe.py c3_teapot "128,64,32,16,8,4,2,1" ["chunk,guide;..."]   -> ms per dispatch, image CRCs must agree"""
+import sys, zlib
 sys.path.insert(0, ".")
 import ray_tracer_b200 as rt
 from ray_tracer_b200 import configs
-name, frames = sys.argv[1], int(sys.argv[2])
-builder = int(sys.argv[3]) if len(sys.argv) > 3 else 1
-tries = int(sys.argv[4]) if len(sys.argv) > 4 else 20
+name = sys.argv[1]
+lengths = [int(x) for x in sys.argv[2].split(",")]
+combos = [tuple(int(v) for v in c.split(",")) for c in (sys.argv[3] if len(sys.argv) > 3 else "0,0").split(";")]
 scene, meta = configs.build(name)
 p = meta["params"]
-w, h = p["width"], p["height"]
-tr = rt.RayTracer(0, w, h)
-tr.set_option(rt._lib.RT_OPT_BUILDER, builder)
-tr.upload_scene(*scene.arrays()); tr.upload_textures(scene.textures); tr.set_camera(scene.camera_uniform()); tr.set_params(**p)
-tr.set_option(rt._lib.RT_OPT_FRAMES_PER_LAUNCH, frames)
-imgs = []
-for i in range(tries):
-    tr.clear(); tr.render_frames(0, frames); tr.sync()
-    img = tr.read_accum()
-    if not any(np.array_equal(img.view(np.uint32), o.view(np.uint32)) for o in imgs):
-        imgs.append(img)
-print("distinct images in %d renders of one hierarchy: %d" % (tries, len(imgs)), flush=True)
-if len(imgs) < 2:
-    sys.exit(0)
-diff = np.zeros((h, w), bool)
-for o in imgs[1:]:
-    diff |= np.any(o.view(np.uint32) != imgs[0].view(np.uint32), axis=2)
-ys, xs = np.nonzero(diff)
-print("pixels involved:", [(int(x), int(y)) for y, x in zip(ys, xs)], flush=True)
-tiles_x = (w + 7) // 8
-n_tiles = tiles_x * ((h + 7) // 8)
-tr.set_option(rt._lib.RT_OPT_TRAVERSAL, 1)
-for y, x in zip(ys, xs):
-    t = (y // 8) * tiles_x + (x // 8)
-    tr.clear(); tr.set_shard(t, n_tiles, 0, 1)
-    tr.render_frames(0, frames); tr.sync()
-    ref = tr.read_accum()[y, x]
-    print("pixel (%d,%d): brute force %s" % (x, y, ref.view(np.uint32)), flush=True)
-    for k, o in enumerate(imgs):
-        print("   image %d %s %s" % (k, o[y, x].view(np.uint32), "== brute force" if np.array_equal(o[y, x].view(np.uint32), ref.view(np.uint32)) else "DIFFERS"), flush=True)
+base = 8 | (1 << 8) | (22 << 16)
+print("%-22s" % "order chunk,guide", *["%9d" % n for n in lengths], " (ms per dispatch)")
+for order in (0, 1):
+    for chunk, guide in combos:
+        tr = rt.RayTracer(0, p["width"], p["height"])
+        tr.set_option(rt._lib.RT_OPT_TILE_ORDER, order)
+        tr.upload_scene(*scene.arrays()); tr.upload_textures(scene.textures); tr.set_camera(scene.camera_uniform()); tr.set_params(**p)
+        tr.set_option(rt._lib.RT_OPT_STAGING_MIB, 8192)
+        tr.set_option(rt._lib.RT_OPT_SCHED, base | ((chunk // 32) << 24) | (guide << 32))
+        row = []; crcs = []
+        for n in lengths:
+            tr.set_option(rt._lib.RT_OPT_FRAMES_PER_LAUNCH, n)
+            best = 1e9
+            for rep in range(4):
+                tr.clear(); tr.reset_counters(); tr.render_frames(0, n); tr.sync()
+                if rep:
+                    best = min(best, tr.counters()["kernel_ms"])
+            row.append(best / n); crcs.append(zlib.crc32(tr.read_accum().tobytes()))
+        print("%-22s" % ("%d     %d,%d" % (order, chunk, guide)), *["%9.4f" % v for v in row], " crc", "%08x" % (zlib.crc32(str(crcs).encode())), flush=True)
+        tr.close()

@@ -182,3 +182,43 @@ def test_pipelined_launches_are_result_invisible(rtlib):
         assert_bits_equal(out[k][0], out[0][0], "pipelined / serial launches")
     assert out[3][1]["rays"] == out[4][1]["rays"]
     assert_bits_equal(out[3][0], out[4][0], "pipelined launches under tile + sample sharding")
+
+
+def test_learned_tile_order_is_result_invisible(rtlib):
+    """RT_OPT_TILE_ORDER: from the second render call on the tiles that were heaviest in the previous call enter the queue first.
+    Same image, counters and primary ids as raster order: over several calls, launch lengths, tile + sample shards, pipelined
+    launches, single dispatches and a resize."""
+    L = rtlib._lib
+    out = {}
+    for order in (0, 1):
+        w, h = 200, 136
+        scene = _config("c3_teapot", w, h)
+        cam, sp, vs, ix, ms = scene
+        tr = rtlib.RayTracer(0, w, h)
+        tr.set_option(L.RT_OPT_TILE_ORDER, order); tr.set_option(L.RT_OPT_PRIMARY_IDS, 1)
+        tr.upload_scene(sp, vs, ix, ms); tr.set_camera(cam.view(rtlib.CAMERA_DT))
+        tr.set_params(number_of_bounces=4, rays_per_pixel=1, skybox=1, frames=0)
+        res = []
+        f = 0
+        for n in (1, 3, 1, 20, 2):                                   # calls of different lengths resume the running mean
+            tr.render_frames(f, n); f += n
+            res.append(tr.read_accum())
+        res.append(tr.read_primary_ids())
+        tr.set_params(number_of_bounces=4, rays_per_pixel=1, skybox=1, frames=f)
+        tr.dispatch(); res.append(tr.read_accum())                   # the reference's own single dispatch
+        tr.set_shard(1, 3, 1, 2)                                     # another tile list: the order starts over
+        tr.render_frames(0, 6); tr.render_frames(6, 6); res.append(tr.read_accum())
+        tr.set_shard(0, 1, 0, 1)
+        tr.set_option(L.RT_OPT_STAGING_MIB, 16); tr.render_frames(0, 60); tr.render_frames(60, 50); tr.render_frames(0, 40); tr.render_frames(40, 40); res.append(tr.read_accum())    # several (pipelined) launches per call
+        res.append(tr.counters()["rays"])
+        tr.update_bind_group(96, 72)                                 # resize
+        scene2 = _config("c3_teapot", 96, 72)
+        tr.set_camera(scene2[0].view(rtlib.CAMERA_DT)); tr.set_params(number_of_bounces=4, rays_per_pixel=1, skybox=1, frames=0, width=96, height=72)
+        tr.render_frames(0, 2); tr.render_frames(2, 2); res.append(tr.read_accum())
+        tr.close()
+        out[order] = res
+    for k, (a, b) in enumerate(zip(out[0], out[1])):
+        if isinstance(a, np.ndarray) and a.dtype == np.float32:
+            assert_bits_equal(b, a, "tile order, step %d" % k)
+        else:
+            assert np.array_equal(a, b), k
