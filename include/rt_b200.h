@@ -141,7 +141,7 @@ enum {
     RT_OPT_INSTANCING = 14,      /* Mesh records that alias one (first, triangles, offset) range (at least two records, 32 triangles, no texture handles) can share ONE object-space hierarchy and appear as proxies in a top-level hierarchy (two-level BVH) instead of being flattened; the triangle test then adds the record's pos per instance with the reference's own operations (wgsl:172-174), so results do not depend on it.  1: instance every eligible range (64x less scene memory on C5, rt_update_records of an instance = a top-level refit; measured 16 % slower than flattened records there); 0: flatten every record; 2 (default): instance only when flattening would exceed 8 M triangles.  Takes effect at the next rt_upload_scene; the exhaustive scan (RT_OPT_TRAVERSAL = 1) and the wavefront kernels (RT_OPT_KERNEL = 1) always flatten and must be selected before the upload of such a scene */
     RT_OPT_NODE_FORMAT = 16,     /* hierarchy nodes of flat (non-instanced) scenes: 0 (default) = by size: 64-byte float nodes up to 262,144 primitives, packed 32-byte nodes (box centres on a 16-bit grid, half extents as bf16, one 256-bit load per node visit) above; 1 = float, 2 = packed; takes effect at the next rt_upload_scene; results do not depend on it */
     RT_OPT_NODES_PACKED = 17,    /* read-only (rt_get_option): 1 when the uploaded scene's hierarchy holds packed nodes (see RT_OPT_NODE_FORMAT; instanced scenes and scenes whose bounds are not finite never do) */
-    RT_OPT_TILE_ORDER = 18,      /* 1 (default): the 8x8 tiles that were heaviest in the context's previous render call enter the work queue first, so that a launch ends on cheap work instead of waiting for its last heavy pixels (the first call after a resize / re-shard uses raster order); 0: always raster order; results do not depend on it */
+    RT_OPT_TILE_ORDER = 18,      /* 1 (default): in launches of at most 4 dispatches (the reference's one dispatch per frame) the 8x8 tiles that were heaviest in the context's previous such launch enter the work queue first, so that the launch ends on cheap work instead of waiting for its last heavy pixels (C3 single dispatch 1.52 -> 1.21 ms; the first call after a resize / re-shard uses raster order); 0: always raster order; results do not depend on it */
     RT_OPT_PIPELINE = 15,        /* 1 (default): when one rt_render_frames call needs several launches (more dispatches than the staging budget holds), they alternate between two streams, half of the staging planes each, so that a launch's blocks fill the SMs the previous one's drain leaves idle (the blends keep dispatch order); 0: one launch after the other; results do not depend on it */
     RT_OPT_ITEM_MODE = 13        /* work items of the trace kernel: 1 = one (pixel, dispatch) pair, frags staged and folded in dispatch order by a blend kernel; 2 = one pixel with all fused dispatches, the progressive store (wgsl:59-66) applied by the owning lane, no staging memory (coarse items: slower on fused launches); 0 = auto (default): 2 for single-dispatch launches, else 1; results do not depend on it */
 };

@@ -217,12 +217,11 @@ int launch(rt_ctx* c, int32_t first_frame, uint32_t n_frames, bool want_ids, int
         if (c->stream2 && (c->tile_order.n != lp.n_warp_tiles / 2u || c->tile_order.geom != geometry)) cudaStreamSynchronize(c->stream2);
         c->tile_order.poll();
         if (c->tile_order.ensure(lp.n_warp_tiles / 2u, geometry, c->stream) == cudaSuccess && c->tile_order.n != 0 && !c->tile_order.disabled) {
-            // the learned order pays where a launch's fixed cost matters and costs a little locality where it does not (same-box, ms per
-            // dispatch, on / off: C3 x 1 1.21 / 1.52, x 4 0.75 / 0.81, x 16 0.607 / 0.616, x 64 0.553 / 0.577, x 128 0.543 / 0.542; C2 x 32 0.283 / 0.296;
-            // C4 at 4K x 32 0.726 / 0.715): used up to 8,192 items per resident warp (16 dispatches at 1080p, 4 at 4K: C4 at 4K x 8 / x 16 lose 1.5 % with it)
-            const uint64_t items = (uint64_t)lp.n_warp_tiles * 32ull * n_frames, warps = (uint64_t)c->n_sms * 32ull;
-            // (longer launches neither use nor feed it: collecting the weights costs them 0.5 %)
-            if (items <= 8192ull * warps) { lp.tile_order = c->tile_order.current(); lp.tile_cost = c->tile_order.cost; c->tile_order.fed = true; }
+            // the learned order pays where a launch's fixed cost dominates — the reference's own pattern of one dispatch per frame — and
+            // costs a little (collecting the weights, some locality) where it does not.  Same-box, ms per dispatch, on / off: C3 x 1
+            // 1.21 / 1.52, x 2 0.88 / 1.05, x 4 0.75 / 0.81, x 16 0.607 / 0.616, x 128 0.543 / 0.542; C4 at 4K x 1 0.84 / 0.90, x 8 0.734 / 0.724;
+            // C1 x 8 0.152 / 0.149.  Hence: launches of at most 4 dispatches.
+            if (n_frames <= 4u) { lp.tile_order = c->tile_order.current(); lp.tile_cost = c->tile_order.cost; c->tile_order.fed = true; }
         } else cudaGetLastError();
     }
 
