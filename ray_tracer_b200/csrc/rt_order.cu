@@ -14,8 +14,7 @@
 namespace rt {
 
 namespace {
-// weight -> sort key: 32 levels of descending weight; inside a level the stable sort keeps raster order (neighbouring
-// tiles share hierarchy nodes, which the L1 of the SMs working on them likes)
+// heaviest tile and the sum of all weights: stats[0] (max), stats[4..5] (64-bit sum)
 __global__ void order_max(uint32_t n, const uint32_t* __restrict__ cost, uint32_t* __restrict__ out)
 {
     uint32_t m = 0; unsigned long long sum = 0;
@@ -29,8 +28,8 @@ __global__ void order_max(uint32_t n, const uint32_t* __restrict__ cost, uint32_
 #ifndef RT_ORDER_LEVELS
 #define RT_ORDER_LEVELS 32u
 #endif
-// level width = max weight / levels, as a shift
-// ... and whether the weights are flat (heaviest tile below twice the mean): then there is nothing to reorder
+// level width = max weight / levels, as a shift (stats[1]), and whether the weights are flat (stats[2]: heaviest tile below
+// twice the mean): then there is nothing to reorder
 __global__ void order_shift(uint32_t* m, uint32_t n)
 {
     uint32_t s = 0;
@@ -39,6 +38,8 @@ __global__ void order_shift(uint32_t* m, uint32_t n)
     m[2] = ((unsigned long long)m[0] * n * 4ull < (unsigned long long)RT_ORDER_FLAT_X4 * sum) ? 1u : 0u;
     m[1] = s; m[0] = 0u; *(unsigned long long*)(m + 4) = 0ull;
 }
+// weight -> sort key: RT_ORDER_LEVELS levels of descending weight; inside a level the stable sort keeps raster order
+// (neighbouring tiles share hierarchy nodes, which the L1 of the SMs working on them likes); the weights are cleared
 __global__ void order_keys_dyn(uint32_t n, uint32_t* __restrict__ cost, uint32_t* __restrict__ keys, uint32_t* __restrict__ vals, const uint32_t* __restrict__ m)
 {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
